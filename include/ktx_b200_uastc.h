@@ -1,0 +1,101 @@
+/* ktx_b200_uastc.h -- C ABI of the B200 (sm_100a) UASTC LDR 4x4 module.
+ *
+ * This is the drop-in boundary: the only symbols libktx's glue (lib/src/basis_encode.cpp,
+ * lib/src/basis_transcode.cpp) needs in order to route UASTC LDR 4x4 work to the GPU.  Plain C types only.
+ * Each entry point names the reference interface it replaces (paths relative to the KTX-Software checkout;
+ * ENC/ = external/basis_universal/encoder/, XC/ = external/basis_universal/transcoder/).
+ *
+ * Threading: every call is re-entrant; calls from different host threads run on different CUDA streams.
+ * Errors: 0 = success; negative = B200_E_* below; b200_uastc_last_error() returns a thread-local message.
+ * There is NO CPU fallback: if no sm_100 device is usable the calls fail with B200_E_NO_DEVICE.
+ */
+#ifndef KTX_B200_UASTC_H
+#define KTX_B200_UASTC_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_E_NO_DEVICE (-1)     /* maps to KTX_UNSUPPORTED_FEATURE in the glue */
+#define B200_E_INVALID_VALUE (-2) /* KTX_INVALID_VALUE */
+#define B200_E_OUT_OF_MEMORY (-3) /* KTX_OUT_OF_MEMORY */
+#define B200_E_CUDA (-4)          /* KTX_INVALID_OPERATION */
+#define B200_E_BAD_BLOCK (-5)     /* KTX_TRANSCODE_FAILED: the input holds an invalid UASTC block */
+
+/* Transcode targets; numeric values are ktx_transcode_fmt_e's (lib/include/ktx.h:1696-1703). */
+#define B200_TTF_BC7_RGBA 6
+#define B200_TTF_ASTC_4x4_RGBA 10
+
+/* Replaces basisu_encoder_init() (lib/src/basis_encode.cpp:625-633) and basisu_transcoder_init()
+ * (lib/src/basis_transcode.cpp:427-436).  Idempotent and thread-safe.  Selects the current CUDA device
+ * of the calling thread (or device 0), creates the stream pool. */
+int b200_uastc_init(void);
+void b200_uastc_shutdown(void);
+const char* b200_uastc_last_error(void);
+/* Number of kernel launches this library has issued since init (bench.py's gpu_launches). */
+uint64_t b200_uastc_launch_count(void);
+
+/* One (level, layer, face/slice) image's worth of blocks inside the texture's pData. */
+typedef struct b200_xcode_span {
+  uint64_t src_offset; /* byte offset of the image's first UASTC block in src_base */
+  uint64_t dst_offset; /* byte offset of its first output block in dst_base       */
+  uint64_t n_blocks;   /* num_blocks_x * num_blocks_y                              */
+} b200_xcode_span;
+
+/* Replaces the per-image loop of transcodeUastcLDR4x4 (lib/src/basis_transcode.cpp:743-804), i.e. every call of
+ * basisu_lowlevel_uastc_ldr_4x4_transcoder::transcode_image (XC/basisu_transcoder.cpp:10331) -> transcode_slice
+ * (:10068) -> transcode_uastc_to_bc7 (:16172) / transcode_uastc_to_astc (:15649), for a whole texture in one call.
+ * HOST pointers (pageable or pinned; pinned is DMA'd directly).  On B200_E_BAD_BLOCK *bad_span (if non-NULL)
+ * receives the index of the first span holding an invalid block, as transcode_slice's `return false` would
+ * have surfaced it (XC:10299-10303). */
+int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t n_spans,
+                         const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span);
+
+/* Device-resident variant (roofline runs; no PCIe in the timed region).  d_src/d_dst are device pointers to
+ * n_blocks contiguous 16-byte blocks; `stream` is a cudaStream_t (NULL = the library's stream for this thread).
+ * d_first_bad (device uint64_t*, may be NULL) receives min(index of invalid blocks) or UINT64_MAX.
+ * Asynchronous with respect to the host when a stream is given. */
+int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, uint64_t n_blocks, void* stream,
+                             uint64_t* d_first_bad);
+
+/* ---- encode ---------------------------------------------------------------------------------------- */
+
+typedef struct b200_image {
+  const uint8_t* rgba;      /* RGBA8, post-swizzle (lib/src/basis_encode.cpp:806-833 did the copy/swizzle) */
+  uint32_t width, height;   /* in pixels; edge texels are replicated to a multiple of 4 (ENC/basisu_comp.cpp:2449) */
+  uint32_t row_pitch_bytes; /* 0 = width*4 */
+} b200_image;
+
+/* Mirrors the fields of ktxBasisParams that reach the UASTC LDR encoder (lib/include/ktx.h:1455-1625) after the
+ * glue's mapping (lib/src/basis_encode.cpp:881-918). */
+typedef struct b200_uastc_params {
+  uint32_t struct_size;      /* sizeof(b200_uastc_params) */
+  uint32_t pack_flags;       /* ktx_pack_uastc_flag_bits_e == basisu cPackUASTC* (ENC/basisu_uastc_enc.h:24-63) */
+  uint32_t rdo_enable;       /* uastcRDO */
+  float rdo_lambda;          /* uastcRDOQualityScalar, 0 -> 1.0 */
+  uint32_t rdo_dict_size;    /* uastcRDODictSize, 0 -> 4096 */
+  float rdo_max_smooth_block_error_scale; /* 0 -> 10 */
+  float rdo_max_smooth_block_std_dev;     /* 0 -> 18 */
+  uint32_t rdo_total_jobs;   /* min(4, threadCount) as ENC/basisu_comp.cpp:1574-1576; 0/1 = one serial chain */
+  uint32_t reserved[4];
+} b200_uastc_params;
+
+/* Replaces basis_compressor::process -> encode_slices_to_uastc_4x4_ldr (ENC/basisu_comp.cpp:1474-1591) and the
+ * .basis unpicking (lib/src/basis_encode.cpp:1084-1150) for codec KTX_BASIS_CODEC_UASTC_LDR_4x4.
+ * out_blocks[i] receives ceil(w/4)*ceil(h/4)*16 bytes in raster block order.  *out_any_alpha = 1 if any input
+ * texel had alpha < 255 (what cBASISHeaderFlagHasAlphaSlices told the glue, basis_encode.cpp:1284-1286). */
+int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params,
+                      uint8_t* const* out_blocks, uint32_t* out_any_alpha);
+
+/* Device-resident variant: d_block_pixels = n_blocks x 64 bytes (4x4 RGBA8 texels, raster within the block, as
+ * basis_compressor::extract_source_blocks lays them out, ENC/basisu_comp.cpp:2705-2766); d_out = n_blocks x 16 B. */
+int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64_t n_blocks, uint32_t pack_flags,
+                                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KTX_B200_UASTC_H */

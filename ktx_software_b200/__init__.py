@@ -1,0 +1,9 @@
+"""ktx_software_b200 -- B200-native UASTC LDR 4x4 encode / transcode behind libktx's C API.
+
+The product is ktx_software_b200/libuastc_b200.so (CUDA, sm_100a; C ABI in include/ktx_b200_uastc.h).  This
+package is the thin host-side mirror used by the tests and the bench: ctypes bindings (api.py) and a mirror of
+libktx's ktxTexture2_TranscodeBasis / ktxTexture2_CompressBasisEx marshalling (ktx2.py).  There is no CPU
+fallback anywhere in this package: if the CUDA library is missing, or no B200 is visible, calls raise.
+"""
+from .api import (B200Error, lib, init, transcode, transcode_dev, launch_count, TTF_BC7_RGBA, TTF_ASTC_4x4_RGBA,  # noqa: F401
+                  EXPORTED_SYMBOLS)

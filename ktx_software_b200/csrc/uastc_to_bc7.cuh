@@ -1,0 +1,473 @@
+// uastc_to_bc7.cuh -- UASTC -> BC7 block (restates transcode_uastc_to_bc7 + encode_bc7_block, reference
+// external/basis_universal/transcoder/basisu_transcoder.cpp:15532-15647 (p-bit pickers), :15669-16161 (per-mode
+// mapping) and :14292-14459 (BC7 bit packer)).  Output must be bit-exact with the reference.
+#pragma once
+#include "uastc_unpack.cuh"
+
+namespace ub {
+
+// The BC7 block under construction: selectors stay packed (ibits per texel) the whole way.
+struct Bc7Build {
+  uint32_t mode, partition, rotation;
+  uint32_t lo[3], hi[3];   // r | g<<8 | b<<16 | a<<24 per subset
+  uint32_t pbits;          // bit (2k) = low p-bit of subset k, bit (2k+1) = high p-bit
+  uint64_t sel, asel;      // colour / alpha selectors, uniform width
+};
+
+UB_FN uint32_t px_c(uint32_t v, uint32_t c) { return (v >> (8 * c)) & 255u; }
+UB_FN uint32_t px_set(uint32_t v, uint32_t c, uint32_t x) { return (v & ~(255u << (8 * c))) | (x << (8 * c)); }
+
+// One channel of the p-bit search: quantise x (= u/255) to `total_bits` with p-bit p, return the (total_bits) code.
+UB_FN uint32_t pbit_quant(float x, float scalep, int iscalep, int p) {
+  const float t = f_add(f_div(f_sub(f_mul(x, scalep), (float)p), 2.0f), .5f);
+  return (uint32_t)clampi(((int)t) * 2 + p, p, iscalep - 1 + p);
+}
+UB_FN uint32_t pbit_expand(uint32_t q, uint32_t total_bits) {
+  uint32_t s = (q << (8 - total_bits)) & 255u;
+  s |= (s >> total_bits);
+  return s;
+}
+
+// determine_unique_pbits (XC:15585-15647).  u_lo/u_hi hold the 8-bit unquantised endpoints per channel; a channel
+// marked in `one_mask` is the constant 1.0f (opaque alpha).  Returns packed 7/5-bit endpoints and the two p-bits.
+UB_FN void unique_pbits(uint32_t total_comps, uint32_t comp_bits, uint32_t u_lo, uint32_t u_hi, uint32_t one_mask,
+                        uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
+  const uint32_t total_bits = comp_bits + 1;
+  const int iscalep = (1 << total_bits) - 1;
+  const float scalep = (float)iscalep;
+  float xl[4], xh[4];
+#pragma unroll
+  for (uint32_t c = 0; c < 4; c++) {
+    xl[c] = ((one_mask >> c) & 1u) ? 1.0f : f_div((float)px_c(u_lo, c), 255.0f);
+    xh[c] = ((one_mask >> c) & 1u) ? 1.0f : f_div((float)px_c(u_hi, c), 255.0f);
+  }
+  float best0 = 1e+9f, best1 = 1e+9f;
+  out_lo = 0; out_hi = 0; pb = 0;
+#pragma unroll
+  for (int p = 0; p < 2; p++) {
+    uint32_t qmin = 0, qmax = 0;
+    float e0 = 0, e1 = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      const uint32_t a = pbit_quant(xl[c], scalep, iscalep, p);
+      const uint32_t b = pbit_quant(xh[c], scalep, iscalep, p);
+      qmin |= (a >> 1) << (8 * c);
+      qmax |= (b >> 1) << (8 * c);
+      if (c < total_comps) {
+        const float da = f_sub((float)pbit_expand(a, total_bits), f_mul(xl[c], 255.0f));
+        const float db = f_sub((float)pbit_expand(b, total_bits), f_mul(xh[c], 255.0f));
+        e0 = f_add(e0, f_mul(da, da));
+        e1 = f_add(e1, f_mul(db, db));
+      }
+    }
+    if (e0 < best0) { best0 = e0; pb = (pb & ~1u) | (uint32_t)p; out_lo = qmin; }
+    if (e1 < best1) { best1 = e1; pb = (pb & ~2u) | ((uint32_t)p << 1); out_hi = qmax; }
+  }
+}
+
+// determine_shared_pbits (XC:15532-15582), BC7 mode 1 only (3 comps, 6 bits, alpha = 1.0f)
+UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
+  const uint32_t total_bits = 7;
+  const int iscalep = 127;
+  const float scalep = 127.0f;
+  float xl[4], xh[4];
+#pragma unroll
+  for (uint32_t c = 0; c < 3; c++) {
+    xl[c] = f_div((float)px_c(u_lo, c), 255.0f);
+    xh[c] = f_div((float)px_c(u_hi, c), 255.0f);
+  }
+  xl[3] = 1.0f; xh[3] = 1.0f;
+  float best = 1e+9f;
+  out_lo = 0; out_hi = 0; pb = 0;
+#pragma unroll
+  for (int p = 0; p < 2; p++) {
+    uint32_t qmin = 0, qmax = 0;
+    float err = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      const uint32_t a = pbit_quant(xl[c], scalep, iscalep, p);
+      const uint32_t b = pbit_quant(xh[c], scalep, iscalep, p);
+      qmin |= (a >> 1) << (8 * c);
+      qmax |= (b >> 1) << (8 * c);
+      if (c < 3) {
+        const float da = f_sub(f_div((float)pbit_expand(a, total_bits), 255.0f), xl[c]);
+        const float db = f_sub(f_div((float)pbit_expand(b, total_bits), 255.0f), xh[c]);
+        err = f_add(err, f_add(f_mul(da, da), f_mul(db, db)));
+      }
+    }
+    if (err < best) { best = err; pb = (uint32_t)p * 3u; out_lo = qmin; out_hi = qmax; }
+  }
+}
+
+// Re-pack the UASTC weights (entries of wb bits) of one plane into `ob`-bit BC7 selectors through a tiny value map.
+// plane_stride = 1 (single plane) or 2; plane = 0/1.  map4 holds up to 32 4-bit outputs? no: see callers.
+UB_FN uint64_t remap_selectors(const UnpackedUastc& u, uint32_t plane_stride, uint32_t plane, uint32_t ob, int kind) {
+  // kind: 0 identity, 1 = 5->4 bits, 2 = 2->4 bits, 3 = 3->4 bits, 4 = 1->2 bits (0 / 3)
+  const uint32_t wb = md_weight_bits(u.desc);
+  uint64_t r = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    uint32_t w = bits_get(u.w, (i * plane_stride + plane) * wb, wb);
+    if (kind == 1) {
+      // s_bc7_5_to_4 (XC:15756): 0,0,1,1,2,2,3,3,4,4,5,5,6,6,6,7,8,9,9,9,10,10,11,11,12,12,13,13,14,14,15,15
+      const uint64_t t_lo = 0x7666554433221100ull, t_hi = 0xFFEEDDCCBBAA9998ull;
+      w = (uint32_t)(((w < 16 ? t_lo : t_hi) >> ((w & 15u) * 4)) & 15u);
+    } else if (kind == 2) {
+      w = w * 5u;                                  // 0,5,10,15
+    } else if (kind == 3) {
+      w = (uint32_t)((0xFDB96420ull >> (w * 4)) & 15u);  // 0,2,4,6,9,11,13,15
+    } else if (kind == 4) {
+      w = w ? 3u : 0u;
+    }
+    r |= (uint64_t)w << (i * ob);
+  }
+  return r;
+}
+
+// expand a "texel belongs to subset k" test into an ob-bit-per-texel XOR mask
+UB_FN uint64_t subset_mask64(uint32_t pat, uint32_t k, uint32_t ob) {
+  const uint64_t ones = lowmask64(ob);
+  uint64_t m = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++)
+    if (((pat >> (2 * i)) & 3u) == k) m |= ones << (i * ob);
+  return m;
+}
+
+UB_FN uint32_t bc7_3_to_2(uint32_t p, uint32_t k) {  // bc7_convert_partition_index_3_to_2 (XC:13946)
+  const uint32_t g = k >> 1;
+  uint32_t r;
+  if (g == 0) r = (p <= 1) ? 0u : 1u;
+  else if (g == 1) r = (p == 0) ? 0u : 1u;
+  else r = ((p == 0) || (p == 2)) ? 0u : 1u;
+  return (k & 1u) ? 1u - r : r;
+}
+
+UB_FN uint32_t ep_unq(const UnpackedUastc& u, uint32_t er, uint32_t i) { return astc_unquant(er, u.ep[i]); }
+
+// Gather the unquantised colour (RGB[A]) of one subset from the RR GG BB (AA) endpoint list.
+UB_FN void subset_endpoints(const UnpackedUastc& u, uint32_t er, uint32_t base, uint32_t comps, uint32_t& lo, uint32_t& hi) {
+  lo = 0; hi = 0;
+#pragma unroll
+  for (uint32_t c = 0; c < 4; c++)
+    if (c < comps) {
+      lo |= ep_unq(u, er, base + 2 * c) << (8 * c);
+      hi |= ep_unq(u, er, base + 2 * c + 1) << (8 * c);
+    }
+}
+
+// Per-mode mapping (XC:15669-16161).
+UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
+  const uint32_t mode = u.mode;
+  const uint32_t er = md_endpoint_range(u.desc);
+  const uint32_t comps = md_comps(u.desc);
+  o.partition = 0; o.rotation = 0; o.pbits = 0; o.sel = 0; o.asel = 0;
+#pragma unroll
+  for (int k = 0; k < 3; k++) { o.lo[k] = 0; o.hi[k] = 0; }
+
+  if (mode == UASTC_MODE_SOLID) {
+    const uint32_t s = u.solid;
+    uint32_t e0 = 0, e1 = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      e0 += UBT(bc7_mode6_opt)[px_c(s, c) * 2 + 0] & 0xFFFFu;
+      e1 += UBT(bc7_mode6_opt)[px_c(s, c) * 2 + 1] & 0xFFFFu;
+    }
+    if (e0 > 0 && e1 > 0) {
+      o.mode = 5;
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) {
+        const uint32_t t = UBT(bc7_mode5_opt)[px_c(s, c)];
+        o.lo[0] |= ((t >> 16) & 255u) << (8 * c);
+        o.hi[0] |= (t >> 24) << (8 * c);
+      }
+      o.lo[0] |= s & 0xFF000000u;
+      o.hi[0] |= s & 0xFF000000u;
+      o.sel = 0x55555555ull;  // index 1 in every 2-bit selector
+    } else {
+      o.mode = 6;
+      const uint32_t bp = (e1 < e0) ? 1u : 0u;
+#pragma unroll
+      for (uint32_t c = 0; c < 4; c++) {
+        const uint32_t t = UBT(bc7_mode6_opt)[px_c(s, c) * 2 + bp];
+        o.lo[0] |= ((t >> 16) & 255u) << (8 * c);
+        o.hi[0] |= (t >> 24) << (8 * c);
+      }
+      o.pbits = bp * 3u;
+      o.sel = 0x5555555555555555ull;  // index 5 in every 4-bit selector
+    }
+    return;
+  }
+
+  switch (mode) {
+    case 0: case 5: case 10: case 12: case 14: case 15: case 18: {
+      o.mode = 6;
+      uint32_t lo, hi, one_mask = 0;
+      if (comps == 2) {
+        const uint32_t l0 = ep_unq(u, er, 0), l1 = ep_unq(u, er, 1);
+        lo = l0 * 0x010101u | (ep_unq(u, er, 2) << 24);
+        hi = l1 * 0x010101u | (ep_unq(u, er, 3) << 24);
+      } else {
+        subset_endpoints(u, er, 0, comps, lo, hi);
+        if (comps == 3) one_mask = 8;
+      }
+      uint32_t pb;
+      unique_pbits(comps == 2 ? 4 : comps, 7, lo, hi, one_mask, o.lo[0], o.hi[0], pb);
+      if (comps == 3) { o.lo[0] = px_set(o.lo[0], 3, 127); o.hi[0] = px_set(o.hi[0], 3, 127); }
+      o.pbits = pb;
+      const int kind = (mode == 18) ? 1 : (mode == 14) ? 2 : ((mode == 5) || (mode == 12)) ? 3 : 0;
+      o.sel = remap_selectors(u, 1, 0, 4, kind);
+      break;
+    }
+    case 1: {
+      o.mode = 3;
+      uint32_t lo = 0, hi = 0;
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) { lo |= (uint32_t)u.ep[2 * c] << (8 * c); hi |= (uint32_t)u.ep[2 * c + 1] << (8 * c); }
+      uint32_t qlo, qhi, pb;
+      unique_pbits(3, 7, lo, hi, 8, qlo, qhi, pb);
+      o.lo[0] = o.lo[1] = qlo & 0xFFFFFFu;
+      o.hi[0] = o.hi[1] = qhi & 0xFFFFFFu;
+      o.pbits = pb | (pb << 2);
+      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      break;
+    }
+    case 2: {
+      o.mode = 1;
+      const uint32_t cpd = UBT(common2)[u.pattern];
+      o.partition = cpd & 255u;
+      const uint32_t inv = cpd >> 24;
+#pragma unroll
+      for (uint32_t s = 0; s < 2; s++) {
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+          lo |= ((uint32_t)u.ep[c * 2 + s * 6] * 17u) << (8 * c);
+          hi |= ((uint32_t)u.ep[c * 2 + s * 6 + 1] * 17u) << (8 * c);
+        }
+        uint32_t qlo, qhi, pb;
+        shared_pbits(lo, hi, qlo, qhi, pb);
+        const uint32_t k = inv ? 1 - s : s;
+        o.lo[k] = qlo & 0xFFFFFFu;
+        o.hi[k] = qhi & 0xFFFFFFu;
+        o.pbits |= (pb & 1u) << (2 * k);
+      }
+      o.sel = remap_selectors(u, 1, 0, 3, 0);
+      break;
+    }
+    case 3: {
+      o.mode = 2;
+      const uint32_t cpd = UBT(common3)[u.pattern];
+      o.partition = cpd & 255u;
+      const uint32_t perm = cpd >> 24;
+#pragma unroll
+      for (uint32_t s = 0; s < 3; s++) {
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+          lo |= ((ep_unq(u, er, c * 2 + s * 6) * 31u + 127u) / 255u) << (8 * c);
+          hi |= ((ep_unq(u, er, c * 2 + 1 + s * 6) * 31u + 127u) / 255u) << (8 * c);
+        }
+        const uint32_t k = UBT(astc_to_bc7_perm)[perm * 3 + s];
+        // k is data dependent: write through selects so lo[]/hi[] stay in registers
+#pragma unroll
+        for (uint32_t q = 0; q < 3; q++) if (q == k) { o.lo[q] = lo; o.hi[q] = hi; }
+      }
+      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      break;
+    }
+    case 4: {
+      o.mode = 3;
+      const uint32_t cpd = UBT(common2)[u.pattern];
+      o.partition = cpd & 255u;
+      const uint32_t inv = cpd >> 24;
+#pragma unroll
+      for (uint32_t s = 0; s < 2; s++) {
+        uint32_t lo, hi;
+        subset_endpoints(u, er, s * 6, 3, lo, hi);
+        uint32_t qlo, qhi, pb;
+        unique_pbits(3, 7, lo, hi, 8, qlo, qhi, pb);
+        const uint32_t k = inv ? 1 - s : s;
+        o.lo[k] = px_set(qlo, 3, 127);
+        o.hi[k] = px_set(qhi, 3, 127);
+        o.pbits |= pb << (2 * k);
+      }
+      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      break;
+    }
+    case 6: case 11: case 13: case 17: {
+      o.mode = 5;
+      o.rotation = (u.ccs + 1) & 3u;
+      if (comps == 2) {
+        const uint32_t l = (ep_unq(u, er, 0) * 127u + 127u) / 255u, h = (ep_unq(u, er, 1) * 127u + 127u) / 255u;
+        o.lo[0] = l * 0x010101u | (ep_unq(u, er, 2) << 24);
+        o.hi[0] = h * 0x010101u | (ep_unq(u, er, 3) << 24);
+      } else {
+#pragma unroll
+        for (uint32_t ac = 0; ac < 4; ac++) {
+          uint32_t bc = ac;
+          if (ac == u.ccs) bc = 3; else if (ac == 3) bc = u.ccs;
+          uint32_t l = 255, h = 255;
+          if (ac < comps) { l = ep_unq(u, er, ac * 2); h = ep_unq(u, er, ac * 2 + 1); }
+          if (bc < 3) { l = (l * 127u + 127u) / 255u; h = (h * 127u + 127u) / 255u; }
+          o.lo[0] |= l << (8 * bc);
+          o.hi[0] |= h << (8 * bc);
+        }
+      }
+      const int kind = (mode == 13) ? 4 : 0;
+      o.sel = remap_selectors(u, 2, 0, 2, kind);
+      o.asel = remap_selectors(u, 2, 1, 2, kind);
+      break;
+    }
+    case 7: {
+      o.mode = 2;
+      const uint32_t cpd = UBT(common7)[u.pattern];
+      o.partition = cpd & 255u;
+      const uint32_t kk = cpd >> 24;
+#pragma unroll
+      for (uint32_t bp = 0; bp < 3; bp++) {
+        const uint32_t ap = bc7_3_to_2(bp, kk);
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+          // ap is 0/1: select between the two subsets' endpoints without dynamic indexing
+          const uint32_t l0 = u.ep[c * 2], l1 = u.ep[c * 2 + 6], h0 = u.ep[c * 2 + 1], h1 = u.ep[c * 2 + 7];
+          o.lo[bp] |= ((astc_unquant(er, ap ? l1 : l0) * 31u + 127u) / 255u) << (8 * c);
+          o.hi[bp] |= ((astc_unquant(er, ap ? h1 : h0) * 31u + 127u) / 255u) << (8 * c);
+        }
+      }
+      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      break;
+    }
+    default: {  // 9, 16
+      o.mode = 7;
+      const uint32_t cpd = UBT(common2)[u.pattern];
+      o.partition = cpd & 255u;
+      const uint32_t inv = cpd >> 24;
+#pragma unroll
+      for (uint32_t s = 0; s < 2; s++) {
+        uint32_t lo, hi;
+        if (comps == 2) {
+          lo = ep_unq(u, er, s * 4) * 0x010101u | (ep_unq(u, er, 2 + s * 4) << 24);
+          hi = ep_unq(u, er, 1 + s * 4) * 0x010101u | (ep_unq(u, er, 3 + s * 4) << 24);
+        } else {
+          subset_endpoints(u, er, s * 8, 4, lo, hi);
+        }
+        uint32_t qlo, qhi, pb;
+        unique_pbits(4, 5, lo, hi, 0, qlo, qhi, pb);
+        const uint32_t k = inv ? 1 - s : s;
+        o.lo[k] = qlo; o.hi[k] = qhi;
+        o.pbits |= pb << (2 * k);
+      }
+      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      break;
+    }
+  }
+}
+
+// BC7 per-mode constants (XC:14262-14272), packed: [2:0]? -- kept as tiny switch-free tables in registers.
+UB_FN uint32_t bc7_subsets(uint32_t m) { return (0x21112323u >> (4 * m)) & 15u; }      // 3,2,3,2,1,1,1,2
+UB_FN uint32_t bc7_color_prec(uint32_t m) { return (0x57757564u >> (4 * m)) & 15u; }   // 4,6,5,7,5,7,7,5
+UB_FN uint32_t bc7_alpha_prec(uint32_t m) { return (0x57860000u >> (4 * m)) & 15u; }   // 0,0,0,0,6,8,7,5
+UB_FN uint32_t bc7_index_bits(uint32_t m) { return (0x24222233u >> (4 * m)) & 15u; }   // 3,3,2,2,2,2,4,2
+
+// encode_bc7_block (XC:14292-14459) for the BC7 modes UASTC maps to (1,2,3,5,6,7; index_selector is always 0).
+UB_FN Bits128 bc7_pack(Bc7Build& o) {
+  const uint32_t m = o.mode;
+  const uint32_t subsets = bc7_subsets(m);
+  const uint32_t ib = bc7_index_bits(m);
+  uint32_t pat = 0;
+  uint32_t anchor[3] = {0, 0, 0};
+  if (subsets == 2) { pat = spread_mask2(UBT(bc7_part2)[o.partition]); anchor[1] = UBT(bc7_anchor2)[o.partition]; }
+  else if (subsets == 3) { pat = UBT(bc7_part3)[o.partition]; anchor[1] = UBT(bc7_anchor3a)[o.partition]; anchor[2] = UBT(bc7_anchor3b)[o.partition]; }
+
+  const bool sep_alpha = (m == 5);
+  const bool shared_p = (m == 1);
+#pragma unroll
+  for (uint32_t k = 0; k < 3; k++) {
+    if (k < subsets) {
+      const uint32_t a = anchor[k];
+      if ((o.sel >> (a * ib + ib - 1)) & 1ull) {
+        o.sel ^= subset_mask64(pat, k, ib);
+        if (sep_alpha) {
+          const uint32_t l = o.lo[k], h = o.hi[k];
+          o.lo[k] = (l & 0xFF000000u) | (h & 0xFFFFFFu);
+          o.hi[k] = (h & 0xFF000000u) | (l & 0xFFFFFFu);
+        } else {
+          const uint32_t t = o.lo[k]; o.lo[k] = o.hi[k]; o.hi[k] = t;
+        }
+        if (!shared_p) {
+          const uint32_t pb = (o.pbits >> (2 * k)) & 3u;
+          o.pbits = (o.pbits & ~(3u << (2 * k))) | ((((pb & 1u) << 1) | (pb >> 1)) << (2 * k));
+        }
+      }
+      if (sep_alpha) {
+        if ((o.asel >> (a * 2 + 1)) & 1ull) {
+          o.asel ^= subset_mask64(pat, k, 2);
+          const uint32_t l = o.lo[k], h = o.hi[k];
+          o.lo[k] = (h & 0xFF000000u) | (l & 0xFFFFFFu);
+          o.hi[k] = (l & 0xFF000000u) | (h & 0xFFFFFFu);
+        }
+      }
+    }
+  }
+
+  BitWriter bw;
+  bw.init();
+  bw.put(1u << m, m + 1);
+  if (m == 5) bw.put(o.rotation, 2);
+  if (subsets > 1) bw.put(o.partition, (m == 0) ? 4 : 6);
+  const uint32_t comps = (m >= 4) ? 4u : 3u;
+  const uint32_t cp = bc7_color_prec(m), ap = bc7_alpha_prec(m);
+#pragma unroll
+  for (uint32_t c = 0; c < 4; c++) {
+    if (c < comps) {
+      const uint32_t nb = (c == 3) ? ap : cp;
+#pragma unroll
+      for (uint32_t k = 0; k < 3; k++)
+        if (k < subsets) { bw.put(px_c(o.lo[k], c), nb); bw.put(px_c(o.hi[k], c), nb); }
+    }
+  }
+  if (m == 1 || m == 3 || m == 6 || m == 7) {
+#pragma unroll
+    for (uint32_t k = 0; k < 3; k++)
+      if (k < subsets) {
+        bw.put((o.pbits >> (2 * k)) & 1u, 1);
+        if (!shared_p) bw.put((o.pbits >> (2 * k + 1)) & 1u, 1);
+      }
+  }
+  // selectors: drop each anchor's (now zero) MSB, highest position first so lower positions stay valid
+  {
+    uint32_t a1 = anchor[1], a2 = anchor[2];
+    uint64_t s = o.sel;
+    uint32_t total = 16 * ib;
+    if (subsets == 3) {
+      const uint32_t hi = a1 > a2 ? a1 : a2, lo = a1 > a2 ? a2 : a1;
+      s = u64_delete_bit(s, hi * ib + ib - 1);
+      s = u64_delete_bit(s, lo * ib + ib - 1);
+      total -= 2;
+    } else if (subsets == 2) {
+      s = u64_delete_bit(s, a1 * ib + ib - 1);
+      total -= 1;
+    }
+    s = u64_delete_bit(s, ib - 1);
+    total -= 1;
+    bw.put(s, total);
+  }
+  if (sep_alpha) {
+    const uint64_t s = u64_delete_bit(o.asel, 1);
+    bw.put(s, 31);
+  }
+  return bw.b;
+}
+
+// Full path for one block.  Returns false on an invalid UASTC block (output then zeroed).
+UB_FN bool transcode_block_to_bc7(const Bits128& src, Bits128& dst) {
+  UnpackedUastc u;
+  if (!unpack_uastc(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
+  Bc7Build o;
+  uastc_to_bc7_build(u, o);
+  dst = bc7_pack(o);
+  return true;
+}
+
+}  // namespace ub

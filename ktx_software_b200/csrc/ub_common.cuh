@@ -1,0 +1,156 @@
+// ub_common.cuh -- shared definitions for the B200 UASTC module.
+//
+// Every algorithmic routine in csrc/*.cuh is written once as a UB_FN function.  nvcc compiles it as
+// __device__ code for sm_100a (the product).  g++ can compile the very same headers as plain inline C++
+// (oracle/port_host.cpp), which is how the restated algorithm is diffed against the unmodified reference
+// on a box without a GPU.  The host build is test infrastructure only; the product library contains no
+// host implementation of the hot path.
+#pragma once
+#include <stdint.h>
+#include <string.h>
+#include <math.h>
+
+#ifdef __CUDACC__
+#define UB_FN __device__ __forceinline__
+#define UB_MFN __device__ __forceinline__
+#define UB_FN_NOINLINE __device__ __noinline__
+#define UB_TABLE(type, name, n) static __device__ const type ubt_##name[n]
+#else
+#define UB_FN static inline
+#define UB_MFN inline
+#define UB_FN_NOINLINE static
+#define UB_TABLE(type, name, n) static const type ubt_##name[n]
+#endif
+#define UBT(name) ubt_##name
+
+namespace ub {
+
+// ---- IEEE single ops with no contraction.  The reference is built with -ffp-contract=off (cmake/fp-settings.cmake:26)
+// so every float op rounds once; on the device we spell the rounding mode so ptxas can never fuse.
+#ifdef __CUDA_ARCH__
+UB_FN float f_add(float a, float b) { return __fadd_rn(a, b); }
+UB_FN float f_sub(float a, float b) { return __fsub_rn(a, b); }
+UB_FN float f_mul(float a, float b) { return __fmul_rn(a, b); }
+UB_FN float f_div(float a, float b) { return __fdiv_rn(a, b); }
+UB_FN float f_sqrt(float a) { return __fsqrt_rn(a); }
+UB_FN double d_add(double a, double b) { return __dadd_rn(a, b); }
+UB_FN double d_sub(double a, double b) { return __dsub_rn(a, b); }
+UB_FN double d_mul(double a, double b) { return __dmul_rn(a, b); }
+UB_FN double d_div(double a, double b) { return __ddiv_rn(a, b); }
+#else
+UB_FN float f_add(float a, float b) { return a + b; }
+UB_FN float f_sub(float a, float b) { return a - b; }
+UB_FN float f_mul(float a, float b) { return a * b; }
+UB_FN float f_div(float a, float b) { return a / b; }
+UB_FN float f_sqrt(float a) { return sqrtf(a); }
+UB_FN double d_add(double a, double b) { return a + b; }
+UB_FN double d_sub(double a, double b) { return a - b; }
+UB_FN double d_mul(double a, double b) { return a * b; }
+UB_FN double d_div(double a, double b) { return a / b; }
+#endif
+
+UB_FN int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+UB_FN uint32_t minu(uint32_t a, uint32_t b) { return a < b ? a : b; }
+UB_FN uint32_t maxu(uint32_t a, uint32_t b) { return a > b ? a : b; }
+
+// ---- a 128-bit little-endian bit string (one compressed block)
+struct Bits128 {
+  uint64_t lo, hi;
+};
+
+UB_FN uint64_t lowmask64(uint32_t n) { return n >= 64 ? ~0ull : ((1ull << n) - 1ull); }
+
+// bits [ofs, ofs+n) of b, n <= 32, zero-filled beyond bit 127
+UB_FN uint32_t bits_get(const Bits128& b, uint32_t ofs, uint32_t n) {
+  uint64_t v;
+  if (ofs >= 128) v = 0;
+  else if (ofs >= 64) v = b.hi >> (ofs - 64);
+  else if (ofs == 0) v = b.lo;
+  else v = (b.lo >> ofs) | (b.hi << (64 - ofs));
+  return (uint32_t)v & (uint32_t)lowmask64(n);
+}
+
+// 64 bits starting at ofs, zero-filled beyond bit 127
+UB_FN uint64_t bits_get64(const Bits128& b, uint32_t ofs) {
+  if (ofs >= 128) return 0;
+  if (ofs >= 64) return b.hi >> (ofs - 64);
+  if (ofs == 0) return b.lo;
+  return (b.lo >> ofs) | (b.hi << (64 - ofs));
+}
+
+UB_FN Bits128 bits_shr(const Bits128& b, uint32_t s) {
+  Bits128 r;
+  if (s == 0) return b;
+  if (s >= 128) { r.lo = 0; r.hi = 0; }
+  else if (s >= 64) { r.lo = b.hi >> (s - 64); r.hi = 0; }
+  else { r.lo = (b.lo >> s) | (b.hi << (64 - s)); r.hi = b.hi >> s; }
+  return r;
+}
+
+// OR `val` (n <= 64 significant bits) in at bit ofs; bits that fall past 127 are dropped
+UB_FN void bits_or(Bits128& b, uint32_t ofs, uint64_t val) {
+  if (ofs >= 128) return;
+  if (ofs >= 64) { b.hi |= val << (ofs - 64); return; }
+  b.lo |= val << ofs;
+  if (ofs) b.hi |= val >> (64 - ofs);
+}
+
+struct BitWriter {
+  Bits128 b;
+  uint32_t pos;
+  UB_MFN void init() { b.lo = 0; b.hi = 0; pos = 0; }
+  UB_MFN void put(uint64_t val, uint32_t n) { bits_or(b, pos, val); pos += n; }
+};
+
+// insert a zero bit at position p (bits >= p move up by one)
+UB_FN Bits128 bits_insert0(const Bits128& b, uint32_t p) {
+  Bits128 r;
+  if (p >= 64) {
+    const uint64_t m = lowmask64(p - 64);
+    r.lo = b.lo;
+    r.hi = (b.hi & m) | ((b.hi & ~m) << 1);
+  } else {
+    const uint64_t m = lowmask64(p);
+    r.lo = (b.lo & m) | ((b.lo & ~m) << 1);
+    r.hi = (b.hi << 1) | (b.lo >> 63);
+  }
+  return r;
+}
+
+// delete bit p of a 64-bit word (bits above move down)
+UB_FN uint64_t u64_delete_bit(uint64_t x, uint32_t p) {
+  const uint64_t m = lowmask64(p);
+  return (x & m) | ((x >> 1) & ~m);
+}
+
+UB_FN uint64_t brev64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+  return __brevll(x);
+#else
+  x = ((x >> 1) & 0x5555555555555555ull) | ((x & 0x5555555555555555ull) << 1);
+  x = ((x >> 2) & 0x3333333333333333ull) | ((x & 0x3333333333333333ull) << 2);
+  x = ((x >> 4) & 0x0F0F0F0F0F0F0F0Full) | ((x & 0x0F0F0F0F0F0F0F0Full) << 4);
+  x = ((x >> 8) & 0x00FF00FF00FF00FFull) | ((x & 0x00FF00FF00FF00FFull) << 8);
+  x = ((x >> 16) & 0x0000FFFF0000FFFFull) | ((x & 0x0000FFFF0000FFFFull) << 16);
+  return (x >> 32) | (x << 32);
+#endif
+}
+
+#include "uastc_tables.inc"
+
+// ---- decoded fields of ubt_uastc_mode_desc (see tools/gen_tables.py for the packing)
+UB_FN uint32_t md_weight_bits(uint32_t d) { return d & 7; }
+UB_FN uint32_t md_endpoint_range(uint32_t d) { return (d >> 3) & 31; }
+UB_FN uint32_t md_subsets(uint32_t d) { return (d >> 8) & 3; }
+UB_FN uint32_t md_dual_plane(uint32_t d) { return (d >> 10) & 1; }
+UB_FN uint32_t md_comps(uint32_t d) { return (d >> 11) & 7; }
+UB_FN uint32_t md_hint_bits(uint32_t d) { return (d >> 14) & 31; }
+UB_FN uint32_t md_huff_len(uint32_t d) { return (d >> 19) & 15; }
+UB_FN uint32_t md_huff_code(uint32_t d) { return (d >> 23) & 127; }
+
+UB_FN uint32_t astc_unquant(uint32_t range, uint32_t code) { return UBT(astc_unquant)[range * 256 + code] & 0xFF; }
+
+const uint32_t UASTC_MODE_SOLID = 8;
+const uint32_t UASTC_TOTAL_MODES = 19;
+
+}  // namespace ub

@@ -1,0 +1,223 @@
+"""ctypes access to the checkers: oracle/_ref/libref_uastc.so (the UNMODIFIED reference, built by oracle/Makefile)
+and oracle/libport_uastc.so (host build of the product's own algorithm headers).  Test infrastructure only."""
+import ctypes, os, subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SO = os.path.join(ROOT, "oracle/_ref/libref_uastc.so")
+PORT_SO = os.path.join(ROOT, "oracle/libport_uastc.so")
+_u8p = ctypes.POINTER(ctypes.c_uint8)
+
+
+def _p(a):
+    return a.ctypes.data_as(_u8p)
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+_ref = None
+_port = None
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = ctypes.CDLL(REF_SO)
+        _ref.ref_transcode.restype = ctypes.c_int64
+        _ref.ref_transcode.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, _u8p]
+        _ref.ref_transcode_mt.restype = ctypes.c_int64
+        _ref.ref_transcode_mt.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, _u8p, ctypes.c_uint32]
+        _ref.ref_encode_blocks.argtypes = [_u8p, ctypes.c_uint32, ctypes.c_uint32, _u8p, ctypes.c_uint32]
+        _ref.ref_encode_image.argtypes = [_u8p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, _u8p, ctypes.c_uint32]
+        _ref.ref_extract_blocks.argtypes = [_u8p, ctypes.c_uint32, ctypes.c_uint32, _u8p]
+        _ref.ref_unpack_rgba.restype = ctypes.c_int64
+        _ref.ref_unpack_rgba.argtypes = [_u8p, ctypes.c_uint64, _u8p, ctypes.c_int]
+        _ref.ref_unpack_bc7.argtypes = [_u8p, ctypes.c_uint64, _u8p]
+        _ref.ref_rdo.argtypes = [_u8p, ctypes.c_uint32, _u8p, ctypes.c_float, ctypes.c_uint32, ctypes.c_float, ctypes.c_float,
+                                 ctypes.c_float, ctypes.c_float, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
+        _ref.ref_init()
+    return _ref
+
+
+def port():
+    global _port
+    if _port is None:
+        if not os.path.exists(PORT_SO):
+            subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "port"])
+        _port = ctypes.CDLL(PORT_SO)
+        _port.port_transcode.restype = ctypes.c_int64
+        _port.port_transcode.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, _u8p]
+    return _port
+
+
+def ref_transcode(blocks, fmt):
+    """blocks: uint8 [n,16]; fmt 0=BC7 1=ASTC -> (out [n,16], first_bad or -1)"""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros_like(blocks)
+    bad = ref().ref_transcode(_p(blocks), blocks.shape[0], fmt, _p(out))
+    return out, bad
+
+
+def port_transcode(blocks, fmt):
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros_like(blocks)
+    bad = port().port_transcode(_p(blocks), blocks.shape[0], fmt, _p(out))
+    return out, bad
+
+
+def ref_extract_blocks(img):
+    """img uint8 [h,w,4] -> [nblocks,64] edge-clamped 4x4 gathers in raster block order"""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape[:2]
+    n = ((w + 3) // 4) * ((h + 3) // 4)
+    out = np.zeros((n, 64), np.uint8)
+    ref().ref_extract_blocks(_p(img), w, h, _p(out))
+    return out
+
+
+def ref_encode_blocks(px, flags, threads=8):
+    px = np.ascontiguousarray(px, dtype=np.uint8).reshape(-1, 64)
+    out = np.zeros((px.shape[0], 16), np.uint8)
+    ref().ref_encode_blocks(_p(px), px.shape[0], flags, _p(out), threads)
+    return out
+
+
+def ref_unpack_rgba(blocks, srgb=False):
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros((blocks.shape[0], 64), np.uint8)
+    bad = ref().ref_unpack_rgba(_p(blocks), blocks.shape[0], _p(out), int(srgb))
+    return out, bad
+
+
+def ref_unpack_bc7(blocks):
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros((blocks.shape[0], 64), np.uint8)
+    ref().ref_unpack_bc7(_p(blocks), blocks.shape[0], _p(out))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Synthetic inputs: deterministic, numpy-vectorised.
+def _lcg_noise(n, seed):
+    """n values of the 32-bit LCG s = s*1664525 + 1013904223; noise = (s>>8)%32 - 16 (vectorised by jump-ahead)."""
+    a, c = np.uint64(1664525), np.uint64(1013904223)
+    # sequential in chunks: compute by doubling (A_k, C_k) s.t. s_{i+k} = A_k s_i + C_k mod 2^32
+    s = np.empty(n, np.uint64)
+    cur = np.uint64(seed & 0xFFFFFFFF)
+    m = np.uint64(0xFFFFFFFF)
+    # generate the first block sequentially then extend by jump-ahead
+    blk = min(n, 1024)
+    for i in range(blk):
+        cur = (cur * a + c) & m
+        s[i] = cur
+    filled = blk
+    A, C = np.uint64(1), np.uint64(0)
+    for _ in range(blk):
+        A, C = (A * a) & m, (C * a + c) & m
+    while filled < n:
+        k = min(filled, n - filled)
+        # jump every element ahead by `filled` steps: need A_filled, C_filled
+        s[filled:filled + k] = (s[:k] * A + C) & m
+        filled += k
+        A, C = (A * A) & m, (C * A + C) & m
+    return ((s >> np.uint64(8)) % np.uint64(32)).astype(np.int32) - 16
+
+
+def img_mix(w, h, seed):
+    n = _lcg_noise(w * h, seed).reshape(h, w)
+    x = np.arange(w, dtype=np.int32)[None, :].repeat(h, 0)
+    y = np.arange(h, dtype=np.int32)[:, None].repeat(w, 1)
+    img = np.empty((h, w, 4), np.uint8)
+    img[..., 0] = np.clip(255 * x // max(w, 1) + n, 0, 255)
+    img[..., 1] = np.clip(255 * y // max(h, 1) + n // 2, 0, 255)
+    img[..., 2] = np.clip(((x ^ y) & 255) + n, 0, 255)
+    img[..., 3] = np.where(x >= w // 2, 255, np.clip((x + y) // 4 + n, 0, 255))
+    # every 16th 64x64 tile solid, every 17th grey (r=g=b)
+    tx, ty = x // 64, y // 64
+    tid = ty * ((w + 63) // 64) + tx
+    solid = (tid % 16) == 15
+    img[solid] = np.stack([(tid[solid] * 37) & 255, (tid[solid] * 59) & 255, (tid[solid] * 83) & 255,
+                           np.where(tid[solid] % 32 == 15, 255, (tid[solid] * 11) & 255)], -1).astype(np.uint8)
+    grey = (tid % 17) == 16
+    img[grey, 1] = img[grey, 0]
+    img[grey, 2] = img[grey, 0]
+    return img
+
+
+def img_noise(w, h, seed):
+    return np.random.default_rng(seed).integers(0, 256, (h, w, 4), dtype=np.uint8)
+
+
+def img_smooth(w, h, seed):
+    x = np.arange(w, dtype=np.int32)[None, :].repeat(h, 0)
+    y = np.arange(h, dtype=np.int32)[:, None].repeat(w, 1)
+    img = np.empty((h, w, 4), np.uint8)
+    img[..., 0] = 255 * x // max(w, 1)
+    img[..., 1] = 255 * y // max(h, 1)
+    img[..., 2] = (x + y + seed) // 8 & 255
+    img[..., 3] = 255
+    return img
+
+
+def adversarial_blocks(seed, n_each=256):
+    """Block families from SURVEY 8(c): solid, 2-colour, grey ramps, LA, binary alpha, single channel, noise."""
+    r = np.random.default_rng(seed)
+    fams = []
+    solid = r.integers(0, 256, (n_each, 1, 4), dtype=np.uint8).repeat(16, 1)
+    fams.append(solid)
+    solid_opaque = solid.copy(); solid_opaque[..., 3] = 255
+    fams.append(solid_opaque)
+    two = r.integers(0, 256, (n_each, 2, 4), dtype=np.uint8)
+    pick = r.integers(0, 2, (n_each, 16))
+    fams.append(np.take_along_axis(two, pick[..., None].repeat(4, -1), 1))
+    t2 = fams[-1].copy(); t2[..., 3] = 255; fams.append(t2)
+    ramp = (np.arange(16)[None, :] * r.integers(1, 17, (n_each, 1)) + r.integers(0, 16, (n_each, 1))).clip(0, 255).astype(np.uint8)
+    g = np.stack([ramp, ramp, ramp, np.full_like(ramp, 255)], -1); fams.append(g)
+    la = np.stack([ramp, ramp, ramp, r.integers(0, 256, (n_each, 16), dtype=np.uint8)], -1); fams.append(la)
+    ba = r.integers(0, 256, (n_each, 16, 4), dtype=np.uint8); ba[..., 3] = r.integers(0, 2, (n_each, 16)) * 255; fams.append(ba)
+    sc = np.zeros((n_each, 16, 4), np.uint8); sc[..., 3] = 255
+    ch = r.integers(0, 3, n_each)
+    sc[np.arange(n_each), :, ch] = r.integers(0, 256, (n_each, 16), dtype=np.uint8); fams.append(sc)
+    fams.append(r.integers(0, 256, (n_each, 16, 4), dtype=np.uint8))
+    op = r.integers(0, 256, (n_each, 16, 4), dtype=np.uint8); op[..., 3] = 255; fams.append(op)
+    # smooth gradients + small noise, opaque and translucent
+    base = r.integers(0, 256, (n_each, 1, 4)).astype(np.int32)
+    dx = r.integers(-12, 13, (n_each, 1, 4)); dy = r.integers(-12, 13, (n_each, 1, 4))
+    xs = (np.arange(16) % 4)[None, :, None]; ys = (np.arange(16) // 4)[None, :, None]
+    sm = (base + dx * xs + dy * ys + r.integers(-2, 3, (n_each, 16, 4))).clip(0, 255).astype(np.uint8)
+    fams.append(sm)
+    smo = sm.copy(); smo[..., 3] = 255; fams.append(smo)
+    return np.concatenate(fams, 0).reshape(-1, 64)
+
+
+HUFF = [(0x1, 4), (0x35, 6), (0x1D, 5), (0x3, 5), (0x13, 5), (0xB, 5), (0x1B, 5), (0x7, 5), (0x17, 5), (0xF, 5), (0x2, 3),
+        (0x0, 2), (0x6, 3), (0x1F, 5), (0xD, 5), (0x5, 7), (0x15, 6), (0x25, 6), (0x9, 4), (0x45, 7)]  # UASTC mode prefix codes
+
+
+def block_modes(blocks):
+    """UASTC mode index of each block (19 = reserved/invalid)."""
+    blocks = np.asarray(blocks, np.uint8).reshape(-1, 16)
+    lut = np.full(128, 255, np.uint8)
+    for m, (code, ln) in enumerate(HUFF):
+        for hi in range(1 << (7 - ln)):
+            lut[code | (hi << ln)] = m
+    return lut[blocks[:, 0] & 127]
+
+
+def random_payload_blocks(seed, n_per_mode=512, include_invalid=True):
+    """Random 128-bit payloads behind every mode prefix (trit/quint bundles may then hold out-of-range digits and
+    pattern fields may be invalid -- exactly the corrupt-input space a transcoder must treat like the reference)."""
+    r = np.random.default_rng(seed)
+    out = []
+    nm = 20 if include_invalid else 19
+    for m in range(nm):
+        code, ln = HUFF[m]
+        b = r.integers(0, 256, (n_per_mode, 16), dtype=np.uint8)
+        lo = b[:, 0].astype(np.uint32) | (b[:, 1].astype(np.uint32) << 8)
+        lo = (lo & ~np.uint32((1 << ln) - 1)) | np.uint32(code)
+        b[:, 0] = lo & 255
+        b[:, 1] = (lo >> 8) & 255
+        out.append(b)
+    return np.concatenate(out)
