@@ -1,0 +1,112 @@
+"""CPU-side checks (no GPU): the oracle(s) against the reference's own fixtures, and the host logic.
+
+ * oracle/_ref  = the UNMODIFIED reference compiled from /root/reference (present in the build container and shipped
+   to the GPU box as a prebuilt .so).  Pinned here against the CTS goldens and the SURVEY known-answer vector.
+ * oracle/port  = host build of the product's algorithm headers; must agree bit-for-bit with the committed goldens.
+"""
+import json, os, ctypes
+import numpy as np
+import pytest
+import refutil as R
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+needs_ref = pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built")
+
+
+def _hex(h):
+    return np.frombuffer(bytes.fromhex(h), np.uint8).reshape(-1, 16)
+
+
+@needs_ref
+def test_ref_matches_cts_transcode_goldens():
+    cts = json.load(open(os.path.join(GOLD, "cts_uastc.json")))["transcode"]
+    assert len(cts) == 8
+    for sub, c in cts.items():
+        u = _hex(c["uastc"])
+        assert (R.ref_transcode(u, 0)[0] == _hex(c["bc7"])).all(), sub
+        assert (R.ref_transcode(u, 1)[0] == _hex(c["astc"])).all(), sub
+
+
+def test_port_matches_cts_transcode_goldens():
+    cts = json.load(open(os.path.join(GOLD, "cts_uastc.json")))["transcode"]
+    for sub, c in cts.items():
+        u = _hex(c["uastc"])
+        assert (R.port_transcode(u, 0)[0] == _hex(c["bc7"])).all(), sub
+        assert (R.port_transcode(u, 1)[0] == _hex(c["astc"])).all(), sub
+
+
+@needs_ref
+def test_ref_known_answer_vector():
+    ka = json.load(open(os.path.join(GOLD, "known_answer.json")))
+    px = np.frombuffer(bytes.fromhex(ka["pixels"]), np.uint8).reshape(1, 64)
+    for lvl, v in ka["levels"].items():
+        u = R.ref_encode_blocks(px, int(lvl), 1)
+        assert u.tobytes().hex() == v["uastc"]
+        assert R.ref_transcode(u, 0)[0].tobytes().hex() == v["bc7"]
+        assert R.ref_transcode(u, 1)[0].tobytes().hex() == v["astc"]
+    # SURVEY 8(c) table, level 0 row, typed in independently of the generator
+    assert ka["levels"]["0"]["uastc"] == "41489b1558025ff82053875a87bafdb9"
+    assert ka["levels"]["2"]["bc7"] == "e007f81ef8ff033c03aa54ff953ea54f"
+    assert ka["levels"]["3"]["astc"] == "42048d17e31fc083ceff5566b89b2102"
+
+
+def test_port_transcode_golden_corpus():
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    assert set(np.unique(R.block_modes(g["uastc"]))) == set(range(19)), "corpus must cover all 19 modes"
+    out, bad = R.port_transcode(g["uastc"], 0)
+    assert bad == -1 and (out == g["bc7"]).all()
+    out, bad = R.port_transcode(g["uastc"], 1)
+    assert bad == -1 and (out == g["astc"]).all()
+
+
+def test_port_rejects_invalid_blocks():
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    inv = g["invalid"]
+    assert len(inv) > 50
+    for fmt in (0, 1):
+        for k in range(len(inv)):
+            assert R.port_transcode(inv[k:k + 1], fmt)[1] == 0
+
+
+@needs_ref
+def test_port_vs_ref_random_payloads():
+    blocks = R.random_payload_blocks(123, 1500, include_invalid=False)
+    for fmt in (0, 1):
+        ok = np.array([R.ref_transcode(blocks[k:k + 1], fmt)[1] < 0 for k in range(len(blocks))])
+        v = blocks[ok]
+        assert (R.port_transcode(v, fmt)[0] == R.ref_transcode(v, fmt)[0]).all()
+        for k in np.nonzero(~ok)[0][:200]:
+            assert R.port_transcode(blocks[k:k + 1], fmt)[1] == 0
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    import re
+    import ktx_software_b200 as K
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "ktx_b200_uastc.h")).read()
+    declared = set(re.findall(r"\b(b200_uastc_\w+)\s*\(", hdr))
+    assert declared == set(K.EXPORTED_SYMBOLS)
+    lib = K.lib()
+    for s in declared:
+        assert hasattr(lib, s), s
+
+
+def test_no_cpu_fallback_without_gpu():
+    """On a box without a GPU the product must fail loudly, not compute on the host."""
+    import torch
+    import ktx_software_b200 as K
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(K.B200Error):
+        K.transcode(np.zeros(16, np.uint8), K.TTF_BC7_RGBA)
+
+
+def test_synthetic_images_are_deterministic():
+    a = R.img_mix(128, 64, 5)
+    b = R.img_mix(128, 64, 5)
+    assert a.shape == (64, 128, 4) and (a == b).all()
+    assert (R.img_mix(128, 64, 6) != a).any()
+    px = R.ref_extract_blocks(a) if R.have_ref() else None
+    if px is not None:
+        assert px.shape == (16 * 32, 64)
+        assert (px[0].reshape(4, 4, 4) == a[:4, :4]).all()
