@@ -1,0 +1,267 @@
+// uastc_encode.cuh -- one 4x4 RGBA block -> one UASTC block.
+// Restates encode_uastc (reference external/basis_universal/encoder/basisu_uastc_enc.cpp:3127-3646): classify,
+// run the enabled modes, score every candidate by UASTC + transcoded-BC7 error, pick, compute hints, pack
+// (pack_uastc :111-466).
+#pragma once
+#include "uastc_modes.cuh"
+#include "uastc_hints.cuh"
+
+namespace ub {
+
+const uint32_t MAX_CANDIDATES = 512;
+
+// Hints carried in the block besides the colour data.
+struct BlockHints {
+  uint32_t bc1_hint0, bc1_hint1;
+  uint32_t etc1_flip, etc1_diff, etc1_inten0, etc1_inten1, etc1_bias;
+  uint32_t etc2_hints;                               // eac table | multiplier << 4
+  uint32_t etc1_selector, etc1_r, etc1_g, etc1_b;    // solid-colour blocks only
+};
+
+#ifdef UB_COMPUTE_HINTS_STUB
+UB_FN void compute_hints(const Candidate& c, const uint32_t* px, const uint32_t* dec, const EncCfg& cfg, BlockHints& h) {
+  (void)px; (void)dec; (void)cfg;
+  // eac multiplier must be >= 1 for alpha modes even in the placeholder
+  h.etc2_hints = (md_comps(UBT(uastc_mode_desc)[c.mode]) != 3) ? (1u << 4) : 0u;
+}
+#endif
+
+// pack_uastc (basisu_uastc_enc.cpp:111-466)
+UB_FN Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHints& h) {
+  const uint32_t mode = c.mode;
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  BitWriter bw;
+  bw.init();
+  bw.put(md_huff_code(d), md_huff_len(d));
+  if (mode == UASTC_MODE_SOLID) {
+    bw.put(solid_rgba, 32);
+    bw.put(h.etc1_diff, 1); bw.put(h.etc1_inten0, 3); bw.put(h.etc1_selector, 2);
+    bw.put(h.etc1_r, 5); bw.put(h.etc1_g, 5); bw.put(h.etc1_b, 5);
+    return bw.b;
+  }
+  if (UBT(uastc_mode_has_bc1_hint0)[mode]) bw.put(h.bc1_hint0, 1);
+  if (UBT(uastc_mode_has_bc1_hint1)[mode]) bw.put(h.bc1_hint1, 1);
+  bw.put(h.etc1_flip, 1); bw.put(h.etc1_diff, 1); bw.put(h.etc1_inten0, 3); bw.put(h.etc1_inten1, 3);
+  if (UBT(uastc_mode_has_etc1_bias)[mode]) bw.put(h.etc1_bias, 5);
+  const uint32_t comps = md_comps(d), subsets = md_subsets(d), planes = 1 + md_dual_plane(d), wb = md_weight_bits(d);
+  if (comps != 3) bw.put(h.etc2_hints, 8);  // every mode with alpha or LA carries the ETC2 EAC hint byte
+  if (subsets == 3) bw.put(c.pattern, 4); else if (subsets == 2) bw.put(c.pattern, 5);
+  if (planes == 2 && mode != 17) bw.put(c.ccs, 2);
+
+  uint8_t w[32], ep[18];
+  for (uint32_t i = 0; i < 32; i++) w[i] = c.w[i];
+  for (uint32_t i = 0; i < 18; i++) ep[i] = c.ep[i];
+  const uint32_t pat = cand_pat(c, d);
+  uint32_t anchors = 0;
+  if (subsets == 3) anchors = UBT(astc_anchor3)[c.pattern];
+  else if (subsets == 2) anchors = (mode == 7) ? UBT(astc_anchor7)[c.pattern] : UBT(astc_anchor2)[c.pattern];
+  const uint32_t wmax = (1u << wb) - 1u;
+
+  // anchor weights must have a clear MSB: flip the subset's (plane's) weights and swap its endpoints otherwise
+  for (uint32_t plane = 0; plane < planes; plane++)
+    for (uint32_t s = 0; s < subsets; s++) {
+      const uint32_t a = (anchors >> (4 * s)) & 15u;
+      if (w[a * planes + plane] & (1u << (wb - 1))) {
+        for (uint32_t i = 0; i < 16; i++)
+          if (((pat >> (2 * i)) & 3u) == s) w[i * planes + plane] = (uint8_t)(wmax - w[i * planes + plane]);
+        if (planes == 2) {
+          for (uint32_t k = 0; k < comps; k++) {
+            const uint32_t cp = (comps == 2) ? k : ((k == c.ccs) ? 1u : 0u);
+            if (cp == plane) { const uint8_t t = ep[2 * k]; ep[2 * k] = ep[2 * k + 1]; ep[2 * k + 1] = t; }
+          }
+        } else {
+          for (uint32_t k = 0; k < comps; k++) {
+            const uint32_t i0 = s * comps * 2 + 2 * k;
+            const uint8_t t = ep[i0]; ep[i0] = ep[i0 + 1]; ep[i0 + 1] = t;
+          }
+        }
+      }
+    }
+
+  // endpoints: trit / quint digits bundled first, then the plain bits
+  const uint32_t total_values = comps * 2 * subsets, er = md_endpoint_range(d);
+  const uint32_t eb = UBT(astc_bise_range)[er * 3], trits = UBT(astc_bise_range)[er * 3 + 1], quints = UBT(astc_bise_range)[er * 3 + 2];
+  if (trits | quints) {
+    const uint32_t base = trits ? 3u : 5u, full = trits ? 243u : 125u;
+    uint32_t acc = 0, mul = 1;
+    for (uint32_t i = 0; i < total_values; i++) {
+      acc += (ep[i] >> eb) * mul;
+      mul *= base;
+      if (mul == full) { bw.put(acc, trits ? 8 : 7); acc = 0; mul = 1; }
+    }
+    if (mul > 1) {
+      uint32_t nb;
+      if (trits) nb = (mul == 3) ? 2 : (mul == 9) ? 4 : (mul == 27) ? 5 : 7;
+      else nb = (mul == 5) ? 3 : 5;
+      bw.put(acc, nb);
+    }
+  }
+  for (uint32_t i = 0; i < total_values; i++) bw.put(ep[i] & ((1u << eb) - 1u), eb);
+
+  for (uint32_t i = 0; i < 16 * planes; i++) {
+    uint32_t nb = wb;
+    const uint32_t texel = i / planes;
+    for (uint32_t s = 0; s < subsets; s++)
+      if (((anchors >> (4 * s)) & 15u) == texel) { nb--; break; }
+    bw.put(w[i] & ((1u << nb) - 1u), nb);
+  }
+  return bw.b;
+}
+
+UB_FN void block_error(const uint32_t* a, const uint32_t* b, uint64_t& rgb, uint64_t& rgba, uint64_t& la) {
+  uint64_t er = 0, eg = 0, eb = 0, ea = 0;
+  for (uint32_t i = 0; i < 16; i++) {
+    const int dr = (int)ch(a[i], 0) - (int)ch(b[i], 0), dg = (int)ch(a[i], 1) - (int)ch(b[i], 1);
+    const int db = (int)ch(a[i], 2) - (int)ch(b[i], 2), da = (int)ch(a[i], 3) - (int)ch(b[i], 3);
+    er += (uint32_t)(dr * dr); eg += (uint32_t)(dg * dg); eb += (uint32_t)(db * db); ea += (uint32_t)(da * da);
+  }
+  la = er + ea; rgb = er + eg + eb; rgba = rgb + ea;
+}
+
+// candidate -> the transcoder's view of it (weights at full width; BC7 packing normalises its own anchors)
+UB_FN void candidate_to_unpacked(const Candidate& c, UnpackedUastc& u) {
+  u.mode = c.mode; u.desc = UBT(uastc_mode_desc)[c.mode]; u.pattern = c.pattern; u.ccs = c.ccs;
+  u.pat = cand_pat(c, u.desc); u.anchors = 0; u.solid = 0; u.hints = 0;
+  for (uint32_t i = 0; i < 18; i++) u.ep[i] = c.ep[i];
+  const uint32_t wb = md_weight_bits(u.desc), n = 16 * (1 + md_dual_plane(u.desc));
+  u.w.lo = 0; u.w.hi = 0;
+  for (uint32_t i = 0; i < n; i++) bits_or(u.w, i * wb, c.w[i]);
+}
+
+UB_FN float u64_to_float(uint64_t v) {
+#ifdef __CUDA_ARCH__
+  return __ull2float_rn(v);
+#else
+  return (float)v;
+#endif
+}
+
+// Candidate generation in the reference's order (basisu_uastc_enc.cpp:3290-3351).  Returns the count.
+UB_FN uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands) {
+  uint32_t n = 0;
+  const uint32_t mm = cfg.mode_mask;
+  const bool est = cfg.estimate_partition;
+  uint32_t parts[8];
+  if (is_la) {
+    uint32_t la_px[16];
+    for (uint32_t i = 0; i < 16; i++) la_px[i] = ch(px[i], 0) | (px[i] & 0xFF000000u);
+    if (mm & (1u << 15)) mode_single_plane(15, 0, 0, la_px, cfg, cands[n++]);
+    if (mm & (1u << 16)) {
+      if (est) { estimate_partitions(2, 4, 4, la_px, parts, 4); for (uint32_t k = 0; k < 4; k++) mode_single_plane(16, 2, parts[k], la_px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(16, 2, cp, la_px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 17)) mode_dual_plane(17, 0, px, cfg, cands[n++]);
+  }
+  if (!has_alpha) {
+    if (mm & (1u << 0)) mode_single_plane(0, 0, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 1)) mode_single_plane(1, 0, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 2)) {
+      if (est) { estimate_partitions(2, 8, 3, px, parts, 1); mode_single_plane(2, 2, parts[0], px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(2, 2, cp, px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 3)) {
+      if (est) { estimate_partitions(3, 4, 3, px, parts, 1); mode_single_plane(3, 3, parts[0], px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 11; cp++) mode_single_plane(3, 3, cp, px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 4)) {
+      if (est) { estimate_partitions(2, 4, 3, px, parts, 1); mode_single_plane(4, 2, parts[0], px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(4, 2, cp, px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 5)) mode_single_plane(5, 0, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 6)) for (uint32_t rot = 0; rot < 3; rot++) mode_dual_plane(6, rot, px, cfg, cands[n++]);
+    if (mm & (1u << 7)) {
+      if (est) { estimate_partitions(7, 4, 3, px, parts, 1); mode_single_plane(7, 7, parts[0], px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 19; cp++) mode_single_plane(7, 7, cp, px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 18)) mode_single_plane(18, 0, 0, px, cfg, cands[n++]);
+  }
+  if (has_alpha || cfg.always_try_alpha) {
+    if (mm & (1u << 9)) {
+      if (est) { estimate_partitions(2, 4, 4, px, parts, 4); for (uint32_t k = 0; k < 4; k++) mode_single_plane(9, 2, parts[k], px, cfg, cands[n++]); }
+      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[n++]);
+    }
+    if (mm & (1u << 10)) mode_single_plane(10, 0, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 11)) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(11, rot, px, cfg, cands[n++]);
+    if (mm & (1u << 12)) mode_single_plane(12, 0, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 13)) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(13, rot, px, cfg, cands[n++]);
+    if (mm & (1u << 14)) mode_single_plane(14, 0, 0, px, cfg, cands[n++]);
+  }
+  return n;
+}
+
+// Candidate scoring + selection (basisu_uastc_enc.cpp:3389-3549).  Returns the winning index.
+UB_FN uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uint32_t n, bool has_alpha, bool is_la, uint32_t flags,
+                                uint64_t* overall, float* uerr_f) {
+  if (n == 1) return 0;
+  const bool favor_uastc = (flags & 8u) != 0;
+  const bool favor_bc7 = !favor_uastc && ((flags & 16u) != 0);
+  const uint32_t bc7_w = favor_bc7 ? 100u : (favor_uastc ? 0u : 50u);
+  const uint32_t uastc_w = favor_bc7 ? 0u : 100u;
+  double best_uerr = (double)1e+20f;
+  for (uint32_t i = 0; i < n; i++) {
+    uint32_t dec[16], dec7[16];
+    decode_uastc_pixels(cands[i], dec);
+    uint64_t u_rgb, u_rgba, u_la, b_rgb, b_rgba, b_la;
+    block_error(px, dec, u_rgb, u_rgba, u_la);
+    UnpackedUastc u;
+    candidate_to_unpacked(cands[i], u);
+    Bc7Build bb;
+    uastc_to_bc7_build(u, bb);
+    const Bits128 bc7 = bc7_pack(bb);
+    decode_bc7_pixels(bc7, dec7);
+    block_error(px, dec7, b_rgb, b_rgba, b_la);
+    const uint64_t ue = is_la ? u_la : (has_alpha ? u_rgba : u_rgb);
+    const uint64_t be = is_la ? b_la : (has_alpha ? b_rgba : b_rgb);
+    overall[i] = (be * bc7_w) / 100 + (ue * uastc_w) / 100;
+    if (!overall[i]) return i;
+    uerr_f[i] = f_sqrt(u64_to_float(ue));
+    if ((double)uerr_f[i] < best_uerr) best_uerr = (double)uerr_f[i];
+  }
+  const bool favor_simpler = (flags & 32u) != 0;  // cPackUASTCFavorSimplerModes
+  uint64_t best_err = ~0ull;
+  uint32_t best = 0;
+  bool found = false;
+  const bool all = (best_uerr == 0.0) || favor_bc7;
+  for (uint32_t i = 0; i < n; i++) {
+    if (!all) {
+      const double delta = d_div((double)uerr_f[i], best_uerr);
+      if (!(delta <= (double)1.3f)) continue;
+    }
+    const float wgt = (favor_simpler && (cands[i].mode == 0 || cands[i].mode == 10)) ? .8f : 1.0f;
+    const uint64_t w = (uint64_t)f_mul(u64_to_float(overall[i]), wgt);
+    if (w < best_err) { best_err = w; best = i; found = true; if (!best_err) break; }
+  }
+  (void)found;
+  return best;
+}
+
+// encode_uastc.  px: 16 texels r | g<<8 | b<<16 | a<<24, raster order.
+UB_FN Bits128 encode_uastc_block(const uint32_t* px, uint32_t flags, Candidate* cands, uint64_t* overall, float* uerr_f) {
+  bool solid = true, has_alpha = false, is_la = true;
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t v = px[i];
+    if ((v >> 24) < 255) has_alpha = true;
+    if (v != px[0]) solid = false;
+    if (ch(v, 0) != ch(v, 1) || ch(v, 0) != ch(v, 2)) is_la = false;
+  }
+  BlockHints h;
+  memset(&h, 0, sizeof(h));
+  if (solid) {
+    Candidate c;
+    memset(&c, 0, sizeof(c));
+    c.mode = UASTC_MODE_SOLID;
+    hints_solid_etc1(px[0], h.etc1_diff, h.etc1_inten0, h.etc1_selector, h.etc1_r, h.etc1_g, h.etc1_b);
+    return pack_uastc(c, px[0], h);
+  }
+  const EncCfg cfg = enc_cfg_from_flags(flags);
+  if (cfg.only_la_on_transparent && is_la && !has_alpha) is_la = false;
+  const uint32_t n = generate_candidates(px, has_alpha, is_la, cfg, cands);
+  const uint32_t best = select_candidate(px, cands, n, has_alpha, is_la, flags, overall, uerr_f);
+  const Candidate& bc = cands[best];
+  uint32_t dec[16];
+  decode_uastc_pixels(bc, dec);
+  compute_hints(bc, px, dec, cfg, h);
+  return pack_uastc(bc, 0, h);
+}
+
+}  // namespace ub

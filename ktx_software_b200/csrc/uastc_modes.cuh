@@ -1,0 +1,214 @@
+// uastc_modes.cuh -- per-mode candidate generation and partition estimation for the UASTC encoder.
+// Restates astc_mode0_or_18 ... astc_mode15 (reference external/basis_universal/encoder/basisu_uastc_enc.cpp:471-2509),
+// estimate_partition2 / _list (:639, :1543), the inline 3-subset and mode-7 estimators (:829-858, :1363-1405) and
+// color_cell_compression_est_astc (encoder/basisu_bc7enc.cpp:1764-1984).
+//
+// The 14 reference functions collapse into two shapes: "N subsets, one plane" and "one subset, two planes"; each
+// is a list of colour-cell jobs (texel subset, weight count, endpoint range, alpha) fed to color_cell_compression.
+#pragma once
+#include "uastc_ccc.cuh"
+#include "uastc_decode.cuh"
+
+namespace ub {
+
+struct EncCfg {
+  uint32_t level, flags, mode_mask, uber_level, ls_passes;
+  bool estimate_partition, always_try_alpha, bc1_hints, only_la_on_transparent;
+  uint32_t eac_mul_rad, eac_table_mask;
+};
+
+// level -> search effort (basisu_uastc_enc.cpp:3188-3256)
+UB_FN EncCfg enc_cfg_from_flags(uint32_t flags) {
+  EncCfg c;
+  int level = (int)(flags & 7u);
+  if (level > 4) level = 4;
+  c.level = (uint32_t)level; c.flags = flags;
+  c.mode_mask = 0xFFFFFFFFu; c.uber_level = 6; c.estimate_partition = false; c.always_try_alpha = true;
+  c.eac_mul_rad = 3; c.eac_table_mask = 0xFFFFFFFFu; c.ls_passes = 2; c.bc1_hints = true; c.only_la_on_transparent = false;
+  const uint32_t fast_tables = (1u << 2) | (1u << 8) | (1u << 11) | (1u << 13);
+  switch (level) {
+    case 0:
+      c.mode_mask = (1u << 0) | (1u << 8) | (1u << 11) | (1u << 12) | (1u << 15);
+      c.always_try_alpha = false; c.eac_mul_rad = 0; c.eac_table_mask = fast_tables; c.uber_level = 0; c.ls_passes = 1;
+      c.bc1_hints = false; c.estimate_partition = true; c.only_la_on_transparent = true;
+      break;
+    case 1:
+      c.mode_mask = (1u << 0) | (1u << 4) | (1u << 6) | (1u << 8) | (1u << 9) | (1u << 11) | (1u << 12) | (1u << 15) | (1u << 17);
+      c.always_try_alpha = false; c.eac_mul_rad = 0; c.eac_table_mask = fast_tables; c.uber_level = 0; c.ls_passes = 1;
+      c.estimate_partition = true;
+      break;
+    case 2:
+      c.mode_mask = (1u << 0) | (1u << 1) | (1u << 4) | (1u << 5) | (1u << 6) | (1u << 8) | (1u << 9) | (1u << 10) | (1u << 11) |
+                    (1u << 12) | (1u << 13) | (1u << 15) | (1u << 16) | (1u << 17);
+      c.always_try_alpha = false; c.eac_mul_rad = 1;
+      c.eac_table_mask = (1u << 0) | (1u << 2) | (1u << 6) | (1u << 7) | (1u << 8) | (1u << 10) | (1u << 11) | (1u << 13);
+      c.uber_level = 1; c.ls_passes = 1; c.estimate_partition = true;
+      break;
+    case 3:
+      c.always_try_alpha = false; c.eac_mul_rad = 2; c.uber_level = 3; c.estimate_partition = true;
+      break;
+    default: break;
+  }
+  return c;
+}
+
+// ---- fast partition error estimate of one subset (color_cell_compression_est_astc, channel weights all 1)
+UB_FN uint64_t est_astc(uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t n) {
+  uint32_t lo[4] = {255, 255, 255, 255}, hi[4] = {0, 0, 0, 0};
+  for (uint32_t i = 0; i < n; i++)
+    for (uint32_t c = 0; c < ncomps; c++) { const uint32_t v = ch(px[i], c); if (v < lo[c]) lo[c] = v; if (v > hi[c]) hi[c] = v; }
+  if (ncomps == 3) { lo[3] = 255; hi[3] = 255; }
+  uint32_t wc[32];
+  int dots[32];
+  const int ar = (int)hi[0] - (int)lo[0], ag = (int)hi[1] - (int)lo[1], ab = (int)hi[2] - (int)lo[2], aa = (int)hi[3] - (int)lo[3];
+  for (uint32_t i = 0; i < nw; i++) {
+    uint32_t v;
+    if (i == 0) v = pk(lo[0], lo[1], lo[2], lo[3]);
+    else if (i == nw - 1) v = pk(hi[0], hi[1], hi[2], hi[3]);
+    else {
+      const uint32_t w = sel_weight(nw, i);
+      v = pk(interp_linear(lo[0], hi[0], w), interp_linear(lo[1], hi[1], w), interp_linear(lo[2], hi[2], w),
+             ncomps == 4 ? interp_linear(lo[3], hi[3], w) : 255u);
+    }
+    wc[i] = v;
+    dots[i] = (int)ch(v, 0) * ar + (int)ch(v, 1) * ag + (int)ch(v, 2) * ab + (ncomps == 4 ? (int)ch(v, 3) * aa : 0);
+  }
+  uint64_t total = 0;
+  for (uint32_t i = 0; i < n; i++) {
+    const uint32_t c = px[i];
+    const int d = ar * (int)ch(c, 0) + ag * (int)ch(c, 1) + ab * (int)ch(c, 2) + (ncomps == 4 ? aa * (int)ch(c, 3) : 0);
+    uint32_t s = 0;
+    for (int j = (int)nw - 2; j >= 0; j--)
+      if (d >= ((dots[j] + dots[j + 1] + 1) >> 1)) { s = (uint32_t)j + 1; break; }
+    total += (ncomps == 4) ? dist_rgba(wc[s], c) : dist_rgb(wc[s], c);
+  }
+  return total;
+}
+
+// total estimate of one pattern: `pat` = subset per texel (2 bits each)
+UB_FN uint64_t est_pattern(uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t pat, uint32_t subsets) {
+  uint64_t total = 0;
+  for (uint32_t s = 0; s < subsets; s++) {
+    uint32_t sub[16], n = 0;
+    for (uint32_t i = 0; i < 16; i++) if (((pat >> (2 * i)) & 3u) == s) sub[n++] = px[i];
+    total += est_astc(nw, ncomps, sub, n);
+  }
+  return total;
+}
+
+// kind: 2 = the 30 two-subset patterns, 3 = the 11 three-subset patterns, 7 = the 19 mode-7 patterns
+UB_FN uint32_t pattern_of(int kind, uint32_t idx) {
+  if (kind == 3) return UBT(astc_pat3)[idx];
+  return spread_mask2(kind == 7 ? UBT(astc_pat7)[idx] : UBT(astc_pat2)[idx]);
+}
+UB_FN uint32_t pattern_count(int kind) { return kind == 3 ? 11u : (kind == 7 ? 19u : 30u); }
+
+// Best `max_parts` patterns, ascending error, first-wins on ties (estimate_partition2 == list of one).
+UB_FN void estimate_partitions(int kind, uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t* parts, uint32_t max_parts) {
+  uint64_t errs[8];
+  for (uint32_t i = 0; i < max_parts; i++) { errs[i] = ~0ull; parts[i] = 0; }
+  const uint32_t total = pattern_count(kind), subsets = (kind == 3) ? 3u : 2u;
+  for (uint32_t cp = 0; cp < total; cp++) {
+    const uint64_t e = est_pattern(nw, ncomps, px, pattern_of(kind, cp), subsets);
+    for (uint32_t i = 0; i < max_parts; i++)
+      if (e < errs[i]) {
+        for (uint32_t j = max_parts - 1; j > i; --j) { parts[j] = parts[j - 1]; errs[j] = errs[j - 1]; }
+        parts[i] = cp; errs[i] = e;
+        break;
+      }
+  }
+}
+
+UB_FN uint32_t sum_unq_rgb(uint32_t range, const uint8_t* ep, uint32_t which) {
+  return astc_unquant(range, ep[0 + which]) + astc_unquant(range, ep[2 + which]) + astc_unquant(range, ep[4 + which]);
+}
+
+// "N subsets, one plane": modes 0,1,2,3,4,5,7,9,10,12,14,15,16,18.
+//   px     the 16 texels the cells see (already (l,0,0,a) for LA modes)
+//   kind   partition family (0 = single subset)
+UB_FN void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const uint32_t* px, const EncCfg& cfg, Candidate& c,
+                             const uint8_t* force_sel = nullptr) {
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t subsets = md_subsets(d), comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
+  const uint32_t pat = kind ? pattern_of(kind, pattern) : 0u;
+  c.mode = mode; c.pattern = pattern; c.ccs = 0;
+  for (uint32_t i = 0; i < 18; i++) c.ep[i] = 0;
+  for (uint32_t i = 0; i < 32; i++) c.w[i] = 0;
+  CccParams p;
+  p.nw = nw; p.range = range; p.has_alpha = (comps != 3); p.force_sel = force_sel;
+  p.uber_level = cfg.uber_level; p.ls_passes = cfg.ls_passes;
+  for (uint32_t s = 0; s < subsets; s++) {
+    uint32_t sub[16], idx[16], n = 0;
+    for (uint32_t i = 0; i < 16; i++) if (((pat >> (2 * i)) & 3u) == s) { sub[n] = px[i]; idx[n] = i; n++; }
+    p.n = n;
+    CccResults r;
+    color_cell_compression(p, sub, r);
+    uint8_t* ep = c.ep + s * comps * 2;
+    if (comps == 2) {
+      ep[0] = (uint8_t)ch(r.astc_lo, 0); ep[1] = (uint8_t)ch(r.astc_hi, 0);
+      ep[2] = (uint8_t)ch(r.astc_lo, 3); ep[3] = (uint8_t)ch(r.astc_hi, 3);
+    } else {
+      for (uint32_t k = 0; k < comps; k++) { ep[2 * k] = (uint8_t)ch(r.astc_lo, k); ep[2 * k + 1] = (uint8_t)ch(r.astc_hi, k); }
+    }
+    bool invert = false;
+    if (comps >= 3 && !force_sel) {
+      if (sum_unq_rgb(range, ep, 1) < sum_unq_rgb(range, ep, 0)) {
+        for (uint32_t k = 0; k < comps; k++) { const uint8_t t = ep[2 * k]; ep[2 * k] = ep[2 * k + 1]; ep[2 * k + 1] = t; }
+        invert = true;
+      }
+    }
+    for (uint32_t j = 0; j < n; j++) c.w[idx[j]] = (uint8_t)(invert ? (nw - 1 - r.sel[j]) : r.sel[j]);
+  }
+}
+
+// "one subset, two planes": modes 6 (rot 0..2), 11 and 13 (rot 0..3), 17 (L plane + A plane).
+UB_FN void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, const EncCfg& cfg, Candidate& c) {
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
+  uint32_t p0[16], p1[16];
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t v = px[i];
+    if (mode == 17) {
+      p1[i] = ch(v, 3) * 0x010101u | 0xFF000000u;
+      p0[i] = ch(v, 0) * 0x010101u | 0xFF000000u;
+    } else {
+      p1[i] = ch(v, rot) * 0x010101u | 0xFF000000u;
+      uint32_t t = v;
+      if (mode == 6) t = (t & ~(255u << (8 * rot))) | (255u << (8 * rot));
+      else { if (rot < 3) t = (t & ~(255u << (8 * rot))) | (ch(v, 3) << (8 * rot)); t |= 0xFF000000u; }
+      p0[i] = t;
+    }
+  }
+  CccParams p;
+  p.n = 16; p.nw = nw; p.range = range; p.has_alpha = false; p.force_sel = nullptr;
+  p.uber_level = cfg.uber_level; p.ls_passes = cfg.ls_passes;
+  CccResults r0, r1;
+  color_cell_compression(p, p0, r0);
+  color_cell_compression(p, p1, r1);
+  c.mode = mode; c.pattern = 0; c.ccs = (mode == 17) ? 3u : rot;
+  for (uint32_t i = 0; i < 18; i++) c.ep[i] = 0;
+  bool invert = false;
+  if (mode == 17) {
+    c.ep[0] = (uint8_t)ch(r0.astc_lo, 0); c.ep[1] = (uint8_t)ch(r0.astc_hi, 0);
+    c.ep[2] = (uint8_t)ch(r1.astc_lo, 0); c.ep[3] = (uint8_t)ch(r1.astc_hi, 0);
+  } else {
+    for (uint32_t k = 0; k < 3; k++) {
+      const CccResults& rr = (rot == k) ? r1 : r0;
+      c.ep[2 * k] = (uint8_t)ch(rr.astc_lo, k); c.ep[2 * k + 1] = (uint8_t)ch(rr.astc_hi, k);
+    }
+    if (comps == 4) {
+      if (rot == 3) { c.ep[6] = (uint8_t)ch(r1.astc_lo, 0); c.ep[7] = (uint8_t)ch(r1.astc_hi, 0); }
+      else { c.ep[6] = (uint8_t)ch(r0.astc_lo, rot); c.ep[7] = (uint8_t)ch(r0.astc_hi, rot); }
+    }
+    if (sum_unq_rgb(range, c.ep, 1) < sum_unq_rgb(range, c.ep, 0)) {
+      for (uint32_t k = 0; k < comps; k++) { const uint8_t t = c.ep[2 * k]; c.ep[2 * k] = c.ep[2 * k + 1]; c.ep[2 * k + 1] = t; }
+      invert = true;
+    }
+  }
+  for (uint32_t i = 0; i < 16; i++) {
+    c.w[2 * i] = (uint8_t)(invert ? (nw - 1 - r0.sel[i]) : r0.sel[i]);
+    c.w[2 * i + 1] = (uint8_t)(invert ? (nw - 1 - r1.sel[i]) : r1.sel[i]);
+  }
+}
+
+}  // namespace ub

@@ -221,3 +221,29 @@ def random_payload_blocks(seed, n_per_mode=512, include_invalid=True):
         b[:, 1] = (lo >> 8) & 255
         out.append(b)
     return np.concatenate(out)
+
+
+HINT_BITS = [15, 15, 15, 15, 15, 15, 15, 15, 0, 23, 17, 17, 17, 23, 23, 23, 23, 23, 15]
+
+
+def hint_mask(blocks):
+    """uint8 [n,16] mask with 1-bits where a block stores transcoding hints (mode-dependent position)."""
+    blocks = np.asarray(blocks, np.uint8).reshape(-1, 16)
+    modes = block_modes(blocks)
+    masks = np.zeros((20, 16), np.uint8)
+    for m in range(19):
+        ln = HUFF[m][1]
+        lo, hi = (ln + 32, ln + 32 + 21) if m == 8 else (ln, ln + HINT_BITS[m])
+        v = ((1 << hi) - 1) ^ ((1 << lo) - 1)
+        masks[m] = np.frombuffer(v.to_bytes(16, "little"), np.uint8)
+    return masks[np.minimum(modes, 19)]
+
+
+def port_encode_blocks(px, flags):
+    px = np.ascontiguousarray(px, dtype=np.uint8).reshape(-1, 64)
+    out = np.zeros((px.shape[0], 16), np.uint8)
+    f = port().port_encode_blocks
+    f.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, _u8p]
+    f.restype = None
+    f(_p(px), px.shape[0], flags, _p(out))
+    return out
