@@ -18,15 +18,40 @@ struct BlockHints {
   uint32_t etc1_selector, etc1_r, etc1_g, etc1_b;    // solid-colour blocks only
 };
 
-#ifdef UB_COMPUTE_HINTS_STUB
-UB_FN void compute_hints(const Candidate& c, const uint32_t* px, const uint32_t* dec, const EncCfg& cfg, BlockHints& h) {
-  (void)px; (void)dec; (void)cfg;
-  // eac multiplier must be >= 1 for alpha modes even in the placeholder
-  h.etc2_hints = (md_comps(UBT(uastc_mode_desc)[c.mode]) != 3) ? (1u << 4) : 0u;
+// Anchor normalisation (first half of pack_uastc, basisu_uastc_enc.cpp:262-338): every subset's (plane's) anchor
+// weight must have a clear MSB; otherwise flip that subset's weights and swap its endpoints.
+UB_FN void normalize_candidate(const Candidate& c, Candidate& o) {
+  o = c;
+  if (c.mode == UASTC_MODE_SOLID) return;
+  const uint32_t d = UBT(uastc_mode_desc)[c.mode];
+  const uint32_t comps = md_comps(d), subsets = md_subsets(d), planes = 1 + md_dual_plane(d), wb = md_weight_bits(d);
+  const uint32_t pat = cand_pat(c, d);
+  uint32_t anchors = 0;
+  if (subsets == 3) anchors = UBT(astc_anchor3)[c.pattern];
+  else if (subsets == 2) anchors = (c.mode == 7) ? UBT(astc_anchor7)[c.pattern] : UBT(astc_anchor2)[c.pattern];
+  const uint32_t wmax = (1u << wb) - 1u;
+  for (uint32_t plane = 0; plane < planes; plane++)
+    for (uint32_t s = 0; s < subsets; s++) {
+      const uint32_t a = (anchors >> (4 * s)) & 15u;
+      if (o.w[a * planes + plane] & (1u << (wb - 1))) {
+        for (uint32_t i = 0; i < 16; i++)
+          if (((pat >> (2 * i)) & 3u) == s) o.w[i * planes + plane] = (uint8_t)(wmax - o.w[i * planes + plane]);
+        if (planes == 2) {
+          for (uint32_t k = 0; k < comps; k++) {
+            const uint32_t cp = (comps == 2) ? k : ((k == c.ccs) ? 1u : 0u);
+            if (cp == plane) { const uint8_t t = o.ep[2 * k]; o.ep[2 * k] = o.ep[2 * k + 1]; o.ep[2 * k + 1] = t; }
+          }
+        } else {
+          for (uint32_t k = 0; k < comps; k++) {
+            const uint32_t i0 = s * comps * 2 + 2 * k;
+            const uint8_t t = o.ep[i0]; o.ep[i0] = o.ep[i0 + 1]; o.ep[i0 + 1] = t;
+          }
+        }
+      }
+    }
 }
-#endif
 
-// pack_uastc (basisu_uastc_enc.cpp:111-466)
+// Bit emission (second half of pack_uastc, :111-260 and :340-466).  `c` must already be normalised.
 UB_FN Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHints& h) {
   const uint32_t mode = c.mode;
   const uint32_t d = UBT(uastc_mode_desc)[mode];
@@ -47,36 +72,11 @@ UB_FN Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHin
   if (comps != 3) bw.put(h.etc2_hints, 8);  // every mode with alpha or LA carries the ETC2 EAC hint byte
   if (subsets == 3) bw.put(c.pattern, 4); else if (subsets == 2) bw.put(c.pattern, 5);
   if (planes == 2 && mode != 17) bw.put(c.ccs, 2);
-
-  uint8_t w[32], ep[18];
-  for (uint32_t i = 0; i < 32; i++) w[i] = c.w[i];
-  for (uint32_t i = 0; i < 18; i++) ep[i] = c.ep[i];
-  const uint32_t pat = cand_pat(c, d);
+  const uint8_t* w = c.w;
+  const uint8_t* ep = c.ep;
   uint32_t anchors = 0;
   if (subsets == 3) anchors = UBT(astc_anchor3)[c.pattern];
   else if (subsets == 2) anchors = (mode == 7) ? UBT(astc_anchor7)[c.pattern] : UBT(astc_anchor2)[c.pattern];
-  const uint32_t wmax = (1u << wb) - 1u;
-
-  // anchor weights must have a clear MSB: flip the subset's (plane's) weights and swap its endpoints otherwise
-  for (uint32_t plane = 0; plane < planes; plane++)
-    for (uint32_t s = 0; s < subsets; s++) {
-      const uint32_t a = (anchors >> (4 * s)) & 15u;
-      if (w[a * planes + plane] & (1u << (wb - 1))) {
-        for (uint32_t i = 0; i < 16; i++)
-          if (((pat >> (2 * i)) & 3u) == s) w[i * planes + plane] = (uint8_t)(wmax - w[i * planes + plane]);
-        if (planes == 2) {
-          for (uint32_t k = 0; k < comps; k++) {
-            const uint32_t cp = (comps == 2) ? k : ((k == c.ccs) ? 1u : 0u);
-            if (cp == plane) { const uint8_t t = ep[2 * k]; ep[2 * k] = ep[2 * k + 1]; ep[2 * k + 1] = t; }
-          }
-        } else {
-          for (uint32_t k = 0; k < comps; k++) {
-            const uint32_t i0 = s * comps * 2 + 2 * k;
-            const uint8_t t = ep[i0]; ep[i0] = ep[i0 + 1]; ep[i0 + 1] = t;
-          }
-        }
-      }
-    }
 
   // endpoints: trit / quint digits bundled first, then the plain bits
   const uint32_t total_values = comps * 2 * subsets, er = md_endpoint_range(d);
@@ -106,6 +106,14 @@ UB_FN Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHin
     bw.put(w[i] & ((1u << nb) - 1u), nb);
   }
   return bw.b;
+}
+
+// All hints of a non-solid block (basisu_uastc_enc.cpp:3607-3637).  nc = normalised winning candidate.
+UB_FN void compute_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, const EncCfg& cfg, BlockHints& h) {
+  if (cfg.bc1_hints) compute_bc1_hints(nc, px, dec, h.bc1_hint0, h.bc1_hint1);
+  const uint32_t d = UBT(uastc_mode_desc)[nc.mode];
+  h.etc2_hints = (md_comps(d) != 3) ? compute_eac_hint(dec, cfg.eac_mul_rad, cfg.eac_table_mask) : 0u;
+  compute_etc1_hints(nc.mode, px, dec, cfg.level, cfg.flags, h.etc1_flip, h.etc1_diff, h.etc1_inten0, h.etc1_inten1, h.etc1_bias);
 }
 
 UB_FN void block_error(const uint32_t* a, const uint32_t* b, uint64_t& rgb, uint64_t& rgba, uint64_t& la) {
@@ -260,8 +268,10 @@ UB_FN Bits128 encode_uastc_block(const uint32_t* px, uint32_t flags, Candidate* 
   const Candidate& bc = cands[best];
   uint32_t dec[16];
   decode_uastc_pixels(bc, dec);
-  compute_hints(bc, px, dec, cfg, h);
-  return pack_uastc(bc, 0, h);
+  Candidate nc;
+  normalize_candidate(bc, nc);
+  compute_hints(nc, px, dec, cfg, h);
+  return pack_uastc(nc, 0, h);
 }
 
 }  // namespace ub

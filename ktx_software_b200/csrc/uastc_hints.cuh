@@ -1,20 +1,493 @@
-// uastc_hints.cuh -- transcoding hints stored in a UASTC block (BC1 hints, ETC1 flip/diff/intensity/bias, ETC2 EAC
-// table+multiplier).  Restates compute_bc1_hints, compute_etc1_hints, uastc_pack_eac_a8 and the solid-colour ETC1
-// packer: reference external/basis_universal/encoder/basisu_uastc_enc.cpp:2536-3105, encoder/basisu_etc.cpp:181.
+// uastc_hints.cuh -- transcoding hints stored in a UASTC block: BC1 hints, ETC1 flip/diff/intensity/bias, ETC2 EAC
+// table+multiplier, and the solid-colour ETC1 encoding.  Restates, from the reference
+// external/basis_universal/encoder/basisu_uastc_enc.cpp: compute_etc1_hints :2715-3011 (+ pack_etc1_estimate_flipped :2669,
+// rgb_to_y_cb_cr / color_diff / gray_distance2 :2638-2667), uastc_pack_eac_a8 :3020-3105, compute_bc1_hints :2536-2629;
+// from encoder/basisu_etc.cpp: pack_etc1_block_solid_color :181-262; from transcoder/basisu_transcoder.cpp:
+// apply_etc1_bias :16182, encode_bc1 :17682-17860 (+ bc1_find_sels :17492, LS :17557, solid :17634),
+// transcode_uastc_to_bc1_hint0/1 :18237/:18335; and unpack_bc1 (encoder/basisu_gpu_texture.cpp:94).
 #pragma once
 #include "uastc_modes.cuh"
 
 namespace ub {
 
-struct BlockHints;
-struct EncCfg;
-
-#ifndef UB_HINTS_IMPLEMENTED
-// Stage-A placeholders: colour data is complete, hint fields are zero (tests mask the hint bits until stage B lands).
+// ---------------------------------------------------------------------------------------------------------
+// solid colour -> ETC1 (diff, inten, selector, r, g, b)
 UB_FN void hints_solid_etc1(uint32_t rgba, uint32_t& diff, uint32_t& inten, uint32_t& sel, uint32_t& r, uint32_t& g, uint32_t& b) {
-  (void)rgba; diff = 0; inten = 0; sel = 0; r = 0; g = 0; b = 0;
+  const uint32_t next_comp[4] = {1, 2, 0, 1};
+  uint32_t col[3] = {ch(rgba, 0), ch(rgba, 1), ch(rgba, 2)};
+  uint32_t best_error = 0xFFFFFFFFu, best_i = 0, best_x = 0, best_c1 = 0, best_c2 = 0;
+  bool done = false;
+  for (uint32_t i = 0; i < 3 && !done; i++) {
+    const uint32_t c1 = col[next_comp[i]], c2 = col[next_comp[i + 1]];
+    for (int delta = -1; delta <= 1 && !done; delta++) {
+      const int cpd = clampi((int)col[i] + delta, 0, 255);
+      const uint16_t* p = UBT(etc1_solid_cfg) + UBT(etc1_solid_cfg_ofs)[cpd];
+      do {
+        const uint32_t x = *p++;
+        const uint16_t* inv = UBT(etc1_inverse) + (x & 0xFFu) * 256;
+        const uint32_t p1 = inv[c1], p2 = inv[c2];
+        const int d0 = cpd - (int)col[i];
+        const uint32_t trial = (uint32_t)(d0 * d0) + (p1 >> 8) * (p1 >> 8) + (p2 >> 8) * (p2 >> 8);
+        if (trial < best_error) {
+          best_error = trial; best_x = x; best_c1 = p1 & 0xFFu; best_c2 = p2 & 0xFFu; best_i = i;
+          if (!best_error) { done = true; break; }
+        }
+      } while (*p != 0xFFFF);
+    }
+  }
+  diff = best_x & 1u; inten = (best_x >> 1) & 7u; sel = (best_x >> 4) & 3u;
+  uint32_t out[3];
+  out[best_i] = (best_x >> 8) & 255u;
+  out[next_comp[best_i]] = best_c1;
+  out[next_comp[best_i + 1]] = best_c2;
+  r = out[0]; g = out[1]; b = out[2];
 }
-#define UB_COMPUTE_HINTS_STUB 1
+
+// ---------------------------------------------------------------------------------------------------------
+// ETC1 hints
+struct YCbCr { int y, cb, cr; };
+UB_FN YCbCr to_ycbcr(uint32_t c) {
+  YCbCr o;
+  o.y = (int)ch(c, 0) * 54 + (int)ch(c, 1) * 183 + (int)ch(c, 2) * 19;
+  o.cb = ((int)ch(c, 2) << 8) - o.y;
+  o.cr = ((int)ch(c, 0) << 8) - o.y;
+  return o;
+}
+UB_FN uint64_t ycc_diff(const YCbCr& a, const YCbCr& b) {
+  const int64_t dy = a.y - b.y, dcb = a.cb - b.cb, dcr = a.cr - b.cr;
+  return (uint64_t)(dy * dy * 4 + dcr * dcr + dcb * dcb);
+}
+UB_FN float u64_to_float_h(uint64_t v) {
+#ifdef __CUDA_ARCH__
+  return __ull2float_rn(v);
+#else
+  return (float)v;
 #endif
+}
+UB_FN int clamp255(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
+
+UB_FN int gray_distance2(uint32_t c, int r, int g, int b) {
+  const int gd = (((int)ch(c, 0) - r) + ((int)ch(c, 1) - g) + ((int)ch(c, 2) - b) + 1) / 3;
+  const int dr = (int)ch(c, 0) - clamp255(r + gd), dg = (int)ch(c, 1) - clamp255(g + gd), db = (int)ch(c, 2) - clamp255(b + gd);
+  return dr * dr + dg * dg + db * db;
+}
+
+UB_FN bool etc1_estimate_flipped(const uint32_t* px) {
+  int upper[3], lower[3], left[3], right[3];
+  for (uint32_t c = 0; c < 3; c++) {
+    int s00 = 0, s10 = 0, s01 = 0, s11 = 0;
+    for (uint32_t y = 0; y < 2; y++)
+      for (uint32_t x = 0; x < 2; x++) {
+        s00 += (int)ch(px[x + y * 4], c); s10 += (int)ch(px[(x + 2) + y * 4], c);
+        s01 += (int)ch(px[x + (y + 2) * 4], c); s11 += (int)ch(px[(x + 2) + (y + 2) * 4], c);
+      }
+    upper[c] = (s00 + s10 + 4) / 8; lower[c] = (s01 + s11 + 4) / 8; left[c] = (s00 + s01 + 4) / 8; right[c] = (s10 + s11 + 4) / 8;
+  }
+  int ug = 0, lg = 0, leg = 0, rg = 0;
+  for (uint32_t i = 0; i < 4; i++)
+    for (uint32_t j = 0; j < 2; j++) {
+      ug += gray_distance2(px[i + j * 4], upper[0], upper[1], upper[2]);
+      lg += gray_distance2(px[i + (2 + j) * 4], lower[0], lower[1], lower[2]);
+      leg += gray_distance2(px[j + i * 4], left[0], left[1], left[2]);
+      rg += gray_distance2(px[(2 + j) + i * 4], right[0], right[1], right[2]);
+    }
+  return (ug + lg) < (leg + rg);
+}
+
+UB_FN int etc1_bias_comp(int v, uint32_t bias, int limit, uint32_t subblock, uint32_t c) {  // apply_etc1_bias, one channel
+  int delta;
+  switch (bias) {
+    case 2: delta = subblock ? 0 : ((c == 0) ? -1 : 0); break;
+    case 5: delta = subblock ? 0 : ((c == 1) ? -1 : 0); break;
+    case 6: delta = subblock ? 0 : ((c == 2) ? -1 : 0); break;
+    case 7: delta = subblock ? 0 : ((c == 0) ? 1 : 0); break;
+    case 11: delta = subblock ? 0 : ((c == 1) ? 1 : 0); break;
+    case 15: delta = subblock ? 0 : ((c == 2) ? 1 : 0); break;
+    case 18: delta = subblock ? ((c == 0) ? -1 : 0) : 0; break;
+    case 19: delta = subblock ? ((c == 1) ? -1 : 0) : 0; break;
+    case 20: delta = subblock ? ((c == 2) ? -1 : 0) : 0; break;
+    case 21: delta = subblock ? ((c == 0) ? 1 : 0) : 0; break;
+    case 24: delta = subblock ? ((c == 1) ? 1 : 0) : 0; break;
+    case 8: delta = subblock ? ((c == 2) ? 1 : 0) : 0; break;
+    case 10: delta = -2; break;
+    case 27: delta = subblock ? 0 : -1; break;
+    case 28: delta = subblock ? -1 : 1; break;
+    case 29: delta = subblock ? 1 : 0; break;
+    case 30: delta = subblock ? -1 : 0; break;
+    case 31: delta = subblock ? 0 : 1; break;
+    default: { const int divs = (c == 0) ? 1 : (c == 1 ? 3 : 9); delta = (int)((bias / (uint32_t)divs) % 3u) - 1; break; }
+  }
+  if (v == 0) { if (delta == -2) v += 3; else v += delta + 1; }
+  else if (v == limit) v += (delta - 1);
+  else { v += delta; if (v < 0 || v > limit) v = (v - delta) - delta; }
+  return v;
+}
+
+// the four decoded colours of one ETC1 sub-block as YCbCr
+UB_FN void etc1_subblock_colors(const int* base8, uint32_t inten, YCbCr* out) {
+  for (uint32_t s = 0; s < 4; s++) {
+    const int m = UBT(etc1_inten)[inten * 4 + s];
+    out[s] = to_ycbcr((uint32_t)clamp255(base8[0] + m) | ((uint32_t)clamp255(base8[1] + m) << 8) | ((uint32_t)clamp255(base8[2] + m) << 16));
+  }
+}
+// texel index j (0..7) of sub-block `subset` under `flip`
+UB_FN uint32_t etc1_texel(uint32_t flip, uint32_t subset, uint32_t j) {
+  return flip ? ((subset * 2 + (j >> 2)) * 4 + (j & 3u)) : ((j >> 1) * 4 + subset * 2 + (j & 1u));
+}
+
+UB_FN void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
+                              uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
+  const bool faster = (flags & 64u) != 0, fastest = (flags & 128u) != 0;
+  const bool has_bias = UBT(uastc_mode_has_etc1_bias)[mode] != 0;
+  const uint8_t sorted_bias[32] = {13, 0, 22, 29, 27, 12, 26, 9, 30, 31, 8, 10, 25, 2, 23, 5, 15, 7, 3, 11, 6, 17, 28, 18, 1, 19, 20, 21, 24, 4, 14, 16};
+  uint32_t last_bias = 1;
+  bool use_table = false;
+  const bool flip_estimate = (level <= 1) || faster || fastest;
+  if (has_bias) {
+    use_table = (level <= 3);
+    switch (level) {
+      case 0: last_bias = fastest ? 1 : (faster ? 1 : 2); break;
+      case 1: last_bias = fastest ? 1 : (faster ? 3 : 5); break;
+      case 2: last_bias = fastest ? 1 : (faster ? 10 : 20); break;
+      case 3: last_bias = fastest ? 1 : (faster ? 16 : 32); break;
+      default: last_bias = 32; break;
+    }
+  }
+  YCbCr src_y[16], dec_y[16];
+  for (uint32_t i = 0; i < 16; i++) { src_y[i] = to_ycbcr(px[i]); dec_y[i] = to_ycbcr(dec[i]); }
+  uint32_t first_flip = 0, last_flip = 2, last_individ = 2;
+  if (flags & 256u) { last_flip = 1; last_individ = 1; }
+  else if (flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
+
+  uint64_t best_err = ~0ull;
+  o_flip = 0; o_diff = 0; o_i0 = 0; o_i1 = 0; o_bias = 0;
+  for (uint32_t flip = first_flip; flip < last_flip; flip++)
+    for (uint32_t individ = 0; individ < last_individ; individ++) {
+      const uint32_t mul = individ ? 15u : 31u;
+      int unb[2][3], mn[2][3], mx[2][3];
+      for (uint32_t s = 0; s < 2; s++) {
+        uint32_t avg[3] = {0, 0, 0};
+        for (uint32_t c = 0; c < 3; c++) { mn[s][c] = 255; mx[s][c] = 0; }
+        for (uint32_t j = 0; j < 8; j++) {
+          const uint32_t p = dec[etc1_texel(flip, s, j)];
+          for (uint32_t c = 0; c < 3; c++) {
+            const int v = (int)ch(p, c);
+            avg[c] += (uint32_t)v;
+            if (v < mn[s][c]) mn[s][c] = v;
+            if (v > mx[s][c]) mx[s][c] = v;
+          }
+        }
+        for (uint32_t c = 0; c < 3; c++) unb[s][c] = (int)((avg[c] * mul + 1020u) / (8u * 255u));
+      }
+      for (uint32_t bi = 0; bi < last_bias; bi++) {
+        const uint32_t bias = use_table ? sorted_bias[bi] : bi;
+        int base8[2][3];
+        {
+          int bc[2][3];
+          for (uint32_t s = 0; s < 2; s++)
+            for (uint32_t c = 0; c < 3; c++) bc[s][c] = has_bias ? etc1_bias_comp(unb[s][c], bias, (int)mul, s, c) : unb[s][c];
+          for (uint32_t c = 0; c < 3; c++) {
+            if (individ) {
+              base8[0][c] = (bc[0][c] << 4) | bc[0][c];
+              base8[1][c] = (bc[1][c] << 4) | bc[1][c];
+            } else {
+              const int d = clampi(bc[1][c] - bc[0][c], -4, 3);
+              const int c1 = clampi(bc[0][c] + d, 0, 31);
+              base8[0][c] = (bc[0][c] << 3) | (bc[0][c] >> 2);
+              base8[1][c] = (c1 << 3) | (c1 >> 2);
+            }
+          }
+        }
+        uint32_t best_inten[2] = {0, 0};
+        for (uint32_t s = 0; s < 2; s++) {
+          int range = 0;
+          for (uint32_t c = 0; c < 3; c++) {
+            int a = mx[s][c] - base8[s][c]; if (a < 0) a = -a;
+            int b = base8[s][c] - mn[s][c]; if (b < 0) b = -b;
+            if (a > range) range = a;
+            if (b > range) range = b;
+          }
+          const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
+          uint64_t best_sub = ~0ull;
+          for (uint32_t it = 0; it < limit; it++) {
+            YCbCr tab[4];
+            etc1_subblock_colors(base8[s], it, tab);
+            uint64_t total = 0;
+            for (uint32_t j = 0; j < 8; j++) {
+              const YCbCr& c = dec_y[etc1_texel(flip, s, j)];
+              uint64_t m = ycc_diff(tab[0], c);
+              for (uint32_t k = 1; k < 4; k++) { const uint64_t e = ycc_diff(tab[k], c); if (e < m) m = e; }
+              total += m;
+            }
+            // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
+            if (!flip && total >= best_sub) break;
+            if (total < best_sub) { best_sub = total; best_inten[s] = it; }
+          }
+        }
+        uint64_t err = 0;
+        for (uint32_t s = 0; s < 2; s++) {
+          YCbCr tab[4];
+          etc1_subblock_colors(base8[s], best_inten[s], tab);
+          for (uint32_t j = 0; j < 8; j++) {
+            const uint32_t t = etc1_texel(flip, s, j);
+            uint64_t m = ycc_diff(tab[0], dec_y[t]) << 2;
+            for (uint32_t k = 1; k < 4; k++) { const uint64_t e = (ycc_diff(tab[k], dec_y[t]) << 2) + k; if (e < m) m = e; }
+            err += ycc_diff(src_y[t], tab[(uint32_t)m & 3u]);
+          }
+        }
+        if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
+      }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// ETC2 EAC A8 table / multiplier hint
+UB_FN uint32_t compute_eac_hint(const uint32_t* dec, uint32_t mul_rad, uint32_t table_mask) {
+  int a[16];
+  int mn = 255, mx = 0;
+  for (uint32_t i = 0; i < 16; i++) { a[i] = (int)(dec[i] >> 24); if (a[i] < mn) mn = a[i]; if (a[i] > mx) mx = a[i]; }
+  if (mn == mx) return 13u | (1u << 4);
+  const uint32_t arange = (uint32_t)(mx - mn);
+  uint64_t best = ~0ull;
+  uint32_t b_table = 0, b_mul = 0;
+  for (uint32_t table = 0; table < 16; table++) {
+    if (!((table_mask >> table) & 1u)) continue;
+    const int8_t* T = UBT(etc2_eac) + table * 8;
+    const float range = (float)((int)T[7] - (int)T[3]);
+    const float t = f_div((float)(0 - (int)T[3]), range);
+    const int center = (int)roundf(f_add((float)mn, f_mul(f_sub((float)mx, (float)mn), t)));
+    const int base = clamp255(center);
+    const int mul = (int)roundf(f_div((float)arange, range));
+    const int mul_low = clampi(mul - (int)mul_rad, 1, 15), mul_high = clampi(mul + (int)mul_rad, 1, 15);
+    for (int m = mul_low; m <= mul_high; m++) {
+      uint64_t total = 0;
+      for (uint32_t i = 0; i < 16; i++) {
+        uint32_t be = 0xFFFFFFFFu;
+        for (uint32_t s = 0; s < 8; s++) {
+          int e = a[i] - clamp255(m * (int)T[s] + base);
+          if (e < 0) e = -e;
+          if ((uint32_t)e < be) be = (uint32_t)e;
+        }
+        total += (uint64_t)be * be;
+      }
+      if (total < best) { best = total; b_mul = (uint32_t)m; b_table = table; if (!best) return b_table | (b_mul << 4); }
+    }
+  }
+  return b_table | (b_mul << 4);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// BC1 hints
+struct Bc1Block { uint32_t lo16, hi16, sels; };  // colour0, colour1, 2-bit selectors (texel 0 in the low bits)
+
+UB_FN void bc1_find_sels(const uint32_t* px, uint32_t lr, uint32_t lg, uint32_t lb, uint32_t hr, uint32_t hg, uint32_t hb, uint8_t* sels) {
+  int br[4], bg[4], bb[4];
+  br[0] = (int)((lr << 3) | (lr >> 2)); bg[0] = (int)((lg << 2) | (lg >> 4)); bb[0] = (int)((lb << 3) | (lb >> 2));
+  br[3] = (int)((hr << 3) | (hr >> 2)); bg[3] = (int)((hg << 2) | (hg >> 4)); bb[3] = (int)((hb << 3) | (hb >> 2));
+  br[1] = (br[0] * 2 + br[3]) / 3; bg[1] = (bg[0] * 2 + bg[3]) / 3; bb[1] = (bb[0] * 2 + bb[3]) / 3;
+  br[2] = (br[3] * 2 + br[0]) / 3; bg[2] = (bg[3] * 2 + bg[0]) / 3; bb[2] = (bb[3] * 2 + bb[0]) / 3;
+  int ar = br[3] - br[0], ag = bg[3] - bg[0], ab = bb[3] - bb[0];
+  int dots[4];
+  for (int i = 0; i < 4; i++) dots[i] = br[i] * ar + bg[i] * ag + bb[i] * ab;
+  const int t0 = dots[0] + dots[1], t1 = dots[1] + dots[2], t2 = dots[2] + dots[3];
+  ar *= 2; ag *= 2; ab *= 2;
+  for (uint32_t i = 0; i < 16; i++) {
+    const int d = (int)ch(px[i], 0) * ar + (int)ch(px[i], 1) * ag + (int)ch(px[i], 2) * ab;
+    sels[i] = (uint8_t)(3 - ((d <= t0) + (d < t1) + (d < t2)));
+  }
+}
+
+UB_FN bool bc1_least_squares(const uint32_t* px, const uint8_t* sels, float* xl, float* xh) {
+  uint32_t q00[3] = {0, 0, 0}, tt[3] = {0, 0, 0}, wacc = 0;
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t s = sels[i];
+    wacc += (s == 0) ? 0x000009u : (s == 1) ? 0x010204u : (s == 2) ? 0x040201u : 0x090000u;
+    for (uint32_t c = 0; c < 3; c++) { const uint32_t v = ch(px[i], c); tt[c] += v; q00[c] += s * v; }
+  }
+  const float z00 = (float)((wacc >> 16) & 0xFFu), z10 = (float)((wacc >> 8) & 0xFFu), z11 = (float)(wacc & 0xFFu);
+  const float z01 = z10;
+  float det = f_sub(f_mul(z00, z11), f_mul(z01, z10));
+  if ((det < 0 ? -det : det) < 1e-8f) return false;
+  det = f_div(3.0f, det);
+  const float iz00 = f_mul(z11, det), iz01 = f_mul(-z01, det), iz10 = f_mul(-z10, det), iz11 = f_mul(z00, det);
+  for (uint32_t c = 0; c < 3; c++) {
+    const float fq00 = (float)q00[c];
+    const float q10 = f_sub(f_mul((float)tt[c], 3.0f), fq00);
+    xl[c] = f_add(f_mul(iz00, fq00), f_mul(iz01, q10));
+    xh[c] = f_add(f_mul(iz10, fq00), f_mul(iz11, q10));
+  }
+  for (uint32_t c = 0; c < 3; c++)
+    if (xl[c] < 0.0f || xh[c] > 255.0f) {
+      uint32_t lo = 0xFFFFFFFFu, hi = 0;
+      for (uint32_t i = 0; i < 16; i++) { lo = minu(lo, ch(px[i], c)); hi = maxu(hi, ch(px[i], c)); }
+      if (lo == hi) { xl[c] = (float)lo; xh[c] = (float)hi; }
+    }
+  return true;
+}
+
+UB_FN uint32_t bc1_to5(uint32_t v) { v = v * 31 + 128; return ((v + (v >> 8)) >> 8) & 255u; }
+UB_FN uint32_t bc1_to6(uint32_t v) { v = v * 63 + 128; return ((v + (v >> 8)) >> 8) & 255u; }
+
+UB_FN Bc1Block bc1_solid(uint32_t fr, uint32_t fg, uint32_t fb) {
+  uint32_t mask = 0xAA;
+  const uint32_t m5r = UBT(bc1_match5)[fr], m6g = UBT(bc1_match6)[fg], m5b = UBT(bc1_match5)[fb];
+  uint32_t max16 = ((m5r & 255u) << 11) | ((m6g & 255u) << 5) | (m5b & 255u);
+  uint32_t min16 = ((m5r >> 8) << 11) | ((m6g >> 8) << 5) | (m5b >> 8);
+  if (min16 == max16) {
+    mask = 0;
+    if (min16 > 0) min16--; else { max16 = 1; min16 = 0; mask = 0x55; }
+  }
+  if (max16 < min16) { const uint32_t t = max16; max16 = min16; min16 = t; mask ^= 0x55; }
+  Bc1Block b; b.lo16 = max16; b.hi16 = min16; b.sels = mask * 0x01010101u;
+  return b;
+}
+
+// encode_bc1 with flags 0 (have_sels = false) or cEncodeBC1UseSelectors (sels given, linear 0..3), one LS pass
+UB_FN Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels) {
+  int avg_r = -1, avg_g = 0, avg_b = 0;
+  uint32_t lr = 0, lg = 0, lb = 0, hr = 0, hg = 0, hb = 0;
+  if (!have_sels) {
+    const uint32_t f0 = px[0] & 0xFFFFFFu;
+    bool solid = true;
+    for (uint32_t j = 1; j < 16; j++) if ((px[j] & 0xFFFFFFu) != f0) { solid = false; break; }
+    if (solid) return bc1_solid(ch(px[0], 0), ch(px[0], 1), ch(px[0], 2));
+    int tot[3] = {0, 0, 0}, mx[3] = {0, 0, 0}, mn[3] = {255, 255, 255};
+    for (uint32_t i = 0; i < 16; i++)
+      for (uint32_t c = 0; c < 3; c++) { const int v = (int)ch(px[i], c); tot[c] += v; if (v > mx[c]) mx[c] = v; if (v < mn[c]) mn[c] = v; }
+    avg_r = (tot[0] + 8) >> 4; avg_g = (tot[1] + 8) >> 4; avg_b = (tot[2] + 8) >> 4;
+    int icov[6] = {0, 0, 0, 0, 0, 0};
+    for (uint32_t i = 0; i < 16; i++) {
+      const int r = (int)ch(px[i], 0) - avg_r, g = (int)ch(px[i], 1) - avg_g, b = (int)ch(px[i], 2) - avg_b;
+      icov[0] += r * r; icov[1] += r * g; icov[2] += r * b; icov[3] += g * g; icov[4] += g * b; icov[5] += b * b;
+    }
+    float cov[6];
+    const float k255 = f_div(1.0f, 255.0f);
+    for (int i = 0; i < 6; i++) cov[i] = f_mul((float)icov[i], k255);
+    float xr = (float)(mx[0] - mn[0]), xg = (float)(mx[1] - mn[1]), xb = (float)(mx[2] - mn[2]);
+    for (int it = 0; it < 4; it++) {
+      const float r = f_add(f_add(f_mul(xr, cov[0]), f_mul(xg, cov[1])), f_mul(xb, cov[2]));
+      const float g = f_add(f_add(f_mul(xr, cov[1]), f_mul(xg, cov[3])), f_mul(xb, cov[4]));
+      const float b = f_add(f_add(f_mul(xr, cov[2]), f_mul(xg, cov[4])), f_mul(xb, cov[5]));
+      xr = r; xg = g; xb = b;
+    }
+    const float ar = xr < 0 ? -xr : xr, ag = xg < 0 ? -xg : xg, ab = xb < 0 ? -xb : xb;
+    float k = ar > ag ? ar : ag;
+    k = k > ab ? k : ab;
+    int sr = 306, sg = 601, sb = 117;
+    if (k >= 2) { const float m = f_div(1024.0f, k); sr = (int)f_mul(xr, m); sg = (int)f_mul(xg, m); sb = (int)f_mul(xb, m); }
+    int low_dot = 0x7FFFFFFF, high_dot = (int)0x80000000, low_c = 0, high_c = 0;
+    for (uint32_t i = 0; i < 16; i++) {
+      const int dot = (int)ch(px[i], 0) * sr + (int)ch(px[i], 1) * sg + (int)ch(px[i], 2) * sb;
+      if (dot < low_dot) { low_dot = dot; low_c = (int)i; }
+      if (dot > high_dot) { high_dot = dot; high_c = (int)i; }
+    }
+    lr = bc1_to5(ch(px[low_c], 0)); lg = bc1_to6(ch(px[low_c], 1)); lb = bc1_to5(ch(px[low_c], 2));
+    hr = bc1_to5(ch(px[high_c], 0)); hg = bc1_to6(ch(px[high_c], 1)); hb = bc1_to5(ch(px[high_c], 2));
+    bc1_find_sels(px, lr, lg, lb, hr, hg, hb, sels);
+  }
+  {
+    float xl[3], xh[3];
+    if (!bc1_least_squares(px, sels, xl, xh)) {
+      if (avg_r < 0) {
+        int tot[3] = {0, 0, 0};
+        for (uint32_t i = 0; i < 16; i++) for (uint32_t c = 0; c < 3; c++) tot[c] += (int)ch(px[i], c);
+        avg_r = (tot[0] + 8) >> 4; avg_g = (tot[1] + 8) >> 4; avg_b = (tot[2] + 8) >> 4;
+      }
+      lr = UBT(bc1_match5)[avg_r] & 255u; lg = UBT(bc1_match6)[avg_g] & 255u; lb = UBT(bc1_match5)[avg_b] & 255u;
+      hr = UBT(bc1_match5)[avg_r] >> 8; hg = UBT(bc1_match6)[avg_g] >> 8; hb = UBT(bc1_match5)[avg_b] >> 8;
+    } else {
+      const float k5 = f_div(31.0f, 255.0f), k6 = f_div(63.0f, 255.0f);
+      lr = (uint32_t)clampi((int)f_add(f_mul(xl[0], k5), .5f), 0, 31); lg = (uint32_t)clampi((int)f_add(f_mul(xl[1], k6), .5f), 0, 63);
+      lb = (uint32_t)clampi((int)f_add(f_mul(xl[2], k5), .5f), 0, 31);
+      hr = (uint32_t)clampi((int)f_add(f_mul(xh[0], k5), .5f), 0, 31); hg = (uint32_t)clampi((int)f_add(f_mul(xh[1], k6), .5f), 0, 63);
+      hb = (uint32_t)clampi((int)f_add(f_mul(xh[2], k5), .5f), 0, 31);
+    }
+    bc1_find_sels(px, lr, lg, lb, hr, hg, hb, sels);
+  }
+  uint32_t lc16 = lb | (lg << 5) | (lr << 11), hc16 = hb | (hg << 5) | (hr << 11);
+  Bc1Block b;
+  if (lc16 == hc16) {
+    uint32_t mask = 0;
+    if (hc16 > 0) hc16--; else { hc16 = 0; lc16 = 1; mask = 0x55; }
+    b.lo16 = lc16; b.hi16 = hc16; b.sels = mask * 0x01010101u;
+  } else {
+    uint32_t inv = 0;
+    if (lc16 < hc16) { const uint32_t t = lc16; lc16 = hc16; hc16 = t; inv = 0x55555555u; }
+    uint32_t packed = 0;
+    for (uint32_t i = 0; i < 16; i++) packed |= ((0x78u >> (2 * sels[i])) & 3u) << (i * 2);  // {0,2,3,1}
+    b.lo16 = lc16; b.hi16 = hc16; b.sels = packed ^ inv;
+  }
+  return b;
+}
+
+UB_FN void bc1_decode(const Bc1Block& b, uint32_t* out) {  // unpack_bc1, RGB only
+  uint32_t c[4][3];
+  const uint32_t l = b.lo16, h = b.hi16;
+  c[0][0] = (l >> 11) & 31u; c[0][1] = (l >> 5) & 63u; c[0][2] = l & 31u;
+  c[1][0] = (h >> 11) & 31u; c[1][1] = (h >> 5) & 63u; c[1][2] = h & 31u;
+  for (int k = 0; k < 2; k++) { c[k][0] = (c[k][0] << 3) | (c[k][0] >> 2); c[k][1] = (c[k][1] << 2) | (c[k][1] >> 4); c[k][2] = (c[k][2] << 3) | (c[k][2] >> 2); }
+  for (int j = 0; j < 3; j++) {
+    if (l > h) { c[2][j] = (c[0][j] * 2 + c[1][j]) / 3; c[3][j] = (c[1][j] * 2 + c[0][j]) / 3; }
+    else { c[2][j] = (c[0][j] + c[1][j]) / 2; c[3][j] = 0; }
+  }
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t s = (b.sels >> (2 * i)) & 3u;
+    out[i] = c[s][0] | (c[s][1] << 8) | (c[s][2] << 16);
+  }
+}
+
+UB_FN uint32_t uastc_to_bc1_sel(uint32_t wb, uint32_t w) {  // s_uastc{1..5}_to_bc1 (XC:17365-17369)
+  switch (wb) {
+    case 1: return w;
+    case 2: return (0x78u >> (2 * w)) & 3u;                                   // 0,2,3,1
+    case 3: return (0x5FA0u >> (2 * w)) & 3u;                                 // 0,0,2,2,3,3,1,1
+    case 4: return (uint32_t)((0x57FFAA80ull >> (2 * w)) & 3u);               // 0,0,0,2,2,2,2,2,3,3,3,3,3,1,1,1
+    default: return (uint32_t)((0x555FFFFFAAAAA000ull >> (2 * w)) & 3u);      // 6x0,10x2,10x3,6x1
+  }
+}
+
+// compute_bc1_hints.  `nc` = the winning candidate AFTER anchor normalisation (what pack + unpack would yield).
+UB_FN void compute_bc1_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, uint32_t& hint0, uint32_t& hint1) {
+  hint0 = 0; hint1 = 0;
+  const uint32_t mode = nc.mode;
+  const bool has0 = UBT(uastc_mode_has_bc1_hint0)[mode] != 0, has1 = UBT(uastc_mode_has_bc1_hint1)[mode] != 0;
+  if (!has0 && !has1) return;
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t er = md_endpoint_range(d), comps = md_comps(d), wb = md_weight_bits(d), pshift = md_dual_plane(d);
+  uint8_t sels[16];
+  uint32_t t_px[16], h0_px[16], h1_px[16];
+  bc1_decode(encode_bc1(dec, false, sels), t_px);
+  for (uint32_t i = 0; i < 16; i++) { h0_px[i] = 0; h1_px[i] = 0; }
+  if (has1) {
+    // BC1 selector order -> linear order {0,3,1,2}
+    for (uint32_t i = 0; i < 16; i++) { const uint32_t s = uastc_to_bc1_sel(wb, nc.w[i << pshift]); sels[i] = (uint8_t)((0x9Cu >> (2 * s)) & 3u); }
+    bc1_decode(encode_bc1(dec, true, sels), h1_px);
+  }
+  if (has0) {
+    uint32_t l[3], h[3];
+    if (comps == 2) { l[0] = l[1] = l[2] = astc_unquant(er, nc.ep[0]); h[0] = h[1] = h[2] = astc_unquant(er, nc.ep[1]); }
+    else for (uint32_t c = 0; c < 3; c++) { l[c] = astc_unquant(er, nc.ep[2 * c]); h[c] = astc_unquant(er, nc.ep[2 * c + 1]); }
+    Bc1Block b;
+    b.lo16 = ((l[0] * 31 + 127) / 255) << 11 | ((l[1] * 63 + 127) / 255) << 5 | ((l[2] * 31 + 127) / 255);
+    b.hi16 = ((h[0] * 31 + 127) / 255) << 11 | ((h[1] * 63 + 127) / 255) << 5 | ((h[2] * 31 + 127) / 255);
+    if (b.lo16 == b.hi16) {
+      uint32_t mask = 0;
+      if (b.hi16 > 0) b.hi16--; else { b.hi16 = 0; b.lo16 = 1; mask = 0x55; }
+      b.sels = mask * 0x01010101u;
+    } else {
+      bool inv = false;
+      if (b.lo16 < b.hi16) { const uint32_t t = b.lo16; b.lo16 = b.hi16; b.hi16 = t; inv = true; }
+      uint32_t s32 = 0;
+      for (int i = 15; i >= 0; --i) { uint32_t s = uastc_to_bc1_sel(wb, nc.w[i << pshift]); if (inv) s ^= 1u; s32 = (s32 << 2) | s; }
+      b.sels = s32;
+    }
+    bc1_decode(b, h0_px);
+  }
+  uint64_t te = 0, e0 = 0, e1 = 0;
+  for (uint32_t i = 0; i < 16; i++) { te += dist_rgb(px[i], t_px[i]); e0 += dist_rgb(px[i], h0_px[i]); e1 += dist_rgb(px[i], h1_px[i]); }
+  const float t_err = f_sqrt(u64_to_float_h(te)), t0 = f_sqrt(u64_to_float_h(e0)), t1 = f_sqrt(u64_to_float_h(e1));
+  if (has0 && t0 <= f_mul(t_err, 1.075f)) hint0 = 1;
+  if (has1 && t1 <= f_mul(t_err, 1.075f)) hint1 = 1;
+}
 
 }  // namespace ub
