@@ -94,3 +94,53 @@ def transcode(src, target, spans=None, dst=None):
 def transcode_dev(target, d_src, d_dst, n_blocks, stream=0, d_first_bad=0):
     """Device-pointer transcode (ints / torch data_ptr()); asynchronous when a stream handle is given."""
     _check(lib().b200_uastc_transcode_dev(target, d_src, d_dst, n_blocks, stream or None, d_first_bad or None))
+
+
+def encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream=0):
+    """Device-pointer encode of n_blocks pre-gathered 4x4 RGBA8 blocks (64 B each) -> 16 B UASTC blocks."""
+    _check(lib().b200_uastc_encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream or None))
+
+
+def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale=0.0, smooth_std_dev=0.0, total_jobs=0):
+    p = UastcParams()
+    p.struct_size = ctypes.sizeof(UastcParams)
+    p.pack_flags = pack_flags
+    p.rdo_enable = 1 if rdo else 0
+    p.rdo_lambda = rdo_lambda
+    p.rdo_dict_size = dict_size
+    p.rdo_max_smooth_block_error_scale = smooth_scale
+    p.rdo_max_smooth_block_std_dev = smooth_std_dev
+    p.rdo_total_jobs = total_jobs
+    return p
+
+
+def encode_images(images, pack_flags, **rdo):
+    """Host-buffer encode through the C ABI (b200_uastc_encode).  images: list of uint8 [h,w,4] arrays.
+    Returns (list of uint8 [nblocks,16] arrays in raster block order, any_alpha)."""
+    imgs = [np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+    arr = (Image * max(1, len(imgs)))()
+    outs = []
+    optr = (ctypes.c_void_p * max(1, len(imgs)))()
+    for i, im in enumerate(imgs):
+        h, w = im.shape[:2]
+        assert im.shape[2] == 4
+        arr[i] = Image(im.ctypes.data, w, h, 0)
+        o = np.zeros((((w + 3) // 4) * ((h + 3) // 4), 16), np.uint8)
+        outs.append(o)
+        optr[i] = o.ctypes.data
+    p = make_params(pack_flags, **rdo)
+    any_alpha = ctypes.c_uint32(0)
+    _check(lib().b200_uastc_encode(arr, len(imgs), ctypes.byref(p), optr, ctypes.byref(any_alpha)))
+    return outs, bool(any_alpha.value)
+
+
+def encode_blocks(block_pixels, pack_flags):
+    """Convenience for tests: n pre-gathered 4x4 blocks (uint8 [n,64]) -> uint8 [n,16], via the image entry point
+    (the blocks are laid out as one 4-texel-high strip image so the C ABI's gather reproduces them)."""
+    px = np.ascontiguousarray(block_pixels, dtype=np.uint8).reshape(-1, 4, 4, 4)
+    n = px.shape[0]
+    if n == 0:
+        return np.zeros((0, 16), np.uint8)
+    strip = np.ascontiguousarray(px.transpose(1, 0, 2, 3).reshape(4, n * 4, 4))
+    outs, _ = encode_images([strip], pack_flags)
+    return outs[0]

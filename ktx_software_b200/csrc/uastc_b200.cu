@@ -15,6 +15,7 @@
 #include "../../include/ktx_b200_uastc.h"
 #include "uastc_to_bc7.cuh"
 #include "uastc_to_astc.cuh"
+#include "uastc_encode.cuh"
 
 namespace {
 
@@ -54,6 +55,72 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
     dst[i] = o;
     if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)i);
   }
+}
+
+// Encode (reference hot loop #1, ENC/basisu_comp.cpp:1519-1562 -> encode_uastc): one thread per 4x4 block, so a warp
+// is a group of 32 neighbouring blocks that walk the mode list in lock-step.  The 4x4 gather with edge replication
+// (image::extract_block_clamped, ENC/basisu_enc.h:3081) is fused into the load.  MAXC bounds the candidate list:
+// 21 at levels 0-3 (partition estimators on), 170 at level 4.
+template <int MAXC>
+__device__ __forceinline__ void encode_one(const uint32_t* px, uint32_t flags, uint4* dst) {
+  ub::Candidate cands[MAXC];
+  uint64_t overall[MAXC];
+  float uerr[MAXC];
+  const ub::Bits128 b = ub::encode_uastc_block(px, flags, cands, overall, uerr);
+  uint4 o;
+  o.x = (uint32_t)b.lo; o.y = (uint32_t)(b.lo >> 32); o.z = (uint32_t)b.hi; o.w = (uint32_t)(b.hi >> 32);
+  *dst = o;
+}
+
+template <int MAXC>
+__global__ void __launch_bounds__(128) k_encode_image(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
+                                                      uint4* __restrict__ out, uint32_t bx, uint32_t by, uint32_t flags,
+                                                      unsigned int* __restrict__ any_alpha) {
+  const uint32_t n = bx * by;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t x0 = (i % bx) * 4, y0 = (i / bx) * 4;
+    uint32_t px[16];
+    uint32_t amin = 255;
+    if (x0 + 4 <= w && y0 + 4 <= h && !(pitch & 15u)) {
+#pragma unroll
+      for (uint32_t y = 0; y < 4; y++) {
+        const uint4 v = __ldg((const uint4*)(img + (size_t)(y0 + y) * pitch + (size_t)x0 * 4));
+        px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
+      }
+    } else {
+      for (uint32_t y = 0; y < 4; y++)
+        for (uint32_t x = 0; x < 4; x++) {
+          const uint32_t sx = min(x0 + x, w - 1), sy = min(y0 + y, h - 1);
+          const uint8_t* q = img + (size_t)sy * pitch + (size_t)sx * 4;
+          px[4 * y + x] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+        }
+    }
+#pragma unroll
+    for (uint32_t k = 0; k < 16; k++) amin = min(amin, px[k] >> 24);
+    if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
+    encode_one<MAXC>(px, flags, out + i);
+  }
+}
+
+template <int MAXC>
+__global__ void __launch_bounds__(128) k_encode_blocks(const uint4* __restrict__ src, uint4* __restrict__ out, uint64_t n, uint32_t flags) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    uint32_t px[16];
+#pragma unroll
+    for (uint32_t y = 0; y < 4; y++) {
+      const uint4 v = __ldg(src + i * 4 + y);
+      px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
+    }
+    encode_one<MAXC>(px, flags, out + i);
+  }
+}
+
+const int ENC_THREADS = 128;
+const int MAXC_FAST = 21, MAXC_FULL = 170;
+
+unsigned encode_grid(uint64_t n) {
+  const uint64_t want = (n + ENC_THREADS - 1) / ENC_THREADS;
+  return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)g_ctx.sm_count * 64));
 }
 
 __global__ void k_set_u64(unsigned long long* p, unsigned long long v) { *p = v; }
@@ -256,11 +323,96 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
   return B200_OK;
 }
 
-int b200_uastc_encode(const b200_image*, uint32_t, const b200_uastc_params*, uint8_t* const*, uint32_t*) {
-  return fail(B200_E_INVALID_VALUE, "b200_uastc_encode: not built yet");
+int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64_t n_blocks, uint32_t pack_flags, void* stream) {
+  if (n_blocks && (!d_block_pixels || !d_out)) return fail(B200_E_INVALID_VALUE, "null device pointer");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  if (!n_blocks) return B200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
+  const bool full = (pack_flags & 7u) >= 4u;
+  if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(n_blocks), ENC_THREADS, 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
+  else k_encode_blocks<MAXC_FAST><<<encode_grid(n_blocks), ENC_THREADS, 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
+  g_launches++;
+  CU(cudaGetLastError());
+  if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
 }
-int b200_uastc_encode_blocks_dev(const void*, void*, uint64_t, uint32_t, void*) {
-  return fail(B200_E_INVALID_VALUE, "b200_uastc_encode_blocks_dev: not built yet");
+
+int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
+                      uint32_t* out_any_alpha) {
+  if (out_any_alpha) *out_any_alpha = 0;
+  if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
+  if (n_images && (!images || !out_blocks)) return fail(B200_E_INVALID_VALUE, "null pointer");
+  if (params->rdo_enable) return fail(B200_E_INVALID_VALUE, "UASTC RDO is not built yet");
+  for (uint32_t i = 0; i < n_images; i++)
+    if (!images[i].rgba || !images[i].width || !images[i].height || !out_blocks[i]) return fail(B200_E_INVALID_VALUE, "bad image");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  cudaStream_t* ss;
+  rc = get_streams(&ss);
+  if (rc) return rc;
+  if (!n_images) return B200_OK;
+
+  // Two staging slots so image i+1 uploads while image i encodes and image i-1 downloads.
+  const int SLOTS = 2;
+  size_t max_in = 0, max_out = 0;
+  for (uint32_t i = 0; i < n_images; i++) {
+    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * 4;
+    if (pitch < (size_t)images[i].width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+    max_in = std::max(max_in, pitch * images[i].height);
+    max_out = std::max(max_out, (size_t)((images[i].width + 3) / 4) * ((images[i].height + 3) / 4) * 16);
+  }
+  uint8_t* d_in[SLOTS] = {0}; uint8_t* d_out[SLOTS] = {0};
+  unsigned int* d_alpha = nullptr;
+  cudaEvent_t ev_in[SLOTS], ev_k[SLOTS], ev_out[SLOTS];
+  const int nslots = (int)std::min<uint32_t>(SLOTS, n_images);
+  auto cleanup = [&]() {
+    for (int i = 0; i < SLOTS; i++) { if (d_in[i]) cudaFree(d_in[i]); if (d_out[i]) cudaFree(d_out[i]); }
+    if (d_alpha) cudaFree(d_alpha);
+  };
+  for (int i = 0; i < nslots; i++) {
+    cudaError_t e1 = cudaMalloc(&d_in[i], max_in), e2 = cudaMalloc(&d_out[i], max_out);
+    if (e1 != cudaSuccess || e2 != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging", e1 != cudaSuccess ? e1 : e2); }
+    cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
+  }
+  if (cudaMalloc(&d_alpha, sizeof(unsigned int)) != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flag"); }
+  cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
+  cudaMemsetAsync(d_alpha, 0, sizeof(unsigned int), s_k);
+  const bool full = (params->pack_flags & 7u) >= 4u;
+  cudaError_t err = cudaSuccess;
+  for (uint32_t i = 0; i < n_images && err == cudaSuccess; i++) {
+    const b200_image& im = images[i];
+    const int b = (int)(i % nslots);
+    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
+    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
+    if (i >= (uint32_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
+    err = cudaMemcpyAsync(d_in[b], im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, s_in);
+    if (err != cudaSuccess) break;
+    cudaEventRecord(ev_in[b], s_in);
+    cudaStreamWaitEvent(s_k, ev_in[b], 0);
+    const uint64_t n = (uint64_t)bx * by;
+    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, im.height, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    else k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, im.height, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    g_launches++;
+    cudaEventRecord(ev_k[b], s_k);
+    cudaStreamWaitEvent(s_out, ev_k[b], 0);
+    err = cudaMemcpyAsync(out_blocks[i], d_out[b], n * 16, cudaMemcpyDeviceToHost, s_out);
+    cudaEventRecord(ev_out[b], s_out);
+  }
+  unsigned int h_alpha = 0;
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_k);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
+  if (err == cudaSuccess) err = cudaGetLastError();
+  if (err == cudaSuccess) err = cudaMemcpy(&h_alpha, d_alpha, sizeof(h_alpha), cudaMemcpyDeviceToHost);
+  for (int i = 0; i < nslots; i++) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); cudaEventDestroy(ev_out[i]); }
+  cleanup();
+  if (err != cudaSuccess) return fail(B200_E_CUDA, "encode pipeline", err);
+  if (out_any_alpha) *out_any_alpha = h_alpha ? 1u : 0u;
+  return B200_OK;
 }
 
 }  // extern "C"

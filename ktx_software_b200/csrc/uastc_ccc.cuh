@@ -97,7 +97,7 @@ UB_FN void set_astc_endpoints(const CccParams& p, CccResults& r) {
 }
 
 // evaluate_solution (bc7enc.cpp:822): interpolate the palette, project each texel, keep the better of two levels.
-UB_FN uint64_t evaluate_solution(uint32_t lo, uint32_t hi, const CccParams& p, const uint32_t* px, CccResults& r) {
+UB_BIG uint64_t evaluate_solution(uint32_t lo, uint32_t hi, const CccParams& p, const uint32_t* px, CccResults& r) {
   uint32_t amin = 0, amax = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++) {
@@ -220,7 +220,7 @@ UB_FN uint64_t find_optimal_solution(Vec4 xl, Vec4 xh, const CccParams& p, const
 
 // compute_least_squares_endpoints_rgb / _rgba (bc7enc.cpp:394-518): normal equations with double accumulators fed by
 // float products.
-UB_FN void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t* px, Vec4& xl, Vec4& xh) {
+UB_BIG void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t* px, Vec4& xl, Vec4& xh) {
   const uint32_t* wt = lsq_table(p.nw);
   const uint32_t nc = p.has_alpha ? 4u : 3u;
   double z00 = 0.0, z10 = 0.0, z11 = 0.0;
@@ -302,7 +302,7 @@ UB_FN uint64_t pack_one_color(int kind, const CccParams& p, const uint32_t* px, 
 }
 
 // color_cell_compression (bc7enc.cpp:1364-1762).  px: p.n texels, r | g<<8 | b<<16 | a<<24.
-UB_FN uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, CccResults& r) {
+UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, CccResults& r) {
   r.best_err = ~0ull;
   r.lo = 0; r.hi = 0; r.astc_lo = 0; r.astc_hi = 0;
   const int sck = p.force_sel ? -1 : single_color_kind(p);

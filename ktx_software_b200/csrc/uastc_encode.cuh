@@ -20,7 +20,7 @@ struct BlockHints {
 
 // Anchor normalisation (first half of pack_uastc, basisu_uastc_enc.cpp:262-338): every subset's (plane's) anchor
 // weight must have a clear MSB; otherwise flip that subset's weights and swap its endpoints.
-UB_FN void normalize_candidate(const Candidate& c, Candidate& o) {
+UB_BIG void normalize_candidate(const Candidate& c, Candidate& o) {
   o = c;
   if (c.mode == UASTC_MODE_SOLID) return;
   const uint32_t d = UBT(uastc_mode_desc)[c.mode];
@@ -52,7 +52,7 @@ UB_FN void normalize_candidate(const Candidate& c, Candidate& o) {
 }
 
 // Bit emission (second half of pack_uastc, :111-260 and :340-466).  `c` must already be normalised.
-UB_FN Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHints& h) {
+UB_BIG Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHints& h) {
   const uint32_t mode = c.mode;
   const uint32_t d = UBT(uastc_mode_desc)[mode];
   BitWriter bw;
@@ -145,7 +145,7 @@ UB_FN float u64_to_float(uint64_t v) {
 }
 
 // Candidate generation in the reference's order (basisu_uastc_enc.cpp:3290-3351).  Returns the count.
-UB_FN uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands) {
+UB_BIG uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands) {
   uint32_t n = 0;
   const uint32_t mm = cfg.mode_mask;
   const bool est = cfg.estimate_partition;
@@ -198,7 +198,7 @@ UB_FN uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_l
 }
 
 // Candidate scoring + selection (basisu_uastc_enc.cpp:3389-3549).  Returns the winning index.
-UB_FN uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uint32_t n, bool has_alpha, bool is_la, uint32_t flags,
+UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uint32_t n, bool has_alpha, bool is_la, uint32_t flags,
                                 uint64_t* overall, float* uerr_f) {
   if (n == 1) return 0;
   const bool favor_uastc = (flags & 8u) != 0;
@@ -225,7 +225,7 @@ UB_FN uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uint
     uerr_f[i] = f_sqrt(u64_to_float(ue));
     if ((double)uerr_f[i] < best_uerr) best_uerr = (double)uerr_f[i];
   }
-  const bool favor_simpler = (flags & 32u) != 0;  // cPackUASTCFavorSimplerModes
+  const bool favor_simpler = (flags & 512u) != 0;  // cPackUASTCFavorSimplerModes (basisu_uastc_enc.h:62)
   uint64_t best_err = ~0ull;
   uint32_t best = 0;
   bool found = false;

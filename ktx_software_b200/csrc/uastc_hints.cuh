@@ -12,7 +12,7 @@ namespace ub {
 
 // ---------------------------------------------------------------------------------------------------------
 // solid colour -> ETC1 (diff, inten, selector, r, g, b)
-UB_FN void hints_solid_etc1(uint32_t rgba, uint32_t& diff, uint32_t& inten, uint32_t& sel, uint32_t& r, uint32_t& g, uint32_t& b) {
+UB_BIG void hints_solid_etc1(uint32_t rgba, uint32_t& diff, uint32_t& inten, uint32_t& sel, uint32_t& r, uint32_t& g, uint32_t& b) {
   const uint32_t next_comp[4] = {1, 2, 0, 1};
   uint32_t col[3] = {ch(rgba, 0), ch(rgba, 1), ch(rgba, 2)};
   uint32_t best_error = 0xFFFFFFFFu, best_i = 0, best_x = 0, best_c1 = 0, best_c2 = 0;
@@ -135,7 +135,7 @@ UB_FN uint32_t etc1_texel(uint32_t flip, uint32_t subset, uint32_t j) {
   return flip ? ((subset * 2 + (j >> 2)) * 4 + (j & 3u)) : ((j >> 1) * 4 + subset * 2 + (j & 1u));
 }
 
-UB_FN void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
+UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
                               uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
   const bool faster = (flags & 64u) != 0, fastest = (flags & 128u) != 0;
   const bool has_bias = UBT(uastc_mode_has_etc1_bias)[mode] != 0;
@@ -242,7 +242,7 @@ UB_FN void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t*
 
 // ---------------------------------------------------------------------------------------------------------
 // ETC2 EAC A8 table / multiplier hint
-UB_FN uint32_t compute_eac_hint(const uint32_t* dec, uint32_t mul_rad, uint32_t table_mask) {
+UB_BIG uint32_t compute_eac_hint(const uint32_t* dec, uint32_t mul_rad, uint32_t table_mask) {
   int a[16];
   int mn = 255, mx = 0;
   for (uint32_t i = 0; i < 16; i++) { a[i] = (int)(dec[i] >> 24); if (a[i] < mn) mn = a[i]; if (a[i] > mx) mx = a[i]; }
@@ -343,7 +343,7 @@ UB_FN Bc1Block bc1_solid(uint32_t fr, uint32_t fg, uint32_t fb) {
 }
 
 // encode_bc1 with flags 0 (have_sels = false) or cEncodeBC1UseSelectors (sels given, linear 0..3), one LS pass
-UB_FN Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels) {
+UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels) {
   int avg_r = -1, avg_g = 0, avg_b = 0;
   uint32_t lr = 0, lg = 0, lb = 0, hr = 0, hg = 0, hb = 0;
   if (!have_sels) {
@@ -447,7 +447,7 @@ UB_FN uint32_t uastc_to_bc1_sel(uint32_t wb, uint32_t w) {  // s_uastc{1..5}_to_
 }
 
 // compute_bc1_hints.  `nc` = the winning candidate AFTER anchor normalisation (what pack + unpack would yield).
-UB_FN void compute_bc1_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, uint32_t& hint0, uint32_t& hint1) {
+UB_BIG void compute_bc1_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, uint32_t& hint0, uint32_t& hint1) {
   hint0 = 0; hint1 = 0;
   const uint32_t mode = nc.mode;
   const bool has0 = UBT(uastc_mode_has_bc1_hint0)[mode] != 0, has1 = UBT(uastc_mode_has_bc1_hint1)[mode] != 0;

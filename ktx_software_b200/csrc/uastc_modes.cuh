@@ -104,7 +104,7 @@ UB_FN uint32_t pattern_of(int kind, uint32_t idx) {
 UB_FN uint32_t pattern_count(int kind) { return kind == 3 ? 11u : (kind == 7 ? 19u : 30u); }
 
 // Best `max_parts` patterns, ascending error, first-wins on ties (estimate_partition2 == list of one).
-UB_FN void estimate_partitions(int kind, uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t* parts, uint32_t max_parts) {
+UB_BIG void estimate_partitions(int kind, uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t* parts, uint32_t max_parts) {
   uint64_t errs[8];
   for (uint32_t i = 0; i < max_parts; i++) { errs[i] = ~0ull; parts[i] = 0; }
   const uint32_t total = pattern_count(kind), subsets = (kind == 3) ? 3u : 2u;
@@ -126,7 +126,7 @@ UB_FN uint32_t sum_unq_rgb(uint32_t range, const uint8_t* ep, uint32_t which) {
 // "N subsets, one plane": modes 0,1,2,3,4,5,7,9,10,12,14,15,16,18.
 //   px     the 16 texels the cells see (already (l,0,0,a) for LA modes)
 //   kind   partition family (0 = single subset)
-UB_FN void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const uint32_t* px, const EncCfg& cfg, Candidate& c,
+UB_BIG void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const uint32_t* px, const EncCfg& cfg, Candidate& c,
                              const uint8_t* force_sel = nullptr) {
   const uint32_t d = UBT(uastc_mode_desc)[mode];
   const uint32_t subsets = md_subsets(d), comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
@@ -162,7 +162,7 @@ UB_FN void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const ui
 }
 
 // "one subset, two planes": modes 6 (rot 0..2), 11 and 13 (rot 0..3), 17 (L plane + A plane).
-UB_FN void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, const EncCfg& cfg, Candidate& c) {
+UB_BIG void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, const EncCfg& cfg, Candidate& c) {
   const uint32_t d = UBT(uastc_mode_desc)[mode];
   const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
   uint32_t p0[16], p1[16];

@@ -14,11 +14,13 @@
 #define UB_FN __device__ __forceinline__
 #define UB_MFN __device__ __forceinline__
 #define UB_FN_NOINLINE __device__ __noinline__
+#define UB_BIG __device__ __noinline__   /* large encoder stages: one out-of-line copy, called from every mode */
 #define UB_TABLE(type, name, n) static __device__ const type ubt_##name[n]
 #else
 #define UB_FN static inline
 #define UB_MFN inline
 #define UB_FN_NOINLINE static
+#define UB_BIG static
 #define UB_TABLE(type, name, n) static const type ubt_##name[n]
 #endif
 #define UBT(name) ubt_##name

@@ -110,3 +110,45 @@ def test_synthetic_images_are_deterministic():
     if px is not None:
         assert px.shape == (16 * 32, 64)
         assert (px[0].reshape(4, 4, 4) == a[:4, :4]).all()
+
+
+# ---- encoder: the host build of the product's encoder headers against the reference's fixtures
+def test_port_encode_matches_cts_encode_goldens():
+    """`ktx create --encode uastc` CTS goldens (tests/cts/clitests/golden/create/encode_uastc), level 2."""
+    cts = json.load(open(os.path.join(GOLD, "cts_uastc.json")))["encode"]
+    for sub, c in cts.items():
+        raw = np.frombuffer(bytes.fromhex(c["raw"]), np.uint8).reshape(c["height"], c["width"], c["comps"])
+        img = np.full((c["height"], c["width"], 4), 255, np.uint8)
+        if c["comps"] == 1:      # lib/src/basis_encode.cpp:696-699 default mappings: r -> rrr1, rg -> rg01
+            img[..., :3] = raw[..., :1]
+        elif c["comps"] == 2:
+            img[..., :2] = raw; img[..., 2] = 0
+        else:
+            img[..., :c["comps"]] = raw
+        px = img.reshape(2, 4, 2, 4, 4).transpose(0, 2, 1, 3, 4).reshape(-1, 64)
+        want = _hex(c["uastc"])
+        assert (R.port_encode_blocks(px, 2) == want).all(), sub
+        if R.have_ref():
+            assert (R.ref_encode_blocks(px, 2) == want).all(), sub
+
+
+@pytest.mark.parametrize("level", [0, 1, 2, 3, 4])
+def test_port_encode_golden_corpus(level):
+    e = np.load(os.path.join(GOLD, "encode_golden.npz"))
+    px = e["pixels"] if level < 4 else e["pixels"][::4]
+    want = e["level%d" % level] if level < 4 else e["level4"][::4]
+    assert (R.port_encode_blocks(px, level) == want).all()
+
+
+def test_port_encode_known_answer():
+    ka = json.load(open(os.path.join(GOLD, "known_answer.json")))
+    px = np.frombuffer(bytes.fromhex(ka["pixels"]), np.uint8).reshape(1, 64)
+    for lvl, v in ka["levels"].items():
+        assert R.port_encode_blocks(px, int(lvl)).tobytes().hex() == v["uastc"]
+
+
+@needs_ref
+def test_port_encode_flag_variants_vs_ref():
+    px = np.concatenate([R.adversarial_blocks(9, 8), R.ref_extract_blocks(R.img_mix(48, 48, 2))])
+    for extra in (8, 16, 64, 128, 256, 512):
+        assert (R.port_encode_blocks(px, 2 | extra) == R.ref_encode_blocks(px, 2 | extra)).all(), extra
