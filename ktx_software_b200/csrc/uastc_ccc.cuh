@@ -19,11 +19,13 @@ struct CccParams {
   uint32_t uber_level, ls_passes;
 };
 
+const uint32_t CCC_NO_SOLUTION = 0xFFFFFFFFu;  // a cell's error is at most 16 * 4 * 255^2 < 2^23
+
 struct CccResults {
-  uint64_t best_err;
+  uint32_t best_err;
   uint32_t lo, hi;            // endpoints as SORTED indices, r | g<<8 | b<<16 | a<<24
   uint32_t astc_lo, astc_hi;  // same endpoints as BISE codes
-  uint8_t sel[16];
+  alignas(16) uint8_t sel[16];
 };
 
 struct Vec4 { float c[4]; };
@@ -96,62 +98,79 @@ UB_FN void set_astc_endpoints(const CccParams& p, CccResults& r) {
   }
 }
 
+// Sum of squared byte differences of two packed texels, and the dot product of two packed texels (unsigned bytes).
+UB_FN uint32_t sqdist4(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  const uint32_t d = __vabsdiffu4(a, b);
+  return __dp4a(d, d, 0u);
+#else
+  uint32_t t = 0;
+  for (uint32_t c = 0; c < 4; c++) { const int d = (int)ch(a, c) - (int)ch(b, c); t += (uint32_t)(d * d); }
+  return t;
+#endif
+}
+UB_FN uint32_t dot4u(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __dp4a(a, b, 0u);
+#else
+  return ch(a, 0) * ch(b, 0) + ch(a, 1) * ch(b, 1) + ch(a, 2) * ch(b, 2) + ch(a, 3) * ch(b, 3);
+#endif
+}
+
 // evaluate_solution (bc7enc.cpp:822): interpolate the palette, project each texel, keep the better of two levels.
-UB_BIG uint64_t evaluate_solution(uint32_t lo, uint32_t hi, const CccParams& p, const uint32_t* px, CccResults& r) {
+// RGB cells run the same code with the alpha byte masked off (the reference's RGB branch ignores alpha throughout).
+UB_BIG uint32_t evaluate_solution(uint32_t lo, uint32_t hi, const CccParams& p, const uint32_t* px, CccResults& r) {
+  const uint32_t amask = p.has_alpha ? 0xFFFFFFFFu : 0x00FFFFFFu;
   uint32_t amin = 0, amax = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++) {
     amin |= sorted_unq(p.range, ch(lo, c)) << (8 * c);
     amax |= sorted_unq(p.range, ch(hi, c)) << (8 * c);
   }
+  amin &= amask; amax &= amask;
   const uint32_t N = p.nw;
-  const uint32_t nc = p.has_alpha ? 4u : 3u;
   uint32_t wc[32];
   wc[0] = amin;
-  for (uint32_t i = 1; i + 1 < N; i++) {
-    const uint32_t w = sel_weight(N, i);
-    uint32_t v = 0;
-    for (uint32_t j = 0; j < nc; j++) v |= interp_linear(ch(amin, j), ch(amax, j), w) << (8 * j);
-    wc[i] = v;
-  }
   wc[N - 1] = amax;
+  if (N > 2) {
+    // astc_interpolate_linear per channel: ((l*257)*(64-w) + (h*257)*w + 32) >> 14 == (base + delta*w) >> 14
+    int base[4], delta[4];
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      const int l = (int)(ch(amin, c) * 257u), h = (int)(ch(amax, c) * 257u);
+      base[c] = l * 64 + 32; delta[c] = h - l;
+    }
+    const uint8_t* wt = weight_table(N);
+#pragma unroll 1
+    for (uint32_t i = 1; i + 1 < N; i++) {
+      const int w = (int)wt[i];
+      wc[i] = (uint32_t)((base[0] + delta[0] * w) >> 14) | ((uint32_t)((base[1] + delta[1] * w) >> 14) << 8) |
+              ((uint32_t)((base[2] + delta[2] * w) >> 14) << 16) | ((uint32_t)((base[3] + delta[3] * w) >> 14) << 24);
+    }
+  }
 
-  const int lr = (int)ch(amin, 0), lg = (int)ch(amin, 1), lb = (int)ch(amin, 2), la = (int)ch(amin, 3);
-  const int dr = (int)ch(amax, 0) - lr, dg = (int)ch(amax, 1) - lg, db = (int)ch(amax, 2) - lb, da = (int)ch(amax, 3) - la;
-
-  uint64_t total = 0;
-  uint8_t tmp[16];
+  uint32_t total = 0;
+  alignas(16) uint8_t tmp[16];
   if (p.force_sel) {
+#pragma unroll 1
     for (uint32_t i = 0; i < p.n; i++) {
       const uint32_t s = p.force_sel[i];
-      total += p.has_alpha ? dist_rgba(wc[s], px[i]) : dist_rgb(wc[s], px[i]);
-      tmp[i] = (uint8_t)s;
-    }
-  } else if (p.has_alpha) {
-    const float f = f_div((float)N, f_add((float)(dr * dr + dg * dg + db * db + da * da), .00000125f));
-    for (uint32_t i = 0; i < p.n; i++) {
-      const uint32_t c = px[i];
-      const int dot = ((int)ch(c, 0) - lr) * dr + ((int)ch(c, 1) - lg) * dg + ((int)ch(c, 2) - lb) * db + ((int)ch(c, 3) - la) * da;
-      int s = (int)f_add(f_mul((float)dot, f), .5f);
-      s = clampi(s, 1, (int)N - 1);
-      const uint32_t e0 = dist_rgba(wc[s - 1], c);
-      uint32_t e1 = dist_rgba(wc[s], c);
-      if (e0 == e1) { if (s - 1 == 0) s = 0; }
-      else if (e1 > e0) { e1 = e0; --s; }
-      total += e1;
+      total += sqdist4(wc[s], px[i] & amask);
       tmp[i] = (uint8_t)s;
     }
   } else {
-    const float f = f_div((float)N, f_add((float)(dr * dr + dg * dg + db * db), .00000125f));
+    // (c - amin) . (amax - amin) == c.amax - c.amin - (amin.amax - amin.amin)
+    const int k0 = (int)dot4u(amin, amax) - (int)dot4u(amin, amin);
+    const float f = f_div((float)N, f_add((float)(int)sqdist4(amax, amin), .00000125f));
+#pragma unroll 1
     for (uint32_t i = 0; i < p.n; i++) {
-      const uint32_t c = px[i];
-      const int dot = ((int)ch(c, 0) - lr) * dr + ((int)ch(c, 1) - lg) * dg + ((int)ch(c, 2) - lb) * db;
+      const uint32_t c = px[i] & amask;
+      const int dot = (int)dot4u(c, amax) - (int)dot4u(c, amin) - k0;
       int s = (int)f_add(f_mul((float)dot, f), .5f);
       s = clampi(s, 1, (int)N - 1);
-      const uint32_t e0 = dist_rgb(wc[s - 1], c);
-      uint32_t e1 = dist_rgb(wc[s], c);
-      if (e0 == e1) { if (s - 1 == 0) s = 0; }
-      else if (e0 < e1) { e1 = e0; --s; }
+      const uint32_t e0 = sqdist4(wc[s - 1], c);
+      uint32_t e1 = sqdist4(wc[s], c);
+      if ((e0 < e1) || (e0 == e1 && s == 1)) { e1 = e0; --s; }
       total += e1;
       tmp[i] = (uint8_t)s;
     }
@@ -159,7 +178,8 @@ UB_BIG uint64_t evaluate_solution(uint32_t lo, uint32_t hi, const CccParams& p, 
   if (total < r.best_err) {
     r.best_err = total;
     r.lo = lo; r.hi = hi;
-    for (uint32_t i = 0; i < p.n; i++) r.sel[i] = tmp[i];
+#pragma unroll
+    for (uint32_t i = 0; i < 4; i++) ((uint32_t*)r.sel)[i] = ((const uint32_t*)tmp)[i];
   }
   return total;
 }
@@ -182,8 +202,8 @@ UB_FN void fix_degenerate(uint32_t& lo, uint32_t& hi, const Vec4& xl, const Vec4
   }
 }
 
-// find_optimal_solution, ASTC-range branch (bc7enc.cpp:1103-1163)
-UB_FN uint64_t find_optimal_solution(Vec4 xl, Vec4 xh, const CccParams& p, const uint32_t* px, CccResults& r) {
+// find_optimal_solution, ASTC-range branch (bc7enc.cpp:1103-1163).  xl/xh in 0..1 units.
+UB_BIG uint32_t find_optimal_solution(Vec4 xl, Vec4 xh, const CccParams& p, const uint32_t* px, CccResults& r) {
 #pragma unroll
   for (int i = 0; i < 4; i++) { xl.c[i] = f_sat(xl.c[i]); xh.c[i] = f_sat(xh.c[i]); }
   const uint32_t rb = UBT(astc_bise_range)[p.range * 3], rt = UBT(astc_bise_range)[p.range * 3 + 1], rq = UBT(astc_bise_range)[p.range * 3 + 2];
@@ -205,51 +225,59 @@ UB_FN uint64_t find_optimal_solution(Vec4 xl, Vec4 xh, const CccParams& p, const
       if (d > 0.0f) degenerate = true;
     }
   if (degenerate) {
-    const int order[4] = {1, 0, 2, 3};
+#pragma unroll 1
     for (int k = 0; k < 4; k++) {
       uint32_t a = tmin, b = tmax;
-      fix_degenerate(a, b, xl, xh, levels - 1, order[k]);
-      if ((r.best_err == ~0ull) || a != r.lo || b != r.hi) evaluate_solution(a, b, p, px, r);
+      fix_degenerate(a, b, xl, xh, levels - 1, (0x3201 >> (4 * k)) & 15);  // flag order 1, 0, 2, 3
+      if ((r.best_err == CCC_NO_SOLUTION) || a != r.lo || b != r.hi) evaluate_solution(a, b, p, px, r);
     }
   } else {
-    if ((r.best_err == ~0ull) || tmin != r.lo || tmax != r.hi) evaluate_solution(tmin, tmax, p, px, r);
+    if ((r.best_err == CCC_NO_SOLUTION) || tmin != r.lo || tmax != r.hi) evaluate_solution(tmin, tmax, p, px, r);
   }
   set_astc_endpoints(p, r);
   return r.best_err;
 }
 
-// compute_least_squares_endpoints_rgb / _rgba (bc7enc.cpp:394-518): normal equations with double accumulators fed by
-// float products.
+// compute_least_squares_endpoints_rgb / _rgba (bc7enc.cpp:394-518): normal equations.  The reference accumulates
+// float products w*c in doubles; w = weight/64 and c <= 255, so every product and every partial sum is an exact
+// integer multiple of 1/64 -- integer accumulation followed by one conversion gives the identical double.
 UB_BIG void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t* px, Vec4& xl, Vec4& xh) {
   const uint32_t* wt = lsq_table(p.nw);
   const uint32_t nc = p.has_alpha ? 4u : 3u;
   double z00 = 0.0, z10 = 0.0, z11 = 0.0;
-  double q00[4] = {0, 0, 0, 0}, t[4] = {0, 0, 0, 0};
+  uint32_t qi[4] = {0, 0, 0, 0}, t_rb = 0, t_ga = 0;
+#pragma unroll 1
   for (uint32_t i = 0; i < p.n; i++) {
     const uint32_t s = sel[i];
     z00 = d_add(z00, (double)bits_to_float(wt[s * 4 + 0]));
     z10 = d_add(z10, (double)bits_to_float(wt[s * 4 + 1]));
     z11 = d_add(z11, (double)bits_to_float(wt[s * 4 + 2]));
-    const float w = bits_to_float(wt[s * 4 + 3]);
-    for (uint32_t c = 0; c < nc; c++) {
-      const uint32_t v = ch(px[i], c);
-      q00[c] = d_add(q00[c], (double)f_mul(w, (float)v));
-      t[c] = d_add(t[c], (double)v);
-    }
+    const uint32_t w = sel_weight(p.nw, s);  // == 64 * wt[s*4+3]
+    const uint32_t c = px[i];
+#pragma unroll
+    for (uint32_t k = 0; k < 4; k++) qi[k] += w * ch(c, k);
+    t_rb += c & 0x00FF00FFu;
+    t_ga += (c >> 8) & 0x00FF00FFu;
   }
+  const uint32_t ti[4] = {t_rb & 0xFFFFu, t_ga & 0xFFFFu, t_rb >> 16, t_ga >> 16};
   const double z01 = z10;
   double det = d_sub(d_mul(z00, z11), d_mul(z01, z10));
   if (det != 0.0) det = d_div(1.0, det);
   const double iz00 = d_mul(z11, det), iz01 = d_mul(-z01, det), iz10 = d_mul(-z10, det), iz11 = d_mul(z00, det);
-  for (uint32_t c = 0; c < nc; c++) {
-    const double q10 = d_sub(t[c], q00[c]);
-    xl.c[c] = (float)d_add(d_mul(iz00, q00[c]), d_mul(iz01, q10));
-    xh.c[c] = (float)d_add(d_mul(iz10, q00[c]), d_mul(iz11, q10));
+#pragma unroll
+  for (uint32_t c = 0; c < 4; c++) {
+    if (c < nc) {
+      const double q00 = d_mul((double)qi[c], 0.015625), q10 = d_sub((double)ti[c], q00);
+      xl.c[c] = (float)d_add(d_mul(iz00, q00), d_mul(iz01, q10));
+      xh.c[c] = (float)d_add(d_mul(iz10, q00), d_mul(iz11, q10));
+    }
   }
   if (!p.has_alpha) { xl.c[3] = 255.0f; xh.c[3] = 255.0f; }
-  for (uint32_t c = 0; c < nc; c++) {
-    if ((xl.c[c] < 0.0f) || (xh.c[c] > 255.0f)) {
+#pragma unroll
+  for (uint32_t c = 0; c < 4; c++) {
+    if (c < nc && ((xl.c[c] < 0.0f) || (xh.c[c] > 255.0f))) {
       uint32_t lo_v = 0xFFFFFFFFu, hi_v = 0;
+#pragma unroll 1
       for (uint32_t i = 0; i < p.n; i++) { lo_v = minu(lo_v, ch(px[i], c)); hi_v = maxu(hi_v, ch(px[i], c)); }
       if (lo_v == hi_v) { xl.c[c] = (float)lo_v; xh.c[c] = (float)hi_v; }
     }
@@ -258,7 +286,7 @@ UB_BIG void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t
 
 // Refit with the given selectors and evaluate: the body repeated all over color_cell_compression.
 // Returns false when the best error reached zero (the reference returns immediately in that case).
-UB_FN bool refit(const CccParams& p, const uint8_t* sel, const uint32_t* px, CccResults& r) {
+UB_BIG bool refit(const CccParams& p, const uint8_t* sel, const uint32_t* px, CccResults& r) {
   Vec4 xl, xh;
   least_squares(p, sel, px, xl, xh);
   const float k = f_div(1.0f, 255.0f);
@@ -277,7 +305,7 @@ UB_FN int single_color_kind(const CccParams& p) {
   if (p.range == 11 && p.nw == 32 && !p.has_alpha) return 4;
   return -1;
 }
-UB_FN uint64_t pack_one_color(int kind, const CccParams& p, const uint32_t* px, uint32_t r, uint32_t g, uint32_t b, uint32_t a,
+UB_BIG uint32_t pack_one_color(int kind, const CccParams& p, const uint32_t* px, uint32_t r, uint32_t g, uint32_t b, uint32_t a,
                               uint32_t& lo, uint32_t& hi, uint32_t& opt_sel) {
   const uint32_t* tab; uint32_t fill_a, w;
   switch (kind) {
@@ -296,25 +324,36 @@ UB_FN uint64_t pack_one_color(int kind, const CccParams& p, const uint32_t* px, 
   const uint32_t ncomp = (kind == 0 || kind == 1) ? 3u : 4u;
   for (uint32_t i = 0; i < ncomp; i++)
     pc |= interp_linear(sorted_unq(p.range, ch(lo, i)), sorted_unq(p.range, ch(hi, i)), w) << (8 * i);
-  uint64_t total = 0;
-  for (uint32_t i = 0; i < p.n; i++) total += (kind == 2) ? dist_rgba(pc, px[i]) : dist_rgb(pc, px[i]);
+  uint32_t total = 0;
+  const uint32_t amask = (kind == 2) ? 0xFFFFFFFFu : 0x00FFFFFFu;
+#pragma unroll 1
+  for (uint32_t i = 0; i < p.n; i++) total += sqdist4(pc & amask, px[i] & amask);
   return total;
 }
 
 // color_cell_compression (bc7enc.cpp:1364-1762).  px: p.n texels, r | g<<8 | b<<16 | a<<24.
-UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, CccResults& r) {
-  r.best_err = ~0ull;
+UB_BIG uint32_t color_cell_compression(const CccParams& p, const uint32_t* px, CccResults& r) {
+  r.best_err = CCC_NO_SOLUTION;
   r.lo = 0; r.hi = 0; r.astc_lo = 0; r.astc_hi = 0;
   const int sck = p.force_sel ? -1 : single_color_kind(p);
 
+  // per-channel sums (the reference adds the texels up in floats; the sums are small integers, so this is exact)
+  uint32_t t_rb = 0, t_ga = 0, diff = 0;
+#pragma unroll 1
+  for (uint32_t i = 0; i < p.n; i++) {
+    const uint32_t c = px[i];
+    t_rb += c & 0x00FF00FFu;
+    t_ga += (c >> 8) & 0x00FF00FFu;
+    diff |= c ^ px[0];
+  }
+
   if (sck >= 0) {
-    bool solid = true;
     const uint32_t mask = (sck == 2) ? 0xFFFFFFFFu : 0x00FFFFFFu;
-    for (uint32_t i = 1; i < p.n; i++) if ((px[i] ^ px[0]) & mask) { solid = false; break; }
-    if (solid) {
+    if (!(diff & mask)) {
       uint32_t os;
-      const uint64_t e = pack_one_color(sck, p, px, ch(px[0], 0), ch(px[0], 1), ch(px[0], 2), ch(px[0], 3), r.lo, r.hi, os);
-      for (uint32_t i = 0; i < p.n; i++) r.sel[i] = (uint8_t)os;
+      const uint32_t e = pack_one_color(sck, p, px, ch(px[0], 0), ch(px[0], 1), ch(px[0], 2), ch(px[0], 3), r.lo, r.hi, os);
+#pragma unroll
+      for (uint32_t i = 0; i < 4; i++) ((uint32_t*)r.sel)[i] = os * 0x01010101u;
       r.best_err = e;
       set_astc_endpoints(p, r);
       return e;
@@ -322,10 +361,7 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
   }
 
   // mean colour
-  Vec4 mean = {{0, 0, 0, 0}};
-  for (uint32_t i = 0; i < p.n; i++)
-#pragma unroll
-    for (uint32_t c = 0; c < 4; c++) mean.c[c] = f_add(mean.c[c], (float)ch(px[i], c));
+  Vec4 mean = {{(float)(t_rb & 0xFFFFu), (float)(t_ga & 0xFFFFu), (float)(t_rb >> 16), (float)(t_ga >> 16)}};
   Vec4 mean_scaled;
   {
     const float k0 = f_div(1.0f, (float)p.n), k1 = f_div(1.0f, f_mul((float)p.n, 255.0f));
@@ -335,6 +371,7 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
 
   Vec4 axis = {{0, 0, 0, 0}};
   if (p.has_alpha) {
+#pragma unroll 1
     for (uint32_t i = 0; i < p.n; i++) {
       Vec4 col;
 #pragma unroll
@@ -352,6 +389,7 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
     f_normalize4(axis);
   } else {
     float cov[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll 1
     for (uint32_t i = 0; i < p.n; i++) {
       const float cr = f_sub((float)ch(px[i], 0), mean_scaled.c[0]);
       const float cg = f_sub((float)ch(px[i], 1), mean_scaled.c[1]);
@@ -360,6 +398,7 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
       cov[3] = f_add(cov[3], f_mul(cg, cg)); cov[4] = f_add(cov[4], f_mul(cg, cb)); cov[5] = f_add(cov[5], f_mul(cb, cb));
     }
     float xr = .9f, xg = 1.0f, xb = .7f;
+#pragma unroll 1
     for (uint32_t it = 0; it < 3; it++) {
       float rr = f_add(f_add(f_mul(xr, cov[0]), f_mul(xg, cov[1])), f_mul(xb, cov[2]));
       float gg = f_add(f_add(f_mul(xr, cov[1]), f_mul(xg, cov[3])), f_mul(xb, cov[4]));
@@ -382,6 +421,7 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
   }
 
   float l = 1e+9f, h = -1e+9f;
+#pragma unroll 1
   for (uint32_t i = 0; i < p.n; i++) {
     Vec4 q;
 #pragma unroll
@@ -405,34 +445,42 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
   }
 
   if (!find_optimal_solution(minc, maxc, p, px, r)) return 0;
+#pragma unroll 1
   for (uint32_t i = 0; i < p.ls_passes; i++)
     if (!refit(p, r.sel, px, r)) return 0;
 
   if (!p.force_sel && p.uber_level > 0) {
-    uint8_t st[16], s1[16];
+    alignas(16) uint8_t st[16], s1[16];
     uint32_t min_sel = 256, max_sel = 0;
+#pragma unroll 1
     for (uint32_t i = 0; i < p.n; i++) { st[i] = r.sel[i]; min_sel = minu(min_sel, st[i]); max_sel = maxu(max_sel, st[i]); }
     const int max_selector = (int)p.nw - 1;
-    for (uint32_t i = 0; i < p.n; i++) { uint32_t s = st[i]; if (s == min_sel && s < p.nw - 1) s++; s1[i] = (uint8_t)s; }
-    if (!refit(p, s1, px, r)) return 0;
-    for (uint32_t i = 0; i < p.n; i++) { uint32_t s = st[i]; if (s == max_sel && s > 0) s--; s1[i] = (uint8_t)s; }
-    if (!refit(p, s1, px, r)) return 0;
-    for (uint32_t i = 0; i < p.n; i++) {
-      uint32_t s = st[i];
-      if (s == min_sel && s < p.nw - 1) s++; else if (s == max_sel && s > 0) s--;
-      s1[i] = (uint8_t)s;
+    // three perturbations: raise the lowest selector, lower the highest, both (bc7enc.cpp:1573-1641)
+#pragma unroll 1
+    for (uint32_t trial = 1; trial <= 3; trial++) {
+#pragma unroll 1
+      for (uint32_t i = 0; i < p.n; i++) {
+        uint32_t s = st[i];
+        if ((trial & 1u) && s == min_sel && s < p.nw - 1) s++;
+        else if ((trial & 2u) && s == max_sel && s > 0) s--;
+        s1[i] = (uint8_t)s;
+      }
+      if (!refit(p, s1, px, r)) return 0;
     }
-    if (!refit(p, s1, px, r)) return 0;
 
     const uint32_t thresh = (p.n * 56) >> 4;
     if (p.uber_level >= 2 && r.best_err > thresh) {
       const int Q = (p.uber_level >= 4) ? (int)p.uber_level - 2 : 1;
+#pragma unroll 1
       for (int ly = -Q; ly <= 1; ly++)
+#pragma unroll 1
         for (int hy = max_selector - 1; hy <= max_selector + Q; hy++) {
           if (ly == 0 && hy == max_selector) continue;
+          const float den = f_sub((float)hy, (float)ly);
+#pragma unroll 1
           for (uint32_t i = 0; i < p.n; i++) {
             const float num = f_mul((float)max_selector, f_sub((float)st[i], (float)ly));
-            float v = floorf(f_add(f_div(num, f_sub((float)hy, (float)ly)), .5f));
+            float v = floorf(f_add(f_div(num, den), .5f));
             if (v < 0) v = 0; else if (v > (float)max_selector) v = (float)max_selector;
             s1[i] = (uint8_t)v;
           }
@@ -445,10 +493,11 @@ UB_BIG uint64_t color_cell_compression(const CccParams& p, const uint32_t* px, C
     const uint32_t mr = (uint32_t)(int)f_add(.5f, f_mul(mean.c[0], 255.0f)), mg = (uint32_t)(int)f_add(.5f, f_mul(mean.c[1], 255.0f));
     const uint32_t mb = (uint32_t)(int)f_add(.5f, f_mul(mean.c[2], 255.0f)), ma = (uint32_t)(int)f_add(.5f, f_mul(mean.c[3], 255.0f));
     uint32_t lo, hi, os;
-    const uint64_t e = pack_one_color(sck, p, px, mr, mg, mb, ma, lo, hi, os);
+    const uint32_t e = pack_one_color(sck, p, px, mr, mg, mb, ma, lo, hi, os);
     if (e < r.best_err) {
       r.best_err = e; r.lo = lo; r.hi = hi;
-      for (uint32_t i = 0; i < p.n; i++) r.sel[i] = (uint8_t)os;
+#pragma unroll
+      for (uint32_t i = 0; i < 4; i++) ((uint32_t*)r.sel)[i] = os * 0x01010101u;
       set_astc_endpoints(p, r);
     }
   }

@@ -9,7 +9,9 @@ import refutil as R
 K.init()
 size = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 levels = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else [0, 1, 2, 3]
-for name, img in (("mix", R.img_mix(size, size, 1)), ("noise", R.img_noise(size, size, 1)), ("smooth", R.img_smooth(size, size, 1))):
+kinds = os.environ.get("PROBE_KINDS", "mix,noise,smooth").split(",")
+mk = {"mix": R.img_mix, "noise": R.img_noise, "smooth": R.img_smooth}
+for name, img in ((k, mk[k](size, size, 1)) for k in kinds):
     h, w = img.shape[:2]
     px = torch.from_numpy(img.reshape(h // 4, 4, w // 4, 4, 4).transpose(0, 2, 1, 3, 4).reshape(-1, 64).copy()).cuda()
     n = px.shape[0]
