@@ -197,6 +197,23 @@ UB_BIG uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_
   return n;
 }
 
+// UASTC and transcoded-BC7 squared error of one candidate against the source texels (basisu_uastc_enc.cpp:3409-3456).
+UB_BIG void score_candidate(const uint32_t* px, const Candidate& c, bool has_alpha, bool is_la, uint64_t& ue, uint64_t& be) {
+  uint32_t dec[16];
+  decode_uastc_pixels(c, dec);
+  uint64_t u_rgb, u_rgba, u_la, b_rgb, b_rgba, b_la;
+  block_error(px, dec, u_rgb, u_rgba, u_la);
+  UnpackedUastc u;
+  candidate_to_unpacked(c, u);
+  Bc7Build bb;
+  uastc_to_bc7_build(u, bb);
+  const Bits128 bc7 = bc7_pack(bb);
+  decode_bc7_pixels(bc7, dec);
+  block_error(px, dec, b_rgb, b_rgba, b_la);
+  ue = is_la ? u_la : (has_alpha ? u_rgba : u_rgb);
+  be = is_la ? b_la : (has_alpha ? b_rgba : b_rgb);
+}
+
 // Candidate scoring + selection (basisu_uastc_enc.cpp:3389-3549).  Returns the winning index.
 UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uint32_t n, bool has_alpha, bool is_la, uint32_t flags,
                                 uint64_t* overall, float* uerr_f) {
@@ -206,20 +223,10 @@ UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uin
   const uint32_t bc7_w = favor_bc7 ? 100u : (favor_uastc ? 0u : 50u);
   const uint32_t uastc_w = favor_bc7 ? 0u : 100u;
   double best_uerr = (double)1e+20f;
+#pragma unroll 1
   for (uint32_t i = 0; i < n; i++) {
-    uint32_t dec[16], dec7[16];
-    decode_uastc_pixels(cands[i], dec);
-    uint64_t u_rgb, u_rgba, u_la, b_rgb, b_rgba, b_la;
-    block_error(px, dec, u_rgb, u_rgba, u_la);
-    UnpackedUastc u;
-    candidate_to_unpacked(cands[i], u);
-    Bc7Build bb;
-    uastc_to_bc7_build(u, bb);
-    const Bits128 bc7 = bc7_pack(bb);
-    decode_bc7_pixels(bc7, dec7);
-    block_error(px, dec7, b_rgb, b_rgba, b_la);
-    const uint64_t ue = is_la ? u_la : (has_alpha ? u_rgba : u_rgb);
-    const uint64_t be = is_la ? b_la : (has_alpha ? b_rgba : b_rgb);
+    uint64_t ue, be;
+    score_candidate(px, cands[i], has_alpha, is_la, ue, be);
     overall[i] = (be * bc7_w) / 100 + (ue * uastc_w) / 100;
     if (!overall[i]) return i;
     uerr_f[i] = f_sqrt(u64_to_float(ue));
@@ -228,8 +235,8 @@ UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uin
   const bool favor_simpler = (flags & 512u) != 0;  // cPackUASTCFavorSimplerModes (basisu_uastc_enc.h:62)
   uint64_t best_err = ~0ull;
   uint32_t best = 0;
-  bool found = false;
   const bool all = (best_uerr == 0.0) || favor_bc7;
+#pragma unroll 1
   for (uint32_t i = 0; i < n; i++) {
     if (!all) {
       const double delta = d_div((double)uerr_f[i], best_uerr);
@@ -237,9 +244,8 @@ UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uin
     }
     const float wgt = (favor_simpler && (cands[i].mode == 0 || cands[i].mode == 10)) ? .8f : 1.0f;
     const uint64_t w = (uint64_t)f_mul(u64_to_float(overall[i]), wgt);
-    if (w < best_err) { best_err = w; best = i; found = true; if (!best_err) break; }
+    if (w < best_err) { best_err = w; best = i; if (!best_err) break; }
   }
-  (void)found;
   return best;
 }
 

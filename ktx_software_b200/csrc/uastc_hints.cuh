@@ -74,6 +74,7 @@ UB_FN int gray_distance2(uint32_t c, int r, int g, int b) {
 
 UB_FN bool etc1_estimate_flipped(const uint32_t* px) {
   int upper[3], lower[3], left[3], right[3];
+#pragma unroll
   for (uint32_t c = 0; c < 3; c++) {
     int s00 = 0, s10 = 0, s01 = 0, s11 = 0;
     for (uint32_t y = 0; y < 2; y++)
@@ -84,7 +85,9 @@ UB_FN bool etc1_estimate_flipped(const uint32_t* px) {
     upper[c] = (s00 + s10 + 4) / 8; lower[c] = (s01 + s11 + 4) / 8; left[c] = (s00 + s01 + 4) / 8; right[c] = (s10 + s11 + 4) / 8;
   }
   int ug = 0, lg = 0, leg = 0, rg = 0;
+#pragma unroll 1
   for (uint32_t i = 0; i < 4; i++)
+#pragma unroll 1
     for (uint32_t j = 0; j < 2; j++) {
       ug += gray_distance2(px[i + j * 4], upper[0], upper[1], upper[2]);
       lg += gray_distance2(px[i + (2 + j) * 4], lower[0], lower[1], lower[2]);
@@ -94,52 +97,56 @@ UB_FN bool etc1_estimate_flipped(const uint32_t* px) {
   return (ug + lg) < (leg + rg);
 }
 
+// apply_etc1_bias (XC:16182) as a table: the per-channel delta of every bias mode, [bias][sub-block][channel].
+UB_TABLE(int8_t, etc1_bias_delta, 192) = {
+  -1,-1,-1,-1,-1,-1,0,-1,-1,0,-1,-1,-1,0,0,0,0,0,-1,0,-1,-1,0,-1,0,0,-1,0,0,-1,0,-1,0,0,0,0,0,0,-1,0,0,0,1,0,0,0,0,0,
+  0,0,0,0,0,1,-1,-1,0,-1,-1,0,-2,-2,-2,-2,-2,-2,0,1,0,0,0,0,-1,0,0,-1,0,0,0,0,0,0,0,0,1,0,0,1,0,0,0,0,1,0,0,0,
+  0,1,0,0,1,0,1,1,0,1,1,0,0,0,0,-1,0,0,0,0,0,0,-1,0,0,0,0,0,0,-1,0,0,0,1,0,0,0,0,1,0,0,1,1,0,1,1,0,1,
+  0,0,0,0,1,0,0,1,1,0,1,1,1,1,1,1,1,1,-1,-1,-1,0,0,0,1,1,1,-1,-1,-1,0,0,0,1,1,1,0,0,0,-1,-1,-1,1,1,1,0,0,0};
+UB_TABLE(uint8_t, etc1_sorted_bias, 32) = {13, 0, 22, 29, 27, 12, 26, 9, 30, 31, 8, 10, 25, 2, 23, 5, 15, 7, 3, 11, 6, 17, 28, 18, 1, 19, 20, 21, 24, 4, 14, 16};
+
 UB_FN int etc1_bias_comp(int v, uint32_t bias, int limit, uint32_t subblock, uint32_t c) {  // apply_etc1_bias, one channel
-  int delta;
-  switch (bias) {
-    case 2: delta = subblock ? 0 : ((c == 0) ? -1 : 0); break;
-    case 5: delta = subblock ? 0 : ((c == 1) ? -1 : 0); break;
-    case 6: delta = subblock ? 0 : ((c == 2) ? -1 : 0); break;
-    case 7: delta = subblock ? 0 : ((c == 0) ? 1 : 0); break;
-    case 11: delta = subblock ? 0 : ((c == 1) ? 1 : 0); break;
-    case 15: delta = subblock ? 0 : ((c == 2) ? 1 : 0); break;
-    case 18: delta = subblock ? ((c == 0) ? -1 : 0) : 0; break;
-    case 19: delta = subblock ? ((c == 1) ? -1 : 0) : 0; break;
-    case 20: delta = subblock ? ((c == 2) ? -1 : 0) : 0; break;
-    case 21: delta = subblock ? ((c == 0) ? 1 : 0) : 0; break;
-    case 24: delta = subblock ? ((c == 1) ? 1 : 0) : 0; break;
-    case 8: delta = subblock ? ((c == 2) ? 1 : 0) : 0; break;
-    case 10: delta = -2; break;
-    case 27: delta = subblock ? 0 : -1; break;
-    case 28: delta = subblock ? -1 : 1; break;
-    case 29: delta = subblock ? 1 : 0; break;
-    case 30: delta = subblock ? -1 : 0; break;
-    case 31: delta = subblock ? 0 : 1; break;
-    default: { const int divs = (c == 0) ? 1 : (c == 1 ? 3 : 9); delta = (int)((bias / (uint32_t)divs) % 3u) - 1; break; }
-  }
+  const int delta = UBT(etc1_bias_delta)[bias * 6 + subblock * 3 + c];
   if (v == 0) { if (delta == -2) v += 3; else v += delta + 1; }
   else if (v == limit) v += (delta - 1);
   else { v += delta; if (v < 0 || v > limit) v = (v - delta) - delta; }
   return v;
 }
 
-// the four decoded colours of one ETC1 sub-block as YCbCr
-UB_FN void etc1_subblock_colors(const int* base8, uint32_t inten, YCbCr* out) {
-  for (uint32_t s = 0; s < 4; s++) {
-    const int m = UBT(etc1_inten)[inten * 4 + s];
-    out[s] = to_ycbcr((uint32_t)clamp255(base8[0] + m) | ((uint32_t)clamp255(base8[1] + m) << 8) | ((uint32_t)clamp255(base8[2] + m) << 16));
-  }
-}
 // texel index j (0..7) of sub-block `subset` under `flip`
 UB_FN uint32_t etc1_texel(uint32_t flip, uint32_t subset, uint32_t j) {
   return flip ? ((subset * 2 + (j >> 2)) * 4 + (j & 3u)) : ((j >> 1) * 4 + subset * 2 + (j & 1u));
+}
+
+// YCbCr of a texel, luma pre-doubled: the metric is 4*dy^2 + dcr^2 + dcb^2 == (2dy)^2 + dcr^2 + dcb^2 (color_diff :2649)
+struct Ycc2 { int y2, cb, cr; };
+UB_FN Ycc2 to_ycc2(uint32_t c) {
+  const YCbCr t = to_ycbcr(c);
+  Ycc2 o; o.y2 = t.y * 2; o.cb = t.cb; o.cr = t.cr;
+  return o;
+}
+UB_FN uint64_t sq64(int d) { return (uint64_t)((int64_t)d * (int64_t)d); }
+UB_FN uint64_t chroma_d(const Ycc2& a, const Ycc2& b) { return sq64(a.cr - b.cr) + sq64(a.cb - b.cb); }
+
+// The four colours of one ETC1 sub-block for intensity table `inten`.  Adding the same modifier to r, g and b moves only
+// luma (54+183+19 == 256), so entries that do not clamp share the base colour's chroma: bit k of the return value is set
+// only when entry k clamped in some channel and needs its own chroma term.
+UB_FN uint32_t etc1_subblock_ycc(const int* base8, uint32_t inten, Ycc2* out) {
+  uint32_t clamped = 0;
+#pragma unroll
+  for (uint32_t k = 0; k < 4; k++) {
+    const int m = UBT(etc1_inten)[inten * 4 + k];
+    const int r = base8[0] + m, g = base8[1] + m, b = base8[2] + m;
+    if (((uint32_t)r | (uint32_t)g | (uint32_t)b) > 255u) clamped |= 1u << k;
+    out[k] = to_ycc2((uint32_t)clamp255(r) | ((uint32_t)clamp255(g) << 8) | ((uint32_t)clamp255(b) << 16));
+  }
+  return clamped;
 }
 
 UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
                               uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
   const bool faster = (flags & 64u) != 0, fastest = (flags & 128u) != 0;
   const bool has_bias = UBT(uastc_mode_has_etc1_bias)[mode] != 0;
-  const uint8_t sorted_bias[32] = {13, 0, 22, 29, 27, 12, 26, 9, 30, 31, 8, 10, 25, 2, 23, 5, 15, 7, 3, 11, 6, 17, 28, 18, 1, 19, 20, 21, 24, 4, 14, 16};
   uint32_t last_bias = 1;
   bool use_table = false;
   const bool flip_estimate = (level <= 1) || faster || fastest;
@@ -153,91 +160,128 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
       default: last_bias = 32; break;
     }
   }
-  YCbCr src_y[16], dec_y[16];
-  for (uint32_t i = 0; i < 16; i++) { src_y[i] = to_ycbcr(px[i]); dec_y[i] = to_ycbcr(dec[i]); }
+  Ycc2 src_y[16], dec_y[16];
+#pragma unroll 1
+  for (uint32_t i = 0; i < 16; i++) { src_y[i] = to_ycc2(px[i]); dec_y[i] = to_ycc2(dec[i]); }
   uint32_t first_flip = 0, last_flip = 2, last_individ = 2;
   if (flags & 256u) { last_flip = 1; last_individ = 1; }
   else if (flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
 
   uint64_t best_err = ~0ull;
   o_flip = 0; o_diff = 0; o_i0 = 0; o_i1 = 0; o_bias = 0;
-  for (uint32_t flip = first_flip; flip < last_flip; flip++)
+#pragma unroll 1
+  for (uint32_t flip = first_flip; flip < last_flip; flip++) {
+    // per sub-block statistics of the decoded texels: channel sums, min, max
+    uint32_t avg[2][3];
+    int mn[2][3], mx[2][3];
+#pragma unroll
+    for (uint32_t s = 0; s < 2; s++) {
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) { avg[s][c] = 0; mn[s][c] = 255; mx[s][c] = 0; }
+#pragma unroll 1
+      for (uint32_t j = 0; j < 8; j++) {
+        const uint32_t p = dec[etc1_texel(flip, s, j)];
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+          const int v = (int)ch(p, c);
+          avg[s][c] += (uint32_t)v;
+          mn[s][c] = v < mn[s][c] ? v : mn[s][c];
+          mx[s][c] = v > mx[s][c] ? v : mx[s][c];
+        }
+      }
+    }
+#pragma unroll 1
     for (uint32_t individ = 0; individ < last_individ; individ++) {
       const uint32_t mul = individ ? 15u : 31u;
-      int unb[2][3], mn[2][3], mx[2][3];
-      for (uint32_t s = 0; s < 2; s++) {
-        uint32_t avg[3] = {0, 0, 0};
-        for (uint32_t c = 0; c < 3; c++) { mn[s][c] = 255; mx[s][c] = 0; }
-        for (uint32_t j = 0; j < 8; j++) {
-          const uint32_t p = dec[etc1_texel(flip, s, j)];
-          for (uint32_t c = 0; c < 3; c++) {
-            const int v = (int)ch(p, c);
-            avg[c] += (uint32_t)v;
-            if (v < mn[s][c]) mn[s][c] = v;
-            if (v > mx[s][c]) mx[s][c] = v;
-          }
-        }
-        for (uint32_t c = 0; c < 3; c++) unb[s][c] = (int)((avg[c] * mul + 1020u) / (8u * 255u));
-      }
+      int unb[2][3];
+#pragma unroll
+      for (uint32_t s = 0; s < 2; s++)
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) unb[s][c] = (int)((avg[s][c] * mul + 1020u) / (8u * 255u));
+#pragma unroll 1
       for (uint32_t bi = 0; bi < last_bias; bi++) {
-        const uint32_t bias = use_table ? sorted_bias[bi] : bi;
+        const uint32_t bias = use_table ? UBT(etc1_sorted_bias)[bi] : bi;
         int base8[2][3];
-        {
-          int bc[2][3];
-          for (uint32_t s = 0; s < 2; s++)
-            for (uint32_t c = 0; c < 3; c++) bc[s][c] = has_bias ? etc1_bias_comp(unb[s][c], bias, (int)mul, s, c) : unb[s][c];
-          for (uint32_t c = 0; c < 3; c++) {
-            if (individ) {
-              base8[0][c] = (bc[0][c] << 4) | bc[0][c];
-              base8[1][c] = (bc[1][c] << 4) | bc[1][c];
-            } else {
-              const int d = clampi(bc[1][c] - bc[0][c], -4, 3);
-              const int c1 = clampi(bc[0][c] + d, 0, 31);
-              base8[0][c] = (bc[0][c] << 3) | (bc[0][c] >> 2);
-              base8[1][c] = (c1 << 3) | (c1 >> 2);
-            }
+#pragma unroll
+        for (uint32_t c = 0; c < 3; c++) {
+          const int b0 = has_bias ? etc1_bias_comp(unb[0][c], bias, (int)mul, 0, c) : unb[0][c];
+          const int b1 = has_bias ? etc1_bias_comp(unb[1][c], bias, (int)mul, 1, c) : unb[1][c];
+          if (individ) {
+            base8[0][c] = (b0 << 4) | b0;
+            base8[1][c] = (b1 << 4) | b1;
+          } else {
+            const int d = clampi(b1 - b0, -4, 3);
+            const int c1 = clampi(b0 + d, 0, 31);
+            base8[0][c] = (b0 << 3) | (b0 >> 2);
+            base8[1][c] = (c1 << 3) | (c1 >> 2);
           }
         }
         uint32_t best_inten[2] = {0, 0};
+        uint64_t err = 0;
+#pragma unroll 1
         for (uint32_t s = 0; s < 2; s++) {
+          const int* b8 = s ? base8[1] : base8[0];
           int range = 0;
+#pragma unroll
           for (uint32_t c = 0; c < 3; c++) {
-            int a = mx[s][c] - base8[s][c]; if (a < 0) a = -a;
-            int b = base8[s][c] - mn[s][c]; if (b < 0) b = -b;
+            int a = mx[s][c] - b8[c]; if (a < 0) a = -a;
+            int b = b8[c] - mn[s][c]; if (b < 0) b = -b;
             if (a > range) range = a;
             if (b > range) range = b;
           }
           const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
+          // chroma distance of every texel to the (unclamped) base colour, shared by all table entries that do not clamp
+          const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
+          uint64_t kj[8];
+#pragma unroll 1
+          for (uint32_t j = 0; j < 8; j++) kj[j] = chroma_d(by, dec_y[etc1_texel(flip, s, j)]);
           uint64_t best_sub = ~0ull;
+          uint32_t bi_s = 0;
+#pragma unroll 1
           for (uint32_t it = 0; it < limit; it++) {
-            YCbCr tab[4];
-            etc1_subblock_colors(base8[s], it, tab);
+            Ycc2 tab[4];
+            const uint32_t clamped = etc1_subblock_ycc(b8, it, tab);
             uint64_t total = 0;
+#pragma unroll 1
             for (uint32_t j = 0; j < 8; j++) {
-              const YCbCr& c = dec_y[etc1_texel(flip, s, j)];
-              uint64_t m = ycc_diff(tab[0], c);
-              for (uint32_t k = 1; k < 4; k++) { const uint64_t e = ycc_diff(tab[k], c); if (e < m) m = e; }
+              const Ycc2 c = dec_y[etc1_texel(flip, s, j)];
+              uint64_t m = ~0ull;
+#pragma unroll
+              for (uint32_t k = 0; k < 4; k++) {
+                uint64_t e = sq64(tab[k].y2 - c.y2);
+                if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
+                m = e < m ? e : m;
+              }
               total += m;
             }
             // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
             if (!flip && total >= best_sub) break;
-            if (total < best_sub) { best_sub = total; best_inten[s] = it; }
+            if (total < best_sub) { best_sub = total; bi_s = it; }
           }
-        }
-        uint64_t err = 0;
-        for (uint32_t s = 0; s < 2; s++) {
-          YCbCr tab[4];
-          etc1_subblock_colors(base8[s], best_inten[s], tab);
+          best_inten[s] = bi_s;
+          // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones)
+          Ycc2 tab[4];
+          const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+#pragma unroll 1
           for (uint32_t j = 0; j < 8; j++) {
             const uint32_t t = etc1_texel(flip, s, j);
-            uint64_t m = ycc_diff(tab[0], dec_y[t]) << 2;
-            for (uint32_t k = 1; k < 4; k++) { const uint64_t e = (ycc_diff(tab[k], dec_y[t]) << 2) + k; if (e < m) m = e; }
-            err += ycc_diff(src_y[t], tab[(uint32_t)m & 3u]);
+            const Ycc2 c = dec_y[t];
+            uint64_t m = ~0ull;
+            uint32_t bk = 0;
+#pragma unroll
+            for (uint32_t k = 0; k < 4; k++) {
+              uint64_t e = sq64(tab[k].y2 - c.y2);
+              if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
+              if (e < m) { m = e; bk = k; }
+            }
+            const Ycc2 sy = src_y[t];
+            err += sq64(sy.y2 - tab[bk].y2) + chroma_d(sy, tab[bk]);
           }
         }
         if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
       }
     }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
