@@ -95,6 +95,13 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
 int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64_t n_blocks, uint32_t pack_flags,
                                  void* stream);
 
+/* Device-resident image variant: d_rgba = one RGBA8 image in device memory (row_pitch_bytes 0 = width*4); the 4x4
+ * gather with edge replication (image::extract_block_clamped, ENC/basisu_enc.h:3081) happens inside the kernel.
+ * d_out = ceil(w/4)*ceil(h/4) x 16 B.  d_any_alpha (device uint32_t*, may be NULL) is OR-ed with 1 when a texel has
+ * alpha < 255.  Asynchronous when a stream is given. */
+int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
+                                uint32_t pack_flags, void* stream, uint32_t* d_any_alpha);
+
 #ifdef __cplusplus
 }
 #endif

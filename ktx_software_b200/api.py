@@ -9,7 +9,8 @@ TTF_BC7_RGBA = 6        # ktx_transcode_fmt_e KTX_TTF_BC7_RGBA (lib/include/ktx.
 TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
-                    "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev"]
+                    "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
+                    "b200_uastc_encode_image_dev"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -54,6 +55,8 @@ def lib():
         l.b200_uastc_encode.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(UastcParams),
                                         ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
+        l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
+                                                  ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         _lib = l
     return _lib
 
@@ -99,6 +102,11 @@ def transcode_dev(target, d_src, d_dst, n_blocks, stream=0, d_first_bad=0):
 def encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream=0):
     """Device-pointer encode of n_blocks pre-gathered 4x4 RGBA8 blocks (64 B each) -> 16 B UASTC blocks."""
     _check(lib().b200_uastc_encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream or None))
+
+
+def encode_image_dev(d_rgba, width, height, d_out, pack_flags, stream=0, row_pitch_bytes=0, d_any_alpha=0):
+    """Device-pointer encode of one RGBA8 image resident in HBM; the 4x4 gather is fused into the kernel."""
+    _check(lib().b200_uastc_encode_image_dev(d_rgba, width, height, row_pitch_bytes, d_out, pack_flags, stream or None, d_any_alpha or None))
 
 
 def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale=0.0, smooth_std_dev=0.0, total_jobs=0):

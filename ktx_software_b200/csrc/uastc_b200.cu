@@ -339,6 +339,27 @@ int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64
   return B200_OK;
 }
 
+int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
+                                uint32_t pack_flags, void* stream, uint32_t* d_any_alpha) {
+  if (!d_rgba || !d_out || !width || !height) return fail(B200_E_INVALID_VALUE, "bad image");
+  const uint32_t pitch = row_pitch_bytes ? row_pitch_bytes : width * 4;
+  if (pitch < width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
+  const uint32_t bx = (width + 3) / 4, by = (height + 3) / 4;
+  const uint64_t n = (uint64_t)bx * by;
+  if ((pack_flags & 7u) >= 4u)
+    k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
+  else
+    k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
+  g_launches++;
+  CU(cudaGetLastError());
+  if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
 int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
                       uint32_t* out_any_alpha) {
   if (out_any_alpha) *out_any_alpha = 0;
@@ -354,19 +375,33 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   if (rc) return rc;
   if (!n_images) return B200_OK;
 
-  // Two staging slots so image i+1 uploads while image i encodes and image i-1 downloads.
-  const int SLOTS = 2;
+  // Slab list: every image is cut into runs of whole block rows (contiguous in the RGBA source and in the UASTC
+  // output) of at most SLAB_BYTES of input, so upload, encode and download of neighbouring slabs overlap on three
+  // streams through a ring of staging buffers.
+  const size_t SLAB_BYTES = 32u << 20;
+  struct Slab { uint32_t img, y0, rows_px; size_t in_bytes, out_off, out_bytes; };
+  std::vector<Slab> slabs;
   size_t max_in = 0, max_out = 0;
   for (uint32_t i = 0; i < n_images; i++) {
-    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * 4;
-    if (pitch < (size_t)images[i].width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
-    max_in = std::max(max_in, pitch * images[i].height);
-    max_out = std::max(max_out, (size_t)((images[i].width + 3) / 4) * ((images[i].height + 3) / 4) * 16);
+    const b200_image& im = images[i];
+    const size_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : (size_t)im.width * 4;
+    if (pitch < (size_t)im.width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
+    uint32_t rows_per = (uint32_t)std::max<size_t>(1, SLAB_BYTES / (pitch * 4));
+    for (uint32_t r0 = 0; r0 < by; r0 += rows_per) {
+      const uint32_t r1 = std::min(by, r0 + rows_per);
+      const uint32_t y0 = r0 * 4, y1 = std::min(im.height, r1 * 4);
+      Slab sl{i, y0, y1 - y0, pitch * (y1 - y0), (size_t)r0 * bx * 16, (size_t)(r1 - r0) * bx * 16};
+      max_in = std::max(max_in, sl.in_bytes);
+      max_out = std::max(max_out, sl.out_bytes);
+      slabs.push_back(sl);
+    }
   }
+  const int SLOTS = 3;
   uint8_t* d_in[SLOTS] = {0}; uint8_t* d_out[SLOTS] = {0};
   unsigned int* d_alpha = nullptr;
   cudaEvent_t ev_in[SLOTS], ev_k[SLOTS], ev_out[SLOTS];
-  const int nslots = (int)std::min<uint32_t>(SLOTS, n_images);
+  const int nslots = (int)std::min<size_t>(SLOTS, slabs.size());
   auto cleanup = [&]() {
     for (int i = 0; i < SLOTS; i++) { if (d_in[i]) cudaFree(d_in[i]); if (d_out[i]) cudaFree(d_out[i]); }
     if (d_alpha) cudaFree(d_alpha);
@@ -383,23 +418,24 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   cudaMemsetAsync(d_alpha, 0, sizeof(unsigned int), s_k);
   const bool full = (params->pack_flags & 7u) >= 4u;
   cudaError_t err = cudaSuccess;
-  for (uint32_t i = 0; i < n_images && err == cudaSuccess; i++) {
-    const b200_image& im = images[i];
-    const int b = (int)(i % nslots);
+  for (size_t k = 0; k < slabs.size() && err == cudaSuccess; k++) {
+    const Slab& sl = slabs[k];
+    const b200_image& im = images[sl.img];
+    const int b = (int)(k % nslots);
     const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
-    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
-    if (i >= (uint32_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
-    err = cudaMemcpyAsync(d_in[b], im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, s_in);
+    const uint32_t bx = (im.width + 3) / 4, by = (sl.rows_px + 3) / 4;
+    if (k >= (size_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
+    err = cudaMemcpyAsync(d_in[b], im.rgba + (size_t)sl.y0 * pitch, sl.in_bytes, cudaMemcpyHostToDevice, s_in);
     if (err != cudaSuccess) break;
     cudaEventRecord(ev_in[b], s_in);
     cudaStreamWaitEvent(s_k, ev_in[b], 0);
     const uint64_t n = (uint64_t)bx * by;
-    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, im.height, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
-    else k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, im.height, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    else k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
     g_launches++;
     cudaEventRecord(ev_k[b], s_k);
     cudaStreamWaitEvent(s_out, ev_k[b], 0);
-    err = cudaMemcpyAsync(out_blocks[i], d_out[b], n * 16, cudaMemcpyDeviceToHost, s_out);
+    err = cudaMemcpyAsync(out_blocks[sl.img] + sl.out_off, d_out[b], sl.out_bytes, cudaMemcpyDeviceToHost, s_out);
     cudaEventRecord(ev_out[b], s_out);
   }
   unsigned int h_alpha = 0;

@@ -63,13 +63,6 @@ UB_FN const uint32_t* lsq_table(uint32_t nw) {
     default: return UBT(lsq_w5);
   }
 }
-UB_FN float bits_to_float(uint32_t b) {
-#ifdef __CUDA_ARCH__
-  return __uint_as_float(b);
-#else
-  float f; memcpy(&f, &b, 4); return f;
-#endif
-}
 
 UB_FN uint32_t interp_linear(uint32_t l, uint32_t h, uint32_t w) {  // astc_interpolate_linear (bc7enc.cpp:177)
   l = (l << 8) | l; h = (h << 8) | h;

@@ -17,85 +17,49 @@ struct Bc7Build {
 UB_FN uint32_t px_c(uint32_t v, uint32_t c) { return (v >> (8 * c)) & 255u; }
 UB_FN uint32_t px_set(uint32_t v, uint32_t c, uint32_t x) { return (v & ~(255u << (8 * c))) | (x << (8 * c)); }
 
-// One channel of the p-bit search: quantise x (= u/255) to `total_bits` with p-bit p, return the (total_bits) code.
-UB_FN uint32_t pbit_quant(float x, float scalep, int iscalep, int p) {
-  const float t = f_add(f_div(f_sub(f_mul(x, scalep), (float)p), 2.0f), .5f);
-  return (uint32_t)clampi(((int)t) * 2 + p, p, iscalep - 1 + p);
-}
-UB_FN uint32_t pbit_expand(uint32_t q, uint32_t total_bits) {
-  uint32_t s = (q << (8 - total_bits)) & 255u;
-  s |= (s >> total_bits);
-  return s;
-}
-
-// determine_unique_pbits (XC:15585-15647).  u_lo/u_hi hold the 8-bit unquantised endpoints per channel; a channel
-// marked in `one_mask` is the constant 1.0f (opaque alpha).  Returns packed 7/5-bit endpoints and the two p-bits.
-UB_FN void unique_pbits(uint32_t total_comps, uint32_t comp_bits, uint32_t u_lo, uint32_t u_hi, uint32_t one_mask,
-                        uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
-  const uint32_t total_bits = comp_bits + 1;
-  const int iscalep = (1 << total_bits) - 1;
-  const float scalep = (float)iscalep;
-  float xl[4], xh[4];
-#pragma unroll
-  for (uint32_t c = 0; c < 4; c++) {
-    xl[c] = ((one_mask >> c) & 1u) ? 1.0f : f_div((float)px_c(u_lo, c), 255.0f);
-    xh[c] = ((one_mask >> c) & 1u) ? 1.0f : f_div((float)px_c(u_hi, c), 255.0f);
-  }
+// determine_unique_pbits (XC:15585-15647).  Each channel's quantised code and fp32 squared error depend only on the
+// 8-bit value, the p-bit and the precision, so they come from tables (tools/gen_pbit_tables.py); what remains is the
+// reference's fp32 summation order over channels and its strict-< choice between p = 0 and p = 1.
+// u_lo/u_hi: 8-bit unquantised endpoints per channel; a channel the reference pins to 1.0f must be passed as 255.
+// wide = true: 7+1 bits (BC7 modes 3 and 6); false: 5+1 bits (BC7 mode 7).
+UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
+  const uint8_t* code = wide ? UBT(pb8_code) : UBT(pb6_code);
+  const uint32_t* err = wide ? UBT(pb8_err) : UBT(pb6_err);
   float best0 = 1e+9f, best1 = 1e+9f;
   out_lo = 0; out_hi = 0; pb = 0;
 #pragma unroll
-  for (int p = 0; p < 2; p++) {
+  for (uint32_t p = 0; p < 2; p++) {
     uint32_t qmin = 0, qmax = 0;
     float e0 = 0, e1 = 0;
 #pragma unroll
     for (uint32_t c = 0; c < 4; c++) {
-      const uint32_t a = pbit_quant(xl[c], scalep, iscalep, p);
-      const uint32_t b = pbit_quant(xh[c], scalep, iscalep, p);
-      qmin |= (a >> 1) << (8 * c);
-      qmax |= (b >> 1) << (8 * c);
-      if (c < total_comps) {
-        const float da = f_sub((float)pbit_expand(a, total_bits), f_mul(xl[c], 255.0f));
-        const float db = f_sub((float)pbit_expand(b, total_bits), f_mul(xh[c], 255.0f));
-        e0 = f_add(e0, f_mul(da, da));
-        e1 = f_add(e1, f_mul(db, db));
-      }
+      const uint32_t ia = p * 256 + px_c(u_lo, c), ib = p * 256 + px_c(u_hi, c);
+      qmin |= (uint32_t)code[ia] << (8 * c);
+      qmax |= (uint32_t)code[ib] << (8 * c);
+      if (c < total_comps) { e0 = f_add(e0, bits_to_float(err[ia])); e1 = f_add(e1, bits_to_float(err[ib])); }
     }
-    if (e0 < best0) { best0 = e0; pb = (pb & ~1u) | (uint32_t)p; out_lo = qmin; }
-    if (e1 < best1) { best1 = e1; pb = (pb & ~2u) | ((uint32_t)p << 1); out_hi = qmax; }
+    if (e0 < best0) { best0 = e0; pb = (pb & ~1u) | p; out_lo = qmin; }
+    if (e1 < best1) { best1 = e1; pb = (pb & ~2u) | (p << 1); out_hi = qmax; }
   }
 }
 
-// determine_shared_pbits (XC:15532-15582), BC7 mode 1 only (3 comps, 6 bits, alpha = 1.0f)
+// determine_shared_pbits (XC:15532-15582), BC7 mode 1 only (3 comps, 6+1 bits, alpha = 1.0f == 255)
 UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
-  const uint32_t total_bits = 7;
-  const int iscalep = 127;
-  const float scalep = 127.0f;
-  float xl[4], xh[4];
-#pragma unroll
-  for (uint32_t c = 0; c < 3; c++) {
-    xl[c] = f_div((float)px_c(u_lo, c), 255.0f);
-    xh[c] = f_div((float)px_c(u_hi, c), 255.0f);
-  }
-  xl[3] = 1.0f; xh[3] = 1.0f;
+  u_lo |= 0xFF000000u; u_hi |= 0xFF000000u;
   float best = 1e+9f;
   out_lo = 0; out_hi = 0; pb = 0;
 #pragma unroll
-  for (int p = 0; p < 2; p++) {
+  for (uint32_t p = 0; p < 2; p++) {
     uint32_t qmin = 0, qmax = 0;
     float err = 0;
 #pragma unroll
     for (uint32_t c = 0; c < 4; c++) {
-      const uint32_t a = pbit_quant(xl[c], scalep, iscalep, p);
-      const uint32_t b = pbit_quant(xh[c], scalep, iscalep, p);
-      qmin |= (a >> 1) << (8 * c);
-      qmax |= (b >> 1) << (8 * c);
-      if (c < 3) {
-        const float da = f_sub(f_div((float)pbit_expand(a, total_bits), 255.0f), xl[c]);
-        const float db = f_sub(f_div((float)pbit_expand(b, total_bits), 255.0f), xh[c]);
-        err = f_add(err, f_add(f_mul(da, da), f_mul(db, db)));
-      }
+      const uint32_t ia = p * 256 + px_c(u_lo, c), ib = p * 256 + px_c(u_hi, c);
+      qmin |= (uint32_t)UBT(pb7s_code)[ia] << (8 * c);
+      qmax |= (uint32_t)UBT(pb7s_code)[ib] << (8 * c);
+      if (c < 3) err = f_add(err, f_add(bits_to_float(UBT(pb7s_err)[ia]), bits_to_float(UBT(pb7s_err)[ib])));
     }
-    if (err < best) { best = err; pb = (uint32_t)p * 3u; out_lo = qmin; out_hi = qmax; }
+    if (err < best) { best = err; pb = p * 3u; out_lo = qmin; out_hi = qmax; }
   }
 }
 
@@ -202,17 +166,17 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
   switch (mode) {
     case 0: case 5: case 10: case 12: case 14: case 15: case 18: {
       o.mode = 6;
-      uint32_t lo, hi, one_mask = 0;
+      uint32_t lo, hi;
       if (comps == 2) {
         const uint32_t l0 = ep_unq(u, er, 0), l1 = ep_unq(u, er, 1);
         lo = l0 * 0x010101u | (ep_unq(u, er, 2) << 24);
         hi = l1 * 0x010101u | (ep_unq(u, er, 3) << 24);
       } else {
         subset_endpoints(u, er, 0, comps, lo, hi);
-        if (comps == 3) one_mask = 8;
+        if (comps == 3) { lo |= 0xFF000000u; hi |= 0xFF000000u; }
       }
       uint32_t pb;
-      unique_pbits(comps == 2 ? 4 : comps, 7, lo, hi, one_mask, o.lo[0], o.hi[0], pb);
+      unique_pbits(comps == 2 ? 4 : comps, true, lo, hi, o.lo[0], o.hi[0], pb);
       if (comps == 3) { o.lo[0] = px_set(o.lo[0], 3, 127); o.hi[0] = px_set(o.hi[0], 3, 127); }
       o.pbits = pb;
       const int kind = (mode == 18) ? 1 : (mode == 14) ? 2 : ((mode == 5) || (mode == 12)) ? 3 : 0;
@@ -225,7 +189,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
 #pragma unroll
       for (uint32_t c = 0; c < 3; c++) { lo |= (uint32_t)u.ep[2 * c] << (8 * c); hi |= (uint32_t)u.ep[2 * c + 1] << (8 * c); }
       uint32_t qlo, qhi, pb;
-      unique_pbits(3, 7, lo, hi, 8, qlo, qhi, pb);
+      unique_pbits(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
       o.lo[0] = o.lo[1] = qlo & 0xFFFFFFu;
       o.hi[0] = o.hi[1] = qhi & 0xFFFFFFu;
       o.pbits = pb | (pb << 2);
@@ -286,7 +250,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
         uint32_t lo, hi;
         subset_endpoints(u, er, s * 6, 3, lo, hi);
         uint32_t qlo, qhi, pb;
-        unique_pbits(3, 7, lo, hi, 8, qlo, qhi, pb);
+        unique_pbits(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
         const uint32_t k = inv ? 1 - s : s;
         o.lo[k] = px_set(qlo, 3, 127);
         o.hi[k] = px_set(qhi, 3, 127);
@@ -353,7 +317,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
           subset_endpoints(u, er, s * 8, 4, lo, hi);
         }
         uint32_t qlo, qhi, pb;
-        unique_pbits(4, 5, lo, hi, 0, qlo, qhi, pb);
+        unique_pbits(4, false, lo, hi, qlo, qhi, pb);
         const uint32_t k = inv ? 1 - s : s;
         o.lo[k] = qlo; o.hi[k] = qhi;
         o.pbits |= pb << (2 * k);

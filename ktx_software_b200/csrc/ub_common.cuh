@@ -51,6 +51,14 @@ UB_FN double d_mul(double a, double b) { return a * b; }
 UB_FN double d_div(double a, double b) { return a / b; }
 #endif
 
+UB_FN float bits_to_float(uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f; memcpy(&f, &b, 4); return f;
+#endif
+}
+
 UB_FN int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 UB_FN uint32_t minu(uint32_t a, uint32_t b) { return a < b ? a : b; }
 UB_FN uint32_t maxu(uint32_t a, uint32_t b) { return a > b ? a : b; }
@@ -139,6 +147,7 @@ UB_FN uint64_t brev64(uint64_t x) {
 }
 
 #include "uastc_tables.inc"
+#include "uastc_pbit_tables.inc"
 
 // ---- decoded fields of ubt_uastc_mode_desc (see tools/gen_tables.py for the packing)
 UB_FN uint32_t md_weight_bits(uint32_t d) { return d & 7; }
