@@ -300,7 +300,7 @@ def run_c5(args):
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                              "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
-                             "kernel": "k_transcode<BC7>", "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": 32 * n},
+                             "kernel": "k_transcode_tiled<BC7>", "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": 32 * n},
                 "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:
@@ -472,7 +472,7 @@ def run_c2(args):
                               "bc7_ms": bc7_ms, "astc_ms": astc_ms, "blocks": total_blocks,
                               "roofline": {"bound": "hbm", "achieved": xc_bytes / (bc7_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"],
                                            "unit": "GB/s", "frac": xc_bytes / (bc7_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
-                                           "kernel": "k_transcode<BC7>", "algorithmic_bytes_per_launch": xc_bytes}},
+                                           "kernel": "k_transcode_tiled<BC7>", "algorithmic_bytes_per_launch": xc_bytes}},
                 "encode_only_mpix_s": imgs[0].shape[0] * imgs[0].shape[1] / (enc0_ms * 1e-3) / 1e6,
                 "cpu_baseline": cpu}
         print(json.dumps(line))

@@ -57,6 +57,156 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Tiled transcode: the streaming kernel.  A CTA owns tiles of XT_TILE consecutive blocks (16 KB in, 16 KB out).
+//   1. one thread issues a TMA bulk copy (cp.async.bulk, mbarrier completion) of the NEXT tile while the current
+//      one is processed (double-buffered);
+//   2. the tile is binned by UASTC mode in shared memory (warp-aggregated counting sort of block indices), so that
+//      a warp works on blocks of ONE mode and runs that mode's fully specialised unpack/pack code -- every bit
+//      offset of a UASTC mode is a compile-time constant -- instead of diverging over the 19-way switch;
+//   3. each result overwrites its block's slot of the shared-memory tile, which leaves as one TMA bulk store.
+// Global traffic is exactly the algorithmic 32 B per block, fully coalesced by construction.
+const int XT_THREADS = 256;
+const int XT_TILE = 1024;
+const int XT_PER_THREAD = XT_TILE / XT_THREADS;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <int TARGET>
+__device__ __forceinline__ bool transcode_dispatch(uint32_t mode, const ub::Bits128& s, ub::Bits128& d) {
+  switch (mode) {
+#define XC_CASE(M) case M: return ub::transcode_known_mode<TARGET, M>(s, d);
+    XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
+    XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
+#undef XC_CASE
+    default: d.lo = 0; d.hi = 0; return false;
+  }
+}
+
+template <int TARGET>
+__global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
+                                                                unsigned long long* __restrict__ first_bad) {
+  __shared__ __align__(128) uint4 s_in[2][XT_TILE];  // a block's result overwrites its own input slot
+  __shared__ uint16_t s_order[XT_TILE];
+  __shared__ uint32_t s_hist[32];
+  __shared__ __align__(8) uint64_t s_bar[2];
+
+  const uint32_t tid = threadIdx.x, lane = tid & 31u;
+  const uint64_t n_tiles = (n_blocks + XT_TILE - 1) / XT_TILE;
+  uint64_t tile = blockIdx.x;
+  if (tile >= n_tiles) return;
+  auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)XT_TILE, n_blocks - t * XT_TILE); };
+
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
+    const uint32_t bytes = tile_count(tile) * 16u;
+    mbar_expect_tx(&s_bar[0], bytes);
+    bulk_g2s(s_in[0], src + tile * XT_TILE, bytes, &s_bar[0]);
+  }
+  __syncthreads();
+
+  uint32_t buf = 0, phase0 = 0, phase1 = 0;
+  for (; tile < n_tiles; tile += gridDim.x) {
+    const uint32_t cnt = tile_count(tile);
+    const uint64_t next = tile + gridDim.x;
+    if (tid == 0 && next < n_tiles) {  // prefetch the next tile into the other buffer once its bulk store has drained it
+      bulk_wait_read0();
+      const uint32_t bytes = tile_count(next) * 16u;
+      mbar_expect_tx(&s_bar[buf ^ 1], bytes);
+      bulk_g2s(s_in[buf ^ 1], src + next * XT_TILE, bytes, &s_bar[buf ^ 1]);
+    }
+    if (tid < 32) s_hist[tid] = 0;
+    mbar_wait(&s_bar[buf], buf ? phase1 : phase0);
+    if (buf) phase1 ^= 1; else phase0 ^= 1;
+    __syncthreads();
+
+    // ---- bin by mode: rank inside the bin from a warp-aggregated shared atomic
+    uint32_t my_mode[XT_PER_THREAD], my_rank[XT_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < XT_PER_THREAD; k++) {
+      const uint32_t i = tid + k * XT_THREADS;
+      const bool live = i < cnt;
+      const uint32_t m = live ? (uint32_t)ub::UBT(uastc_huff_modes)[s_in[buf][live ? i : 0].x & 127u] : 31u;
+      const uint32_t peers = __match_any_sync(0xFFFFFFFFu, m);
+      const uint32_t leader = __ffs(peers) - 1;
+      uint32_t base = 0;
+      if (lane == leader) base = atomicAdd(&s_hist[m], __popc(peers));
+      base = __shfl_sync(0xFFFFFFFFu, base, leader);
+      my_mode[k] = m;
+      my_rank[k] = base + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    if (tid < 32) {  // exclusive scan of the 32 bin counts
+      const uint32_t c = s_hist[tid];
+      uint32_t v = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v, o); if ((int)lane >= o) v += t; }
+      s_hist[tid] = v - c;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < XT_PER_THREAD; k++) {
+      const uint32_t i = tid + k * XT_THREADS;
+      if (i < cnt) s_order[s_hist[my_mode[k]] + my_rank[k]] = (uint16_t)(i | (my_mode[k] << 10));
+    }
+    __syncthreads();
+
+    // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
+#pragma unroll 1
+    for (int k = 0; k < XT_PER_THREAD; k++) {
+      const uint32_t j = tid + k * XT_THREADS;
+      if (j < cnt) {
+        const uint32_t e = s_order[j], idx = e & 1023u, m = e >> 10;
+        const uint4 v = s_in[buf][idx];
+        ub::Bits128 s, d;
+        s.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
+        s.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
+        const bool ok = transcode_dispatch<TARGET>(m, s, d);
+        uint4 o;
+        o.x = (uint32_t)d.lo; o.y = (uint32_t)(d.lo >> 32); o.z = (uint32_t)d.hi; o.w = (uint32_t)(d.hi >> 32);
+        s_in[buf][idx] = o;
+        if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)(tile * XT_TILE + idx));
+      }
+    }
+    fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
+    __syncthreads();
+    if (tid == 0) bulk_s2g(dst + tile * XT_TILE, s_in[buf], cnt * 16u);
+    buf ^= 1;
+  }
+  if (tid == 0) bulk_wait0();
+}
+
 // Encode (reference hot loop #1, ENC/basisu_comp.cpp:1519-1562 -> encode_uastc): one thread per 4x4 block, so a warp
 // is a group of 32 neighbouring blocks that walk the mode list in lock-step.  The 4x4 gather with edge replication
 // (image::extract_block_clamped, ENC/basisu_enc.h:3081) is fused into the load.  MAXC bounds the candidate list:
@@ -127,15 +277,13 @@ __global__ void k_set_u64(unsigned long long* p, unsigned long long v) { *p = v;
 
 int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n, cudaStream_t st, uint64_t* d_first_bad) {
   if (!n) return B200_OK;
-  const int threads = 256;
-  const uint64_t want = (n + threads - 1) / threads;
-  const uint64_t wave = (uint64_t)g_ctx.sm_count * 8;  // 8 resident CTAs of 256 threads per SM
-  uint64_t grid = want;
-  if (grid > wave) grid = wave * std::min<uint64_t>(4, (want + wave - 1) / wave);
+  // persistent tiles: up to 6 CTAs (34 KB of shared memory each) per SM, each walking tiles with a grid stride
+  const uint64_t tiles = (n + XT_TILE - 1) / XT_TILE;
+  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * 6);
   if (target == B200_TTF_BC7_RGBA)
-    k_transcode<0><<<(unsigned)grid, threads, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<0><<<grid, XT_THREADS, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
   else
-    k_transcode<1><<<(unsigned)grid, threads, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<1><<<grid, XT_THREADS, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
   g_launches++;
   CU(cudaGetLastError());
   return B200_OK;
@@ -269,19 +417,8 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
       if (err != cudaSuccess) break;
       cudaEventRecord(ev_in[b], s_in);
       cudaStreamWaitEvent(s_k, ev_in[b], 0);
-      // block indices inside the kernel are slab-relative; bias the flag by testing per slab below
-      {
-        const int threads = 256;
-        const uint64_t want = (n + threads - 1) / threads;
-        const uint64_t wave = (uint64_t)g_ctx.sm_count * 8;
-        uint64_t grid = want;
-        if (grid > wave) grid = wave * std::min<uint64_t>(4, (want + wave - 1) / wave);
-        if (target == B200_TTF_BC7_RGBA)
-          k_transcode<0><<<(unsigned)grid, threads, 0, s_k>>>((const uint4*)d_in[b], (uint4*)d_out[b], n, d_bad + ri);
-        else
-          k_transcode<1><<<(unsigned)grid, threads, 0, s_k>>>((const uint4*)d_in[b], (uint4*)d_out[b], n, d_bad + ri);
-        g_launches++;
-      }
+      // block indices inside the kernel are slab-relative; the flag only has to say "this run holds a bad block"
+      launch_transcode(target, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
       cudaEventRecord(ev_k[b], s_k);
       cudaStreamWaitEvent(s_out, ev_k[b], 0);
       err = cudaMemcpyAsync(dst_base + r.dofs + o * 16, d_out[b], n * 16, cudaMemcpyDeviceToHost, s_out);

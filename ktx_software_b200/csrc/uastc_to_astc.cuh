@@ -3,14 +3,16 @@
 // :14663-14795, :14587-14659, :14482-14501, and the blue-contraction undo in unpack_uastc :15328-15371).
 #pragma once
 #include "uastc_unpack.cuh"
+#include "uastc_to_bc7.cuh"
 
 namespace ub {
 
 // BISE-encode `n` endpoint codes of the given range at bit `pos` (values = bits | trit_or_quint << nbits).
+template <int KM>
 UB_FN void astc_pack_bise(Bits128& dst, const uint8_t* vals, uint32_t n, uint32_t range, uint32_t pos) {
-  const uint32_t nb = UBT(astc_bise_range)[range * 3 + 0];
-  const uint32_t trits = UBT(astc_bise_range)[range * 3 + 1];
-  const uint32_t quints = UBT(astc_bise_range)[range * 3 + 2];
+  const uint32_t nb = (KM >= 0) ? bise_c(range, 0) : UBT(astc_bise_range)[range * 3 + 0];
+  const uint32_t trits = (KM >= 0) ? bise_c(range, 1) : UBT(astc_bise_range)[range * 3 + 1];
+  const uint32_t quints = (KM >= 0) ? bise_c(range, 2) : UBT(astc_bise_range)[range * 3 + 2];
   const uint32_t bm = (1u << nb) - 1u;
   if (trits) {
     // groups of five: m0 T[1:0] m1 T[3:2] m2 T[4] m3 T[6:5] m4 T[7]
@@ -71,12 +73,14 @@ UB_FN Bits128 astc_pack_solid(uint32_t rgba) {  // void-extent block, UNORM16 = 
   return d;
 }
 
-UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) {
+template <int KM>
+UB_FN bool transcode_block_to_astc_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
-  if (!unpack_uastc(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
-  if (u.mode == UASTC_MODE_SOLID) { dst = astc_pack_solid(u.solid); return true; }
+  if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
+  const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
+  if (mode == UASTC_MODE_SOLID) { dst = astc_pack_solid(u.solid); return true; }
 
-  const uint32_t d = u.desc;
+  const uint32_t d = (KM >= 0) ? mode_desc_c(KM) : u.desc;
   const uint32_t subsets = md_subsets(d), comps = md_comps(d), er = md_endpoint_range(d), wb = md_weight_bits(d);
   const uint32_t planes = 1 + md_dual_plane(d);
 
@@ -114,7 +118,7 @@ UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) {
   }
 
   Bits128 o;
-  o.lo = UBT(uastc_mode_astc_block_mode)[u.mode];
+  o.lo = UBT(uastc_mode_astc_block_mode)[mode];
   o.hi = 0;
   uint32_t pos = 11;
   o.lo |= (uint64_t)(subsets - 1) << pos; pos += 2;
@@ -123,7 +127,7 @@ UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) {
   else {
     uint32_t seed;
     if (subsets == 3) seed = (UBT(common3)[u.pattern] >> 8) & 0xFFFFu;
-    else if (u.mode == 7) seed = (UBT(common7)[u.pattern] >> 8) & 0xFFFFu;
+    else if (mode == 7) seed = (UBT(common7)[u.pattern] >> 8) & 0xFFFFu;
     else seed = (UBT(common2)[u.pattern] >> 8) & 0xFFFFu;
     o.lo |= (uint64_t)seed << pos; pos += 10;
     o.lo |= (uint64_t)((cem << 2) & 63u) << pos; pos += 6;
@@ -131,7 +135,7 @@ UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) {
   const uint32_t total_wbits = 16 * planes * wb;
   if (planes == 2) bits_or(o, 128 - total_wbits - 2, u.ccs);
 
-  astc_pack_bise(o, u.ep, comps * 2 * subsets, er, pos);
+  astc_pack_bise<KM>(o, u.ep, comps * 2 * subsets, er, pos);
 
   // weights: each entry bit-reversed, entry 0 ending at bit 127 -> the reversal of the whole packed string
   {
@@ -142,6 +146,14 @@ UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) {
   }
   dst = o;
   return true;
+}
+UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) { return transcode_block_to_astc_t<-1>(src, dst); }
+
+// Mode-dispatched transcode of one block whose mode the caller already decoded (blocks binned by mode, so a warp takes
+// one case).  TARGET 0 = BC7, 1 = ASTC.
+template <int TARGET, int KM>
+UB_FN bool transcode_known_mode(const Bits128& src, Bits128& dst) {
+  return TARGET ? transcode_block_to_astc_t<KM>(src, dst) : transcode_block_to_bc7_t<KM>(src, dst);
 }
 
 }  // namespace ub

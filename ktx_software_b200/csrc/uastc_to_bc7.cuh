@@ -65,9 +65,9 @@ UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t
 
 // Re-pack the UASTC weights (entries of wb bits) of one plane into `ob`-bit BC7 selectors through a tiny value map.
 // plane_stride = 1 (single plane) or 2; plane = 0/1.  map4 holds up to 32 4-bit outputs? no: see callers.
-UB_FN uint64_t remap_selectors(const UnpackedUastc& u, uint32_t plane_stride, uint32_t plane, uint32_t ob, int kind) {
+UB_FN uint64_t remap_selectors(const UnpackedUastc& u, uint32_t desc, uint32_t plane_stride, uint32_t plane, uint32_t ob, int kind) {
   // kind: 0 identity, 1 = 5->4 bits, 2 = 2->4 bits, 3 = 3->4 bits, 4 = 1->2 bits (0 / 3)
-  const uint32_t wb = md_weight_bits(u.desc);
+  const uint32_t wb = md_weight_bits(desc);
   uint64_t r = 0;
 #pragma unroll
   for (uint32_t i = 0; i < 16; i++) {
@@ -121,10 +121,12 @@ UB_FN void subset_endpoints(const UnpackedUastc& u, uint32_t er, uint32_t base, 
 }
 
 // Per-mode mapping (XC:15669-16161).
-UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
-  const uint32_t mode = u.mode;
-  const uint32_t er = md_endpoint_range(u.desc);
-  const uint32_t comps = md_comps(u.desc);
+template <int KM>
+UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
+  const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
+  const uint32_t desc = (KM >= 0) ? mode_desc_c(KM) : u.desc;
+  const uint32_t er = md_endpoint_range(desc);
+  const uint32_t comps = md_comps(desc);
   o.partition = 0; o.rotation = 0; o.pbits = 0; o.sel = 0; o.asel = 0;
 #pragma unroll
   for (int k = 0; k < 3; k++) { o.lo[k] = 0; o.hi[k] = 0; }
@@ -180,7 +182,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
       if (comps == 3) { o.lo[0] = px_set(o.lo[0], 3, 127); o.hi[0] = px_set(o.hi[0], 3, 127); }
       o.pbits = pb;
       const int kind = (mode == 18) ? 1 : (mode == 14) ? 2 : ((mode == 5) || (mode == 12)) ? 3 : 0;
-      o.sel = remap_selectors(u, 1, 0, 4, kind);
+      o.sel = remap_selectors(u, desc, 1, 0, 4, kind);
       break;
     }
     case 1: {
@@ -193,7 +195,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
       o.lo[0] = o.lo[1] = qlo & 0xFFFFFFu;
       o.hi[0] = o.hi[1] = qhi & 0xFFFFFFu;
       o.pbits = pb | (pb << 2);
-      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
       break;
     }
     case 2: {
@@ -216,7 +218,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
         o.hi[k] = qhi & 0xFFFFFFu;
         o.pbits |= (pb & 1u) << (2 * k);
       }
-      o.sel = remap_selectors(u, 1, 0, 3, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 3, 0);
       break;
     }
     case 3: {
@@ -237,7 +239,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
 #pragma unroll
         for (uint32_t q = 0; q < 3; q++) if (q == k) { o.lo[q] = lo; o.hi[q] = hi; }
       }
-      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
       break;
     }
     case 4: {
@@ -256,7 +258,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
         o.hi[k] = px_set(qhi, 3, 127);
         o.pbits |= pb << (2 * k);
       }
-      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
       break;
     }
     case 6: case 11: case 13: case 17: {
@@ -279,8 +281,8 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
         }
       }
       const int kind = (mode == 13) ? 4 : 0;
-      o.sel = remap_selectors(u, 2, 0, 2, kind);
-      o.asel = remap_selectors(u, 2, 1, 2, kind);
+      o.sel = remap_selectors(u, desc, 2, 0, 2, kind);
+      o.asel = remap_selectors(u, desc, 2, 1, 2, kind);
       break;
     }
     case 7: {
@@ -299,7 +301,7 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
           o.hi[bp] |= ((astc_unquant(er, ap ? h1 : h0) * 31u + 127u) / 255u) << (8 * c);
         }
       }
-      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
       break;
     }
     default: {  // 9, 16
@@ -322,11 +324,13 @@ UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) {
         o.lo[k] = qlo; o.hi[k] = qhi;
         o.pbits |= pb << (2 * k);
       }
-      o.sel = remap_selectors(u, 1, 0, 2, 0);
+      o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
       break;
     }
   }
 }
+
+UB_FN void uastc_to_bc7_build(const UnpackedUastc& u, Bc7Build& o) { uastc_to_bc7_build_t<-1>(u, o); }
 
 // BC7 per-mode constants (XC:14262-14272), packed: [2:0]? -- kept as tiny switch-free tables in registers.
 UB_FN uint32_t bc7_subsets(uint32_t m) { return (0x21112323u >> (4 * m)) & 15u; }      // 3,2,3,2,1,1,1,2
@@ -425,13 +429,15 @@ UB_FN Bits128 bc7_pack(Bc7Build& o) {
 }
 
 // Full path for one block.  Returns false on an invalid UASTC block (output then zeroed).
-UB_FN bool transcode_block_to_bc7(const Bits128& src, Bits128& dst) {
+template <int KM>
+UB_FN bool transcode_block_to_bc7_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
-  if (!unpack_uastc(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
+  if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
   Bc7Build o;
-  uastc_to_bc7_build(u, o);
+  uastc_to_bc7_build_t<KM>(u, o);
   dst = bc7_pack(o);
   return true;
 }
+UB_FN bool transcode_block_to_bc7(const Bits128& src, Bits128& dst) { return transcode_block_to_bc7_t<-1>(src, dst); }
 
 }  // namespace ub

@@ -31,10 +31,12 @@ UB_FN uint32_t spread_mask2(uint32_t m16) {  // 16-bit subset mask -> 2 bits per
 }
 
 // Returns false for an invalid block (reserved mode code, pattern index out of range): XC:14944, :15036-15049.
-UB_FN bool unpack_uastc(const Bits128& blk, UnpackedUastc& u, bool want_hints) {
-  const uint32_t mode = UBT(uastc_huff_modes)[(uint32_t)blk.lo & 127u];
-  if (mode >= UASTC_TOTAL_MODES) return false;
-  const uint32_t d = UBT(uastc_mode_desc)[mode];
+// KM >= 0: the caller already knows the mode (blocks binned by mode); every field offset then folds to a constant.
+template <int KM>
+UB_FN bool unpack_uastc_t(const Bits128& blk, UnpackedUastc& u, bool want_hints) {
+  const uint32_t mode = (KM >= 0) ? (uint32_t)KM : (uint32_t)UBT(uastc_huff_modes)[(uint32_t)blk.lo & 127u];
+  if (KM < 0 && mode >= UASTC_TOTAL_MODES) return false;
+  const uint32_t d = (KM >= 0) ? mode_desc_c(KM) : UBT(uastc_mode_desc)[mode];
   u.mode = mode;
   u.desc = d;
   u.pattern = 0;
@@ -86,9 +88,9 @@ UB_FN bool unpack_uastc(const Bits128& blk, UnpackedUastc& u, bool want_hints) {
   const uint32_t comps = md_comps(d);
   const uint32_t total_values = comps * 2 * subsets;
   const uint32_t er = md_endpoint_range(d);
-  const uint32_t ep_bits = UBT(astc_bise_range)[er * 3 + 0];
-  const uint32_t has_trits = UBT(astc_bise_range)[er * 3 + 1];
-  const uint32_t has_quints = UBT(astc_bise_range)[er * 3 + 2];
+  const uint32_t ep_bits = (KM >= 0) ? bise_c(er, 0) : UBT(astc_bise_range)[er * 3 + 0];
+  const uint32_t has_trits = (KM >= 0) ? bise_c(er, 1) : UBT(astc_bise_range)[er * 3 + 1];
+  const uint32_t has_quints = (KM >= 0) ? bise_c(er, 2) : UBT(astc_bise_range)[er * 3 + 2];
 
   uint32_t tq = 0;  // up to four bundles, 8 bits each
   uint32_t bundle = 0, mul = 0;
@@ -163,6 +165,8 @@ UB_FN bool unpack_uastc(const Bits128& blk, UnpackedUastc& u, bool want_hints) {
   u.w = w;
   return true;
 }
+
+UB_FN bool unpack_uastc(const Bits128& blk, UnpackedUastc& u, bool want_hints) { return unpack_uastc_t<-1>(blk, u, want_hints); }
 
 // weight entry i (UASTC order) of an unpacked block
 UB_FN uint32_t uastc_weight(const UnpackedUastc& u, uint32_t i) {

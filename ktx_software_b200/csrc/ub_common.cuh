@@ -16,12 +16,14 @@
 #define UB_FN_NOINLINE __device__ __noinline__
 #define UB_BIG __device__ __noinline__   /* large encoder stages: one out-of-line copy, called from every mode */
 #define UB_TABLE(type, name, n) static __device__ const type ubt_##name[n]
+#define UB_CONSTEXPR __host__ __device__ constexpr
 #else
 #define UB_FN static inline
 #define UB_MFN inline
 #define UB_FN_NOINLINE static
 #define UB_BIG static
 #define UB_TABLE(type, name, n) static const type ubt_##name[n]
+#define UB_CONSTEXPR constexpr
 #endif
 #define UBT(name) ubt_##name
 
@@ -158,6 +160,18 @@ UB_FN uint32_t md_comps(uint32_t d) { return (d >> 11) & 7; }
 UB_FN uint32_t md_hint_bits(uint32_t d) { return (d >> 14) & 31; }
 UB_FN uint32_t md_huff_len(uint32_t d) { return (d >> 19) & 15; }
 UB_FN uint32_t md_huff_code(uint32_t d) { return (d >> 23) & 127; }
+
+
+// ---- compile-time copies of the two tiny tables the mode-specialised transcoders fold on (checked against the
+// generated tables by tests/test_oracle_cpu.py::test_constexpr_tables_match)
+UB_CONSTEXPR uint32_t mode_desc_c(int m) {
+  constexpr uint32_t t[19] = {0x00a3d99cu,0x1ab3d9a2u,0x0eabda43u,0x01abdb3au,0x09abda62u,0x05abd9a3u,0x0dabdd92u,0x03abda62u,0x0ba82000u,0x07ade242u,0x011c616cu,0x0014656au,0x031c619bu,0x0fade5a1u,0x06ade1a2u,0x02bdd1a4u,0x0ab5d2a2u,0x12b5d5a2u,0x04a3d95du};
+  return t[m < 0 ? 0 : m];
+}
+UB_CONSTEXPR uint32_t bise_c(uint32_t range, uint32_t k) {  // k: 0 = bits, 1 = trits, 2 = quints
+  constexpr uint8_t t[63] = {1,0,0,0,1,0,2,0,0,0,0,1,1,1,0,3,0,0,1,0,1,2,1,0,4,0,0,2,0,1,3,1,0,5,0,0,3,0,1,4,1,0,6,0,0,4,0,1,5,1,0,7,0,0,5,0,1,6,1,0,8,0,0};
+  return t[range * 3 + k];
+}
 
 UB_FN uint32_t astc_unquant(uint32_t range, uint32_t code) { return UBT(astc_unquant)[range * 256 + code] & 0xFF; }
 

@@ -152,3 +152,18 @@ def test_port_encode_flag_variants_vs_ref():
     px = np.concatenate([R.adversarial_blocks(9, 8), R.ref_extract_blocks(R.img_mix(48, 48, 2))])
     for extra in (8, 16, 64, 128, 256, 512):
         assert (R.port_encode_blocks(px, 2 | extra) == R.ref_encode_blocks(px, 2 | extra)).all(), extra
+
+
+def test_constexpr_tables_match():
+    """ub_common.cuh's compile-time copies (mode_desc_c, bise_c) of two generated tables must equal the generated ones."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    tabs = open(os.path.join(root, "ktx_software_b200/csrc/uastc_tables.inc")).read()
+    com = open(os.path.join(root, "ktx_software_b200/csrc/ub_common.cuh")).read()
+
+    def nums(txt):
+        return [int(x.strip().rstrip("u"), 0) for x in txt.replace("\n", "").split(",") if x.strip()]
+    md = nums(re.search(r"uastc_mode_desc, 19\) = \{(.*?)\};", tabs, re.S).group(1))
+    br = nums(re.search(r"astc_bise_range, 63\) = \{(.*?)\};", tabs, re.S).group(1))
+    assert nums(re.search(r"constexpr uint32_t t\[19\] = \{(.*?)\};", com, re.S).group(1)) == md
+    assert nums(re.search(r"constexpr uint8_t t\[63\] = \{(.*?)\};", com, re.S).group(1)) == br

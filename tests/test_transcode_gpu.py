@@ -91,3 +91,33 @@ def test_device_variant_matches_host_variant(K):
     K.transcode_dev(K.TTF_ASTC_4x4_RGBA, u2.data_ptr(), out.data_ptr(), u2.shape[0], 0, bad.data_ptr())
     torch.cuda.synchronize()
     assert bad.item() == 7
+
+
+@pytest.mark.parametrize("n", [1, 31, 1023, 1024, 1025, 2048 + 17, 300000])
+def test_tile_boundaries_and_mode_binning(K, n):
+    """The tiled kernel bins each 1024-block tile by mode; sizes around the tile edge and mode-sorted / mode-shuffled
+    inputs must give the same bytes as the per-block golden answers."""
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    rng = np.random.default_rng(n)
+    pick = rng.integers(0, len(g["uastc"]), n)
+    if n == 300000:
+        pick = np.sort(pick)  # long single-mode runs (the corpus is grouped by source)
+    u = g["uastc"][pick]
+    assert (K.transcode(u, K.TTF_BC7_RGBA).reshape(-1, 16) == g["bc7"][pick]).all()
+    assert (K.transcode(u, K.TTF_ASTC_4x4_RGBA).reshape(-1, 16) == g["astc"][pick]).all()
+
+
+def test_many_invalid_blocks_report_first(K):
+    import torch
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    u = torch.from_numpy(g["uastc"][:5000].copy()).cuda()
+    inv = torch.from_numpy(g["invalid"][:3].copy()).cuda()
+    u[4097] = inv[0]; u[1500] = inv[1]; u[4999] = inv[2]
+    out = torch.empty_like(u)
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    K.transcode_dev(K.TTF_BC7_RGBA, u.data_ptr(), out.data_ptr(), u.shape[0], 0, bad.data_ptr())
+    torch.cuda.synchronize()
+    assert bad.item() == 1500
+    ok = np.ones(5000, bool); ok[[1500, 4097, 4999]] = False
+    assert (out.cpu().numpy()[ok] == g["bc7"][:5000][ok]).all()
+    assert (out.cpu().numpy()[~ok] == 0).all()
