@@ -46,3 +46,60 @@ PORT_API uint64_t port_ccc(const uint8_t* px, uint32_t n, uint32_t nw, uint32_t 
   memcpy(out, &r.astc_lo, 4); memcpy(out + 4, &r.astc_hi, 4); memcpy(out + 8, r.sel, 16);
   return e;
 }
+
+// ---- RDO: the serial walk, written the plain way over the product's per-block pieces (uastc_rdo.cuh).
+#include "../ktx_software_b200/csrc/uastc_rdo.cuh"
+#include <vector>
+
+static void port_rdo_range(uint8_t* blocks, const uint8_t* px, uint32_t first_index, uint32_t last_index, const ub::RdoParams& p) {
+  uint32_t cap = 16;
+  while (cap < 2 * (last_index - first_index) + 16) cap <<= 1;
+  std::vector<ub::RdoHistEntry> hist(cap);
+  memset(hist.data(), 0, cap * sizeof(ub::RdoHistEntry));
+  const uint32_t mask = cap - 1;
+  for (uint32_t bi = first_index; bi < last_index; bi++) {
+    ub::Bits128 blk;
+    memcpy(&blk, blocks + (size_t)bi * 16, 16);
+    uint32_t pp[16];
+    memcpy(pp, px + (size_t)bi * 64, 64);
+    ub::RdoCur c;
+    if (!ub::rdo_prepare(pp, blk, p, c)) return;
+    if (c.solid) continue;
+    if (c.skip) { ub::rdo_hist_set(hist.data(), mask, c.first, c.sel_lo, bi); continue; }
+    float best_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist.data(), mask, c.first, c.sel_lo), bi, p);
+    ub::Bits128 best = blk;
+    bool modified = false;
+    const int lo = (int)first_index > (int)bi - (int)p.window ? (int)first_index : (int)bi - (int)p.window;
+    for (int pi = (int)bi - 1; pi >= lo; --pi) {
+      ub::Bits128 prev;
+      memcpy(&prev, blocks + (size_t)pi * 16, 16);
+      uint64_t slo, shi;
+      ub::rdo_get_sel(prev, c.first, c.total, slo, shi);
+      const int64_t h = ub::rdo_hist_find(hist.data(), mask, c.first, slo);
+      const int64_t match = h >= 0 ? h : pi;
+      if (match > pi) continue;
+      if (ub::UBT(uastc_huff_modes)[(uint32_t)prev.lo & 127u] >= ub::UASTC_TOTAL_MODES) return;  // unpack of prev failed
+      float t; ub::Bits128 trial;
+      if (!ub::rdo_trial(pp, blk, prev, c, bi, (uint32_t)match, p, t, trial)) continue;
+      if (t < best_t) { best_t = t; best = trial; modified = true; }
+    }
+    if (modified) {
+      if (p.refine && c.mode == 0) best = ub::rdo_refine_mode0(pp, best);
+      best = ub::rdo_rehint(pp, best, p.flags);
+      memcpy(blocks + (size_t)bi * 16, &best, 16);
+    }
+    uint64_t slo, shi;
+    ub::rdo_get_sel(best, c.first, c.total, slo, shi);
+    ub::rdo_hist_set(hist.data(), mask, c.first, slo, bi);
+  }
+}
+
+PORT_API void port_rdo(uint8_t* blocks, uint32_t n, const uint8_t* px, float lambda, uint32_t dict_size, float max_rms_ratio,
+                       float skip_rms, float smooth_scale, float smooth_std_dev, uint32_t flags, uint32_t total_jobs) {
+  ub::RdoParams p;
+  p.lambda = lambda; p.max_rms_ratio = max_rms_ratio; p.skip_rms = skip_rms; p.smooth_scale = smooth_scale;
+  p.smooth_std_dev = smooth_std_dev; p.window = dict_size / 16 ? dict_size / 16 : 1; p.literal_cost = 100; p.flags = flags; p.refine = 1;
+  uint32_t per;
+  const uint32_t jobs = ub::rdo_job_ranges(n, total_jobs, &per);
+  for (uint32_t j = 0; j < jobs; j++) port_rdo_range(blocks, px, j * per, (j + 1) * per < n ? (j + 1) * per : n, p);
+}

@@ -247,3 +247,30 @@ def port_encode_blocks(px, flags):
     f.restype = None
     f(_p(px), px.shape[0], flags, _p(out))
     return out
+
+
+RDO_DEFAULTS = dict(lam=1.0, dict_size=4096, max_rms_ratio=10.0, skip_rms=8.0, smooth_scale=10.0, smooth_std_dev=18.0)
+
+
+def ref_rdo(blocks, px, flags, threads=4, total_jobs=0, **kw):
+    """Reference uastc_rdo in place on a copy.  total_jobs as basisu_comp.cpp:1576 (min(4, threads) or 0)."""
+    k = dict(RDO_DEFAULTS); k.update(kw)
+    b = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16).copy()
+    px = np.ascontiguousarray(px, dtype=np.uint8).reshape(-1, 64)
+    rc = ref().ref_rdo(_p(b), b.shape[0], _p(px), k["lam"], k["dict_size"], k["max_rms_ratio"], k["skip_rms"], k["smooth_scale"],
+                       k["smooth_std_dev"], flags, threads, total_jobs)
+    assert rc == 0
+    return b
+
+
+def port_rdo(blocks, px, flags, total_jobs=0, **kw):
+    k = dict(RDO_DEFAULTS); k.update(kw)
+    b = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16).copy()
+    px = np.ascontiguousarray(px, dtype=np.uint8).reshape(-1, 64)
+    f = port().port_rdo
+    f.restype = None
+    f.argtypes = [_u8p, ctypes.c_uint32, _u8p, ctypes.c_float, ctypes.c_uint32, ctypes.c_float, ctypes.c_float, ctypes.c_float,
+                  ctypes.c_float, ctypes.c_uint32, ctypes.c_uint32]
+    f(_p(b), b.shape[0], _p(px), k["lam"], k["dict_size"], k["max_rms_ratio"], k["skip_rms"], k["smooth_scale"], k["smooth_std_dev"],
+      flags, total_jobs)
+    return b
