@@ -102,6 +102,13 @@ int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64
 int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
                                 uint32_t pack_flags, void* stream, uint32_t* d_any_alpha);
 
+/* The RDO post-pass alone, device-resident: replaces uastc_rdo (ENC/basisu_uastc_enc.cpp:4109) as
+ * encode_slices_to_uastc_4x4_ldr calls it per slice (ENC/basisu_comp.cpp:1564-1577).  d_blocks: n_blocks UASTC blocks of ONE
+ * image, rewritten in place; d_block_pixels: their n_blocks x 64 B source texels.  Uses params->rdo_* and
+ * params->pack_flags (for the hint recomputation); job ranges follow params->rdo_total_jobs.  Synchronous. */
+int b200_uastc_rdo_blocks_dev(void* d_blocks, const void* d_block_pixels, uint64_t n_blocks, const b200_uastc_params* params,
+                              void* stream);
+
 #ifdef __cplusplus
 }
 #endif

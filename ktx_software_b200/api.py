@@ -10,7 +10,7 @@ TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
-                    "b200_uastc_encode_image_dev"]
+                    "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -57,6 +57,7 @@ def lib():
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
         l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        l.b200_uastc_rdo_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.POINTER(UastcParams), ctypes.c_void_p]
         _lib = l
     return _lib
 
@@ -120,6 +121,12 @@ def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale
     p.rdo_max_smooth_block_std_dev = smooth_std_dev
     p.rdo_total_jobs = total_jobs
     return p
+
+
+def rdo_blocks_dev(d_blocks, d_block_pixels, n_blocks, pack_flags, stream=0, **rdo):
+    """RDO post-pass in place on device-resident blocks of one image (b200_uastc_rdo_blocks_dev)."""
+    p = make_params(pack_flags, rdo=True, **rdo)
+    _check(lib().b200_uastc_rdo_blocks_dev(d_blocks, d_block_pixels, n_blocks, ctypes.byref(p), stream or None))
 
 
 def encode_images(images, pack_flags, **rdo):

@@ -16,6 +16,7 @@
 #include "uastc_to_bc7.cuh"
 #include "uastc_to_astc.cuh"
 #include "uastc_encode.cuh"
+#include "uastc_rdo.cuh"
 
 namespace {
 
@@ -265,6 +266,202 @@ __global__ void __launch_bounds__(128) k_encode_blocks(const uint4* __restrict__
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// RDO (reference hot loop #2, ENC/basisu_uastc_enc.cpp:3825-4165).  Three kernels:
+//   k_rdo_prep    one warp per block, lane = weight level: the per-texel error tables of uastc_rdo.cuh (parallel);
+//   k_rdo_chain   one CTA per job range: the serial walk.  256 threads score the (up to) 256 window candidates of
+//                 the current block from its table in shared memory, a 64-bit shared atomicMin picks the winner
+//                 (ties -> nearest earlier block, the reference's scan order), thread 0 commits it;
+//   k_rdo_rehint  one thread per modified block: recompute the transcoding hints (parallel).
+// The walk is cut into chunks of RDO_CHUNK steps so the tables of a chunk (2 KB per block) stay small.
+struct RdoChain {
+  uint32_t first, last;      // job range [first, last) in the concatenated block array
+  uint64_t hist_off;         // first entry of this chain's selector history
+  uint32_t hist_mask;
+  uint32_t pad;
+};
+const int RDO_THREADS = 288;       // 256 trial threads + one warp that prepares the current block
+const uint32_t RDO_CHUNK = 8192;   // steps per launch
+
+__global__ void __launch_bounds__(256) k_gather_blocks(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
+                                                       uint4* __restrict__ out, uint32_t bx, uint32_t by, unsigned int* __restrict__ any_alpha) {
+  const uint32_t n = bx * by;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t x0 = (i % bx) * 4, y0 = (i / bx) * 4;
+    uint32_t amin = 255;
+    for (uint32_t y = 0; y < 4; y++) {
+      uint32_t r[4];
+      for (uint32_t x = 0; x < 4; x++) {
+        const uint32_t sx = min(x0 + x, w - 1), sy = min(y0 + y, h - 1);
+        const uint8_t* q = img + (size_t)sy * pitch + (size_t)sx * 4;
+        r[x] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+        amin = min(amin, r[x] >> 24);
+      }
+      out[(size_t)i * 4 + y] = make_uint4(r[0], r[1], r[2], r[3]);
+    }
+    if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
+  }
+}
+
+__device__ __forceinline__ ub::Bits128 to_bits(const uint4& v) {
+  ub::Bits128 b;
+  b.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
+  b.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
+  return b;
+}
+__device__ __forceinline__ uint4 from_bits(const ub::Bits128& b) {
+  return make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
+}
+
+// chunk-local table slot of block `bi` of chain `c`: c * RDO_CHUNK + (bi - first - step0)
+__global__ void __launch_bounds__(256) k_rdo_prep(const uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
+                                                  uint32_t n_chains, uint32_t step0, ub::RdoBlockInfo* __restrict__ info,
+                                                  uint32_t* __restrict__ tables, unsigned int* __restrict__ err_flag) {
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+  const uint32_t c = warp / RDO_CHUNK, k = warp % RDO_CHUNK;
+  if (c >= n_chains) return;
+  const uint32_t bi = chains[c].first + step0 + k;
+  if (bi >= chains[c].last) return;
+  uint32_t p[16];
+#pragma unroll
+  for (uint32_t y = 0; y < 4; y++) {
+    const uint4 v = __ldg(px + (size_t)bi * 4 + y);
+    p[4 * y] = v.x; p[4 * y + 1] = v.y; p[4 * y + 2] = v.z; p[4 * y + 3] = v.w;
+  }
+  const ub::Bits128 blk = to_bits(__ldg(blocks + bi));
+  ub::RdoBlockInfo f;
+  ub::UnpackedUastc u;
+  const bool ok = ub::rdo_block_info(blk, f, u);
+  if (lane == 0) { info[(size_t)c * RDO_CHUNK + k] = f; if (!ok) atomicOr(err_flag, 1u); }
+  if (!ok || f.mode == ub::UASTC_MODE_SOLID) return;
+  if (lane < (1u << f.wb)) ub::rdo_fill_level(p, u, f, lane, tables + ((size_t)c * RDO_CHUNK + k) * ub::RDO_TABLE_WORDS);
+}
+
+__global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
+                                                           uint32_t step0, const ub::RdoBlockInfo* __restrict__ info,
+                                                           const uint32_t* __restrict__ tables, ub::RdoHistEntry* __restrict__ hist_all,
+                                                           uint8_t* __restrict__ modified, ub::RdoParams p) {
+  __shared__ __align__(16) uint32_t s_table[ub::RDO_TABLE_WORDS];
+  __shared__ __align__(16) uint4 s_ring[256];
+  __shared__ __align__(16) uint32_t s_px[16];
+  __shared__ uint4 s_blk;
+  __shared__ ub::RdoBlockInfo s_info;
+  __shared__ ub::RdoCur s_cur;
+  __shared__ float s_keep_t;
+  __shared__ unsigned long long s_best;
+
+  const RdoChain ch = chains[blockIdx.x];
+  const uint32_t tid = threadIdx.x;
+  ub::RdoHistEntry* hist = hist_all + ch.hist_off;
+  const uint32_t begin = ch.first + step0;
+  if (begin >= ch.last) return;
+  const uint32_t end = min(ch.last, begin + RDO_CHUNK);
+  // refill the ring with the (final) blocks just before this chunk
+  if (tid < 256) { const uint32_t back = tid + 1; if (begin >= ch.first + back) s_ring[(begin - back) & 255u] = blocks[begin - back]; }
+  __syncthreads();
+
+  for (uint32_t bi = begin; bi < end; bi++) {
+    const size_t slot = (size_t)blockIdx.x * RDO_CHUNK + (bi - begin);
+    if (tid < 128) ((uint4*)s_table)[tid] = __ldg((const uint4*)(tables + slot * ub::RDO_TABLE_WORDS) + tid);
+    else if (tid < 132) ((uint4*)s_px)[tid - 128] = __ldg(px + (size_t)bi * 4 + (tid - 128));
+    else if (tid == 132) s_blk = blocks[bi];
+    else if (tid == 133) s_info = info[slot];
+    else if (tid == 134) s_best = ~0ull;
+    __syncthreads();
+    const ub::RdoBlockInfo f = s_info;
+    const ub::Bits128 blk = to_bits(s_blk);
+    if (f.mode == ub::UASTC_MODE_SOLID || !f.valid) {  // uniform: left alone, but later blocks may still splice from it
+      if (tid == 0) s_ring[bi & 255u] = s_blk;
+      __syncthreads();
+      continue;
+    }
+    const uint32_t first = ub::UBT(rdo_sel_bits)[f.mode * 2], total = ub::UBT(rdo_sel_bits)[f.mode * 2 + 1];
+    const uint32_t lo_index = (bi - ch.first > p.window) ? bi - p.window : ch.first;
+    const uint32_t n_win = bi - lo_index;
+
+    // ---- score: thread k takes candidates k, k+256, ... (nearest first); the spare warp prepares the current block
+    uint64_t my_err = 0; uint32_t my_k = 0xFFFFFFFFu, my_match = 0;
+    unsigned long long my_key = ~0ull;
+    if (tid == 256) {
+      ub::RdoCur c;
+      ub::rdo_prepare_fast(s_px, blk, f, s_table, p, c);
+      s_cur = c;
+      s_keep_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist, ch.hist_mask, c.first, c.sel_lo), bi, p);
+    }
+    // the gate on a trial needs the current block's error, which the spare warp is computing meanwhile: before the
+    // barrier a trial thread only looks its candidate up and sums its table entries
+    if (tid < 256 && tid < n_win) {
+      const uint32_t pi = bi - 1 - tid;
+      const ub::Bits128 prev = to_bits(s_ring[pi & 255u]);
+      uint64_t slo, shi;
+      ub::rdo_get_sel(prev, first, total, slo, shi);
+      const int64_t h = ub::rdo_hist_find(hist, ch.hist_mask, first, slo);
+      const uint32_t match = h >= 0 ? (uint32_t)h : pi;
+      if (match <= pi) { my_err = ub::rdo_fast_error(s_table, f, slo, shi); my_k = tid; my_match = match; }
+    }
+    __syncthreads();
+    const ub::RdoCur c = s_cur;
+    if (!c.skip && tid < 256) {
+      if (my_k != 0xFFFFFFFFu) {
+        const float ms = ub::rdo_ms_err(my_err);
+        if (!(ub::f_sqrt(ms) > ub::f_mul(c.rms_err, p.max_rms_ratio))) {
+          const float t = ub::f_add(ub::f_mul(ms, c.smooth), ub::f_mul((float)(int)ub::rdo_match_cost((bi - my_match) * 16u), p.lambda));
+          my_key = ((unsigned long long)__float_as_uint(t) << 32) | my_k;
+        }
+      }
+      for (uint32_t k = tid + 256; k < n_win; k += 256) {  // window larger than the ring: read the blocks from global
+        const uint32_t pi = bi - 1 - k;
+        const ub::Bits128 prev = to_bits(blocks[pi]);
+        uint64_t slo, shi;
+        ub::rdo_get_sel(prev, first, total, slo, shi);
+        const int64_t h = ub::rdo_hist_find(hist, ch.hist_mask, first, slo);
+        const uint32_t match = h >= 0 ? (uint32_t)h : pi;
+        if (match > pi) continue;
+        float t;
+        if (!ub::rdo_trial_fast(s_table, f, slo, shi, c, bi, match, p, t)) continue;
+        const unsigned long long key = ((unsigned long long)__float_as_uint(t) << 32) | k;
+        my_key = key < my_key ? key : my_key;
+      }
+      if (my_key != ~0ull) atomicMin(&s_best, my_key);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      ub::Bits128 best = blk;
+      uint64_t key_lo = c.sel_lo;
+      if (!c.skip) {
+        const unsigned long long w = s_best;
+        if (w != ~0ull && __uint_as_float((uint32_t)(w >> 32)) < s_keep_t) {
+          const uint32_t pi = bi - 1 - (uint32_t)(w & 0xFFFFFFFFu);
+          const ub::Bits128 prev = (bi - pi <= 256) ? to_bits(s_ring[pi & 255u]) : to_bits(blocks[pi]);
+          best = ub::rdo_splice(blk, prev, first, total);
+          if (p.refine && f.mode == 0) best = ub::rdo_refine_mode0(s_px, best);
+          blocks[bi] = from_bits(best);
+          modified[bi] = 1;
+          uint64_t hi;
+          ub::rdo_get_sel(best, first, total, key_lo, hi);
+        }
+      }
+      ub::rdo_hist_set(hist, ch.hist_mask, first, key_lo, bi);
+      s_ring[bi & 255u] = from_bits(best);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, const uint4* __restrict__ px, const uint8_t* __restrict__ modified,
+                                                    uint64_t n, uint32_t flags) {
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    if (!modified[i]) continue;
+    uint32_t p[16];
+#pragma unroll
+    for (uint32_t y = 0; y < 4; y++) {
+      const uint4 v = __ldg(px + i * 4 + y);
+      p[4 * y] = v.x; p[4 * y + 1] = v.y; p[4 * y + 2] = v.z; p[4 * y + 3] = v.w;
+    }
+    blocks[i] = from_bits(ub::rdo_rehint(p, to_bits(blocks[i]), flags));
+  }
+}
+
 const int ENC_THREADS = 128;
 const int MAXC_FAST = 21, MAXC_FULL = 170;
 
@@ -286,6 +483,131 @@ int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n
     k_transcode_tiled<1><<<grid, XT_THREADS, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
   g_launches++;
   CU(cudaGetLastError());
+  return B200_OK;
+}
+
+// The RDO post-pass over n device-resident blocks that form `n_images` consecutive images (image i holds
+// img_blocks[i] blocks; job ranges never cross an image, ENC/basisu_comp.cpp:1574 calls uastc_rdo per slice).
+int rdo_run(uint4* d_blocks, const uint4* d_px, const std::vector<uint64_t>& img_blocks, const b200_uastc_params& prm, cudaStream_t st) {
+  ub::RdoParams p;
+  p.lambda = prm.rdo_lambda > 0.0f ? prm.rdo_lambda : 1.0f;
+  p.max_rms_ratio = 10.0f;   // UASTC_RDO_DEFAULT_MAX_ALLOWED_RMS_INCREASE_RATIO (libktx does not expose it)
+  p.skip_rms = 8.0f;         // UASTC_RDO_DEFAULT_SKIP_BLOCK_RMS_THRESH
+  p.smooth_scale = prm.rdo_max_smooth_block_error_scale > 0.0f ? prm.rdo_max_smooth_block_error_scale : 10.0f;
+  p.smooth_std_dev = prm.rdo_max_smooth_block_std_dev > 0.0f ? prm.rdo_max_smooth_block_std_dev : 18.0f;
+  const uint32_t dict = prm.rdo_dict_size ? prm.rdo_dict_size : 4096u;
+  p.window = std::max<uint32_t>(1u, dict / 16u);
+  p.literal_cost = 100; p.flags = prm.pack_flags; p.refine = 1;
+
+  std::vector<RdoChain> chains;
+  uint64_t base = 0, hist_total = 0, n_total = 0;
+  uint32_t longest = 0;
+  for (uint64_t nb : img_blocks) {
+    uint32_t per;
+    const uint32_t jobs = ub::rdo_job_ranges((uint32_t)nb, prm.rdo_total_jobs, &per);
+    for (uint32_t j = 0; j < jobs; j++) {
+      RdoChain c;
+      c.first = (uint32_t)(base + (uint64_t)j * per);
+      c.last = (uint32_t)(base + std::min<uint64_t>(nb, (uint64_t)(j + 1) * per));
+      uint32_t cap = 16;
+      while (cap < 2 * (c.last - c.first) + 16) cap <<= 1;
+      c.hist_off = hist_total; c.hist_mask = cap - 1; c.pad = 0;
+      hist_total += cap;
+      longest = std::max(longest, c.last - c.first);
+      chains.push_back(c);
+    }
+    base += nb;
+  }
+  n_total = base;
+  if (n_total >= 0xFFFFFFFFull) return fail(B200_E_INVALID_VALUE, "too many blocks for one RDO call");
+  if (chains.empty()) return B200_OK;
+  const uint32_t nc = (uint32_t)chains.size();
+
+  RdoChain* d_chains = nullptr; ub::RdoHistEntry* d_hist = nullptr; ub::RdoBlockInfo* d_info = nullptr;
+  uint32_t* d_tables = nullptr; uint8_t* d_mod = nullptr; unsigned int* d_err = nullptr;
+  auto cleanup = [&]() { cudaFree(d_chains); cudaFree(d_hist); cudaFree(d_info); cudaFree(d_tables); cudaFree(d_mod); cudaFree(d_err); };
+  cudaError_t e = cudaSuccess;
+  if (e == cudaSuccess) e = cudaMalloc(&d_chains, nc * sizeof(RdoChain));
+  if (e == cudaSuccess) e = cudaMalloc(&d_hist, hist_total * sizeof(ub::RdoHistEntry));
+  if (e == cudaSuccess) e = cudaMalloc(&d_info, (size_t)nc * RDO_CHUNK * sizeof(ub::RdoBlockInfo));
+  if (e == cudaSuccess) e = cudaMalloc(&d_tables, (size_t)nc * RDO_CHUNK * ub::RDO_TABLE_WORDS * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&d_mod, n_total);
+  if (e == cudaSuccess) e = cudaMalloc(&d_err, 4);
+  if (e != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc RDO state", e); }
+  cudaMemcpyAsync(d_chains, chains.data(), nc * sizeof(RdoChain), cudaMemcpyHostToDevice, st);
+  cudaMemsetAsync(d_hist, 0, hist_total * sizeof(ub::RdoHistEntry), st);
+  cudaMemsetAsync(d_mod, 0, n_total, st);
+  cudaMemsetAsync(d_err, 0, 4, st);
+  for (uint32_t step0 = 0; step0 < longest; step0 += RDO_CHUNK) {
+    const uint64_t warps = (uint64_t)nc * RDO_CHUNK;
+    k_rdo_prep<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(d_blocks, d_px, d_chains, nc, step0, d_info, d_tables, d_err);
+    k_rdo_chain<<<nc, RDO_THREADS, 0, st>>>(d_blocks, d_px, d_chains, step0, d_info, d_tables, d_hist, d_mod, p);
+    g_launches += 2;
+  }
+  k_rdo_rehint<<<(unsigned)std::min<uint64_t>((n_total + 127) / 128, (uint64_t)g_ctx.sm_count * 64), 128, 0, st>>>(d_blocks, d_px, d_mod, n_total, prm.pack_flags);
+  g_launches++;
+  unsigned int h_err = 0;
+  e = cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  cleanup();
+  if (e != cudaSuccess) return fail(B200_E_CUDA, "RDO pipeline", e);
+  if (h_err) return fail(B200_E_BAD_BLOCK, "RDO: an input block does not unpack");
+  return B200_OK;
+}
+
+// Encode + RDO for a host call: every image's texel blocks and UASTC blocks stay resident (64 + 16 B per block) so the
+// post-pass can walk them; job ranges are per image, all ranges of all images walk concurrently.
+int encode_with_rdo(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
+                    uint32_t* out_any_alpha, cudaStream_t* ss) {
+  std::vector<uint64_t> nb(n_images);
+  uint64_t total = 0;
+  size_t max_in = 0;
+  for (uint32_t i = 0; i < n_images; i++) {
+    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * 4;
+    if (pitch < (size_t)images[i].width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+    nb[i] = (uint64_t)((images[i].width + 3) / 4) * ((images[i].height + 3) / 4);
+    total += nb[i];
+    max_in = std::max(max_in, pitch * images[i].height);
+  }
+  uint8_t* d_img = nullptr; uint4* d_px = nullptr; uint4* d_blk = nullptr; unsigned int* d_alpha = nullptr;
+  auto cleanup = [&]() { cudaFree(d_img); cudaFree(d_px); cudaFree(d_blk); cudaFree(d_alpha); };
+  cudaError_t e = cudaMalloc(&d_img, max_in);
+  if (e == cudaSuccess) e = cudaMalloc(&d_px, total * 64);
+  if (e == cudaSuccess) e = cudaMalloc(&d_blk, total * 16);
+  if (e == cudaSuccess) e = cudaMalloc(&d_alpha, 4);
+  if (e != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc RDO buffers", e); }
+  cudaStream_t st = ss[1];
+  cudaMemsetAsync(d_alpha, 0, 4, st);
+  const bool full = (params->pack_flags & 7u) >= 4u;
+  uint64_t off = 0;
+  for (uint32_t i = 0; i < n_images && e == cudaSuccess; i++) {
+    const b200_image& im = images[i];
+    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
+    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
+    e = cudaMemcpyAsync(d_img, im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) break;
+    k_gather_blocks<<<(unsigned)std::min<uint64_t>((nb[i] + 255) / 256, (uint64_t)g_ctx.sm_count * 16), 256, 0, st>>>(d_img, im.width, im.height, pitch, d_px + off * 4, bx, by, d_alpha);
+    if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(nb[i]), ENC_THREADS, 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
+    else k_encode_blocks<MAXC_FAST><<<encode_grid(nb[i]), ENC_THREADS, 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
+    g_launches += 2;
+    off += nb[i];
+  }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) { cleanup(); return fail(B200_E_CUDA, "encode before RDO", e); }
+  int rc = rdo_run(d_blk, d_px, nb, *params, st);
+  if (rc) { cleanup(); return rc; }
+  off = 0;
+  for (uint32_t i = 0; i < n_images && e == cudaSuccess; i++) {
+    e = cudaMemcpyAsync(out_blocks[i], d_blk + off, nb[i] * 16, cudaMemcpyDeviceToHost, st);
+    off += nb[i];
+  }
+  unsigned int h_alpha = 0;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&h_alpha, d_alpha, 4, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cleanup();
+  if (e != cudaSuccess) return fail(B200_E_CUDA, "RDO download", e);
+  if (out_any_alpha) *out_any_alpha = h_alpha ? 1u : 0u;
   return B200_OK;
 }
 
@@ -497,12 +819,23 @@ int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t hei
   return B200_OK;
 }
 
+int b200_uastc_rdo_blocks_dev(void* d_blocks, const void* d_block_pixels, uint64_t n_blocks, const b200_uastc_params* params, void* stream) {
+  if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
+  if (n_blocks && (!d_blocks || !d_block_pixels)) return fail(B200_E_INVALID_VALUE, "null device pointer");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  if (!n_blocks) return B200_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
+  std::vector<uint64_t> nb(1, n_blocks);
+  return rdo_run((uint4*)d_blocks, (const uint4*)d_block_pixels, nb, *params, st);
+}
+
 int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
                       uint32_t* out_any_alpha) {
   if (out_any_alpha) *out_any_alpha = 0;
   if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
   if (n_images && (!images || !out_blocks)) return fail(B200_E_INVALID_VALUE, "null pointer");
-  if (params->rdo_enable) return fail(B200_E_INVALID_VALUE, "UASTC RDO is not built yet");
   for (uint32_t i = 0; i < n_images; i++)
     if (!images[i].rgba || !images[i].width || !images[i].height || !out_blocks[i]) return fail(B200_E_INVALID_VALUE, "bad image");
   int rc = b200_uastc_init();
@@ -511,6 +844,7 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   rc = get_streams(&ss);
   if (rc) return rc;
   if (!n_images) return B200_OK;
+  if (params->rdo_enable) return encode_with_rdo(images, n_images, params, out_blocks, out_any_alpha, ss);
 
   // Slab list: every image is cut into runs of whole block rows (contiguous in the RGBA source and in the UASTC
   // output) of at most SLAB_BYTES of input, so upload, encode and download of neighbouring slabs overlap on three

@@ -151,6 +151,81 @@ UB_FN void rdo_hist_set(RdoHistEntry* tab, uint32_t mask, uint32_t ofs, uint64_t
   }
 }
 
+// ---- fast trial scoring.  A trial differs from the current block only in its weights, and both decodes (UASTC, and
+// BC7 after transcoding) are per-texel functions of that texel's own weight(s): endpoints, partition, p-bits and the
+// BC7 anchor normalisation do not depend on the other texels.  So the error of ANY trial is a sum of per-texel table
+// entries  E[texel][plane][weight] = uastc_err + bc7_err of that texel (plane 1 = the dual-plane channel), built once
+// per block by decoding the block with all weights set to each level in turn -- through the very same
+// decode / transcode / BC7-decode code, so the tables are exact by construction.
+struct RdoBlockInfo {
+  uint8_t mode, wb, planes, npos;  // npos = anchor MSBs to re-insert into the selector field
+  uint8_t pos[3];                  // their bit positions, ascending
+  uint8_t valid;                   // 0 = the block does not unpack; solid blocks have mode == 8
+};
+const uint32_t RDO_TABLE_WORDS = 512;  // 16 texels x planes x levels <= 512 (mode 18: 16 x 1 x 32; dual plane: 16 x 2 x 4)
+
+UB_FN uint32_t rdo_table_index(const RdoBlockInfo& f, uint32_t texel, uint32_t plane, uint32_t w) {
+  return ((texel * f.planes + plane) << f.wb) + w;
+}
+
+UB_FN bool rdo_block_info(const Bits128& blk, RdoBlockInfo& f, UnpackedUastc& u) {
+  memset(&f, 0, sizeof(f));
+  if (!unpack_uastc(blk, u, false)) return false;
+  f.valid = 1; f.mode = (uint8_t)u.mode;
+  if (u.mode == UASTC_MODE_SOLID) return true;
+  const uint32_t wb = md_weight_bits(u.desc), subsets = md_subsets(u.desc);
+  f.wb = (uint8_t)wb; f.planes = (uint8_t)(1 + md_dual_plane(u.desc));
+  if (f.planes == 2) { f.npos = 2; f.pos[0] = (uint8_t)(wb - 1); f.pos[1] = (uint8_t)(2 * wb - 1); }
+  else {
+    uint32_t a0 = u.anchors & 15, a1 = (u.anchors >> 4) & 15, a2 = (u.anchors >> 8) & 15, t;
+    if (subsets == 1) { f.npos = 1; f.pos[0] = (uint8_t)(wb - 1); }
+    else if (subsets == 2) {
+      if (a0 > a1) { t = a0; a0 = a1; a1 = t; }
+      f.npos = 2; f.pos[0] = (uint8_t)(a0 * wb + wb - 1); f.pos[1] = (uint8_t)(a1 * wb + wb - 1);
+    } else {
+      if (a0 > a1) { t = a0; a0 = a1; a1 = t; }
+      if (a1 > a2) { t = a1; a1 = a2; a2 = t; }
+      if (a0 > a1) { t = a0; a0 = a1; a1 = t; }
+      f.npos = 3; f.pos[0] = (uint8_t)(a0 * wb + wb - 1); f.pos[1] = (uint8_t)(a1 * wb + wb - 1); f.pos[2] = (uint8_t)(a2 * wb + wb - 1);
+    }
+  }
+  return true;
+}
+
+// Table column for one weight level: decode the block with every weight (both planes) set to `level`.
+UB_BIG void rdo_fill_level(const uint32_t* px, const UnpackedUastc& u, const RdoBlockInfo& f, uint32_t level, uint32_t* table) {
+  Candidate c;
+  c.mode = u.mode; c.pattern = u.pattern; c.ccs = u.ccs;
+  for (uint32_t i = 0; i < 18; i++) c.ep[i] = u.ep[i];
+  for (uint32_t i = 0; i < 32; i++) c.w[i] = (uint8_t)level;
+  uint32_t du[16], db[16];
+  decode_uastc_pixels(c, du);
+  UnpackedUastc t;
+  candidate_to_unpacked(c, t);
+  Bc7Build bb;
+  uastc_to_bc7_build(t, bb);
+  const Bits128 bc7 = bc7_pack(bb);
+  decode_bc7_pixels(bc7, db);
+  const uint32_t m1 = (f.planes == 2) ? (255u << (8 * u.ccs)) : 0u;  // the channel plane 1 drives
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t p = px[i];
+    table[rdo_table_index(f, i, 0, level)] = sqdist4(p & ~m1, du[i] & ~m1) + sqdist4(p & ~m1, db[i] & ~m1);
+    if (f.planes == 2) table[rdo_table_index(f, i, 1, level)] = sqdist4(p & m1, du[i] & m1) + sqdist4(p & m1, db[i] & m1);
+  }
+}
+
+// (uastc_err + bc7_err) / 2 of the block whose selector field holds (lo, hi), from the block's table
+UB_FN uint64_t rdo_fast_error(const uint32_t* table, const RdoBlockInfo& f, uint64_t lo, uint64_t hi) {
+  Bits128 w;
+  w.lo = lo; w.hi = hi;
+  for (uint32_t k = 0; k < 3; k++) if (k < f.npos) w = bits_insert0(w, f.pos[k]);
+  uint32_t total = 0;
+  const uint32_t n = 16u * f.planes, wb = f.wb;
+  for (uint32_t e = 0; e < 32; e++)
+    if (e < n) total += table[(e << wb) + bits_get(w, e * wb, wb)];  // e = texel * planes + plane
+  return (uint64_t)(total >> 1);
+}
+
 // ---- the pieces of one step of the walk
 
 // What the walk needs to know about the current block before the trials are judged (:3836-3928).
@@ -176,6 +251,31 @@ UB_FN bool rdo_prepare(const uint32_t* px, const Bits128& blk, const RdoParams& 
   uint64_t hi;
   rdo_get_sel(blk, c.first, c.total, c.sel_lo, hi);
   c.skip = (c.rms_err >= p.skip_rms);
+  return true;
+}
+
+// Same, from the block's table (the drivers use this one; rdo_prepare is kept as the definition it must agree with).
+UB_FN void rdo_prepare_fast(const uint32_t* px, const Bits128& blk, const RdoBlockInfo& f, const uint32_t* table, const RdoParams& p, RdoCur& c) {
+  c.mode = f.mode; c.solid = (f.mode == UASTC_MODE_SOLID); c.skip = false;
+  c.first = UBT(rdo_sel_bits)[c.mode * 2]; c.total = UBT(rdo_sel_bits)[c.mode * 2 + 1];
+  c.sel_lo = 0; c.ms_err = 0; c.rms_err = 0; c.smooth = 1.0f;
+  if (c.solid) return;
+  c.smooth = rdo_smooth_scale(px, p);
+  uint64_t hi;
+  rdo_get_sel(blk, c.first, c.total, c.sel_lo, hi);
+  c.ms_err = rdo_ms_err(rdo_fast_error(table, f, c.sel_lo, hi));
+  c.rms_err = f_sqrt(c.ms_err);
+  c.skip = (c.rms_err >= p.skip_rms);
+}
+
+// One trial from the table: prev's selector bits (slo, shi) spliced into the current block.
+UB_FN bool rdo_trial_fast(const uint32_t* table, const RdoBlockInfo& f, uint64_t slo, uint64_t shi, const RdoCur& c,
+                          uint32_t block_index, uint32_t match_index, const RdoParams& p, float& t) {
+  const float ms = rdo_ms_err(rdo_fast_error(table, f, slo, shi));
+  const float rms = f_sqrt(ms);
+  if (rms > f_mul(c.rms_err, p.max_rms_ratio)) return false;
+  const uint32_t bits = rdo_match_cost((block_index - match_index) * 16u);
+  t = f_add(f_mul(ms, c.smooth), f_mul((float)(int)bits, p.lambda));
   return true;
 }
 
@@ -256,7 +356,7 @@ UB_BIG Bits128 rdo_rehint(const uint32_t* px, const Bits128& blk, uint32_t flags
 
 // Job ranges of one image (:4117-4135): total_jobs ranges of n/total_jobs blocks plus a remainder range; one range
 // when there is no pool, one job, or ranges would hold <= 8 blocks.
-UB_FN uint32_t rdo_job_ranges(uint32_t n, uint32_t total_jobs, uint32_t* blocks_per_job) {
+inline uint32_t rdo_job_ranges(uint32_t n, uint32_t total_jobs, uint32_t* blocks_per_job) {  // host-side planning
   const uint32_t per = total_jobs ? n / total_jobs : 0;
   if (total_jobs <= 1 || per <= 8) { *blocks_per_job = n; return n ? 1u : 0u; }
   *blocks_per_job = per;

@@ -51,6 +51,11 @@ PORT_API uint64_t port_ccc(const uint8_t* px, uint32_t n, uint32_t nw, uint32_t 
 #include "../ktx_software_b200/csrc/uastc_rdo.cuh"
 #include <vector>
 
+static int g_port_rdo_check = 0;
+static uint64_t g_port_rdo_mismatch = 0;
+// check = 1: every table-scored trial is also scored the direct way; returns the number of disagreements so far
+PORT_API uint64_t port_rdo_set_check(int check) { g_port_rdo_check = check; return g_port_rdo_mismatch; }
+
 static void port_rdo_range(uint8_t* blocks, const uint8_t* px, uint32_t first_index, uint32_t last_index, const ub::RdoParams& p) {
   uint32_t cap = 16;
   while (cap < 2 * (last_index - first_index) + 16) cap <<= 1;
@@ -63,7 +68,17 @@ static void port_rdo_range(uint8_t* blocks, const uint8_t* px, uint32_t first_in
     uint32_t pp[16];
     memcpy(pp, px + (size_t)bi * 64, 64);
     ub::RdoCur c;
-    if (!ub::rdo_prepare(pp, blk, p, c)) return;
+    ub::RdoBlockInfo info;
+    ub::UnpackedUastc un;
+    uint32_t table[ub::RDO_TABLE_WORDS];
+    if (!ub::rdo_block_info(blk, info, un)) return;
+    if (info.mode != ub::UASTC_MODE_SOLID)
+      for (uint32_t l = 0; l < (1u << info.wb); l++) ub::rdo_fill_level(pp, un, info, l, table);
+    ub::rdo_prepare_fast(pp, blk, info, table, p, c);
+    if (g_port_rdo_check) {  // the table path must agree with the direct definition
+      ub::RdoCur c2;
+      if (!ub::rdo_prepare(pp, blk, p, c2) || c2.ms_err != c.ms_err || c2.skip != c.skip || c2.sel_lo != c.sel_lo) { g_port_rdo_mismatch++; }
+    }
     if (c.solid) continue;
     if (c.skip) { ub::rdo_hist_set(hist.data(), mask, c.first, c.sel_lo, bi); continue; }
     float best_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist.data(), mask, c.first, c.sel_lo), bi, p);
@@ -79,9 +94,15 @@ static void port_rdo_range(uint8_t* blocks, const uint8_t* px, uint32_t first_in
       const int64_t match = h >= 0 ? h : pi;
       if (match > pi) continue;
       if (ub::UBT(uastc_huff_modes)[(uint32_t)prev.lo & 127u] >= ub::UASTC_TOTAL_MODES) return;  // unpack of prev failed
-      float t; ub::Bits128 trial;
-      if (!ub::rdo_trial(pp, blk, prev, c, bi, (uint32_t)match, p, t, trial)) continue;
-      if (t < best_t) { best_t = t; best = trial; modified = true; }
+      float t;
+      const bool ok = ub::rdo_trial_fast(table, info, slo, shi, c, bi, (uint32_t)match, p, t);
+      if (g_port_rdo_check) {
+        float t2; ub::Bits128 tr2;
+        const bool ok2 = ub::rdo_trial(pp, blk, prev, c, bi, (uint32_t)match, p, t2, tr2);
+        if (ok2 != ok || (ok && t2 != t)) g_port_rdo_mismatch++;
+      }
+      if (!ok) continue;
+      if (t < best_t) { best_t = t; best = ub::rdo_splice(blk, prev, c.first, c.total); modified = true; }
     }
     if (modified) {
       if (p.refine && c.mode == 0) best = ub::rdo_refine_mode0(pp, best);

@@ -167,3 +167,33 @@ def test_constexpr_tables_match():
     br = nums(re.search(r"astc_bise_range, 63\) = \{(.*?)\};", tabs, re.S).group(1))
     assert nums(re.search(r"constexpr uint32_t t\[19\] = \{(.*?)\};", com, re.S).group(1)) == md
     assert nums(re.search(r"constexpr uint8_t t\[63\] = \{(.*?)\};", com, re.S).group(1)) == br
+
+
+# ---- RDO: the host walk over the product's per-block RDO pieces against the reference's uastc_rdo
+@needs_ref
+@pytest.mark.parametrize("flags,kw,jobs", [(2 | 512, {}, 4), (3, {"lam": 3.0}, 0), (2 | 8, {"lam": 2.0, "dict_size": 32768}, 4)])
+def test_port_rdo_matches_reference(flags, kw, jobs):
+    port = R.port()
+    port.port_rdo_set_check.restype = ctypes.c_uint64
+    before = port.port_rdo_set_check(1)      # also score every table-based trial the direct way
+    px = np.concatenate([R.ref_extract_blocks(R.img_mix(96, 96, 3)), R.adversarial_blocks(5, 12)])
+    u = R.ref_encode_blocks(px, flags)
+    want = R.ref_rdo(u, px, flags, 4, jobs, **kw)
+    got = R.port_rdo(u, px, flags, jobs, **kw)
+    assert (want != u).any(1).sum() > 10
+    assert (got == want).all()
+    assert port.port_rdo_set_check(0) == before, "table-based trial scoring disagreed with direct scoring"
+
+
+def test_rdo_match_cost_staircase():
+    """rdo_match_cost restates the reference's two deflate extra-bits tables arithmetically; pin a few known entries
+    (ENC/basisu_uastc_enc.cpp:3758-3774: small[4]=1, small[511]=7, large[2]=8, large[127]=13)."""
+    def cost(d):
+        if d < 512:
+            extra = 0 if d < 4 else d.bit_length() - 2
+        else:
+            extra = (min(d, 32767) >> 8).bit_length() - 1 + 7
+            while d >= 32768:
+                extra += 1; d >>= 1
+        return 12 + extra
+    assert [cost(d) for d in (0, 3, 4, 16, 511, 512, 1023, 1024, 32767, 32768, 65536)] == [12, 12, 13, 15, 19, 20, 20, 21, 25, 26, 27]
