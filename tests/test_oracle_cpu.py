@@ -176,7 +176,7 @@ def test_port_rdo_matches_reference(flags, kw, jobs):
     port = R.port()
     port.port_rdo_set_check.restype = ctypes.c_uint64
     before = port.port_rdo_set_check(1)      # also score every table-based trial the direct way
-    px = np.concatenate([R.ref_extract_blocks(R.img_mix(96, 96, 3)), R.adversarial_blocks(5, 12)])
+    px = np.concatenate([R.ref_extract_blocks(R.img_mix(128, 128, 3)), R.adversarial_blocks(5, 12)])
     u = R.ref_encode_blocks(px, flags)
     want = R.ref_rdo(u, px, flags, 4, jobs, **kw)
     got = R.port_rdo(u, px, flags, jobs, **kw)
