@@ -316,7 +316,8 @@ __device__ __forceinline__ uint4 from_bits(const ub::Bits128& b) {
 // chunk-local table slot of block `bi` of chain `c`: c * RDO_CHUNK + (bi - first - step0)
 __global__ void __launch_bounds__(256) k_rdo_prep(const uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
                                                   uint32_t n_chains, uint32_t step0, ub::RdoBlockInfo* __restrict__ info,
-                                                  uint32_t* __restrict__ tables, unsigned int* __restrict__ err_flag) {
+                                                  ub::RdoPre* __restrict__ pre, uint32_t* __restrict__ tables,
+                                                  unsigned int* __restrict__ err_flag, ub::RdoParams prm) {
   const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
   const uint32_t c = warp / RDO_CHUNK, k = warp % RDO_CHUNK;
   if (c >= n_chains) return;
@@ -334,19 +335,46 @@ __global__ void __launch_bounds__(256) k_rdo_prep(const uint4* __restrict__ bloc
   const bool ok = ub::rdo_block_info(blk, f, u);
   if (lane == 0) { info[(size_t)c * RDO_CHUNK + k] = f; if (!ok) atomicOr(err_flag, 1u); }
   if (!ok || f.mode == ub::UASTC_MODE_SOLID) return;
-  if (lane < (1u << f.wb)) ub::rdo_fill_level(p, u, f, lane, tables + ((size_t)c * RDO_CHUNK + k) * ub::RDO_TABLE_WORDS);
+  uint32_t* table = tables + ((size_t)c * RDO_CHUNK + k) * ub::RDO_TABLE_WORDS;
+  if (lane < (1u << f.wb)) ub::rdo_fill_level(p, u, f, lane, table);
+  __syncwarp();  // orders the lanes' table writes before lane 0's reads
+  if (lane == 0) {
+    ub::RdoCur cur;
+    ub::rdo_prepare_fast(p, blk, f, table, prm, cur);
+    pre[(size_t)c * RDO_CHUNK + k] = ub::rdo_pre_of(cur);
+  }
+}
+
+// hazard[bi] = 1 when a block of a mode that reads a mode-0 block's endpoint bits follows within the window in the
+// same chain (then a mode-0 endpoint re-fit at bi must happen inside the walk; otherwise it is postponed to k_rdo_rehint)
+__global__ void __launch_bounds__(256) k_rdo_hazard(const uint4* __restrict__ blocks, const RdoChain* __restrict__ chains, uint32_t n_chains,
+                                                    uint32_t window, uint8_t* __restrict__ hazard) {
+  const uint32_t c = blockIdx.y;
+  if (c >= n_chains) return;
+  const RdoChain ch = chains[c];
+  for (uint32_t bi = ch.first + blockIdx.x * blockDim.x + threadIdx.x; bi < ch.last; bi += gridDim.x * blockDim.x) {
+    uint8_t hz = 0;
+    if (ub::UBT(uastc_huff_modes)[blocks[bi].x & 127u] == 0) {
+      const uint32_t end = (uint32_t)min((uint64_t)ch.last, (uint64_t)bi + 1 + window);
+      for (uint32_t j = bi + 1; j < end; j++)
+        if (ub::rdo_mode_reads_mode0_endpoints(ub::UBT(uastc_huff_modes)[blocks[j].x & 127u])) { hz = 1; break; }
+    }
+    hazard[bi] = hz;
+  }
 }
 
 __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
                                                            uint32_t step0, const ub::RdoBlockInfo* __restrict__ info,
-                                                           const uint32_t* __restrict__ tables, ub::RdoHistEntry* __restrict__ hist_all,
+                                                           const ub::RdoPre* __restrict__ pre, const uint32_t* __restrict__ tables,
+                                                           ub::RdoHistEntry* __restrict__ hist_all, const uint8_t* __restrict__ hazard,
                                                            uint8_t* __restrict__ modified, ub::RdoParams p) {
-  __shared__ __align__(16) uint32_t s_table[ub::RDO_TABLE_WORDS];
+  // per-step inputs are double-buffered: while step bi is scored, the loads of step bi+1 are in flight
+  __shared__ __align__(16) uint32_t s_table[2][ub::RDO_TABLE_WORDS];
+  __shared__ __align__(16) uint32_t s_px[2][16];
+  __shared__ __align__(16) uint4 s_blk[2];
+  __shared__ __align__(16) ub::RdoPre s_pre[2];
+  __shared__ ub::RdoBlockInfo s_info[2];
   __shared__ __align__(16) uint4 s_ring[256];
-  __shared__ __align__(16) uint32_t s_px[16];
-  __shared__ uint4 s_blk;
-  __shared__ ub::RdoBlockInfo s_info;
-  __shared__ ub::RdoCur s_cur;
   __shared__ float s_keep_t;
   __shared__ unsigned long long s_best;
 
@@ -358,92 +386,95 @@ __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ b
   const uint32_t end = min(ch.last, begin + RDO_CHUNK);
   // refill the ring with the (final) blocks just before this chunk
   if (tid < 256) { const uint32_t back = tid + 1; if (begin >= ch.first + back) s_ring[(begin - back) & 255u] = blocks[begin - back]; }
+
+  // what each thread fetches for a step: 128 threads the table, 4 the texels, one each the block, info and pre-computed stats
+  uint4 nx = make_uint4(0, 0, 0, 0);
+  ub::RdoBlockInfo nx_info;
+  ub::RdoPre nx_pre;
+  auto fetch = [&](uint32_t bi) {
+    const size_t slot = (size_t)blockIdx.x * RDO_CHUNK + (bi - begin);
+    if (tid < 128) nx = __ldg((const uint4*)(tables + slot * ub::RDO_TABLE_WORDS) + tid);
+    else if (tid < 132) nx = __ldg(px + (size_t)bi * 4 + (tid - 128));
+    else if (tid == 132) nx = blocks[bi];
+    else if (tid == 133) nx_info = info[slot];
+    else if (tid == 134) nx_pre = pre[slot];
+  };
+  auto stash = [&](uint32_t b) {
+    if (tid < 128) ((uint4*)s_table[b])[tid] = nx;
+    else if (tid < 132) ((uint4*)s_px[b])[tid - 128] = nx;
+    else if (tid == 132) s_blk[b] = nx;
+    else if (tid == 133) s_info[b] = nx_info;
+    else if (tid == 134) s_pre[b] = nx_pre;
+  };
+  fetch(begin);
+  stash(0);
+  if (tid == 0) s_best = ~0ull;
   __syncthreads();
 
-  for (uint32_t bi = begin; bi < end; bi++) {
-    const size_t slot = (size_t)blockIdx.x * RDO_CHUNK + (bi - begin);
-    if (tid < 128) ((uint4*)s_table)[tid] = __ldg((const uint4*)(tables + slot * ub::RDO_TABLE_WORDS) + tid);
-    else if (tid < 132) ((uint4*)s_px)[tid - 128] = __ldg(px + (size_t)bi * 4 + (tid - 128));
-    else if (tid == 132) s_blk = blocks[bi];
-    else if (tid == 133) s_info = info[slot];
-    else if (tid == 134) s_best = ~0ull;
-    __syncthreads();
-    const ub::RdoBlockInfo f = s_info;
-    const ub::Bits128 blk = to_bits(s_blk);
-    if (f.mode == ub::UASTC_MODE_SOLID || !f.valid) {  // uniform: left alone, but later blocks may still splice from it
-      if (tid == 0) s_ring[bi & 255u] = s_blk;
-      __syncthreads();
-      continue;
-    }
+  uint32_t b = 0;
+  for (uint32_t bi = begin; bi < end; bi++, b ^= 1) {
+    if (bi + 1 < end) fetch(bi + 1);  // block bi+1 is not rewritten before its own step, so reading it now is safe
+    const ub::RdoBlockInfo f = s_info[b];
+    const ub::Bits128 blk = to_bits(s_blk[b]);
+    const bool active = f.valid && f.mode != ub::UASTC_MODE_SOLID;  // uniform; solid blocks are left alone but stay splice sources
     const uint32_t first = ub::UBT(rdo_sel_bits)[f.mode * 2], total = ub::UBT(rdo_sel_bits)[f.mode * 2 + 1];
-    const uint32_t lo_index = (bi - ch.first > p.window) ? bi - p.window : ch.first;
-    const uint32_t n_win = bi - lo_index;
-
-    // ---- score: thread k takes candidates k, k+256, ... (nearest first); the spare warp prepares the current block
-    uint64_t my_err = 0; uint32_t my_k = 0xFFFFFFFFu, my_match = 0;
-    unsigned long long my_key = ~0ull;
-    if (tid == 256) {
-      ub::RdoCur c;
-      ub::rdo_prepare_fast(s_px, blk, f, s_table, p, c);
-      s_cur = c;
-      s_keep_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist, ch.hist_mask, c.first, c.sel_lo), bi, p);
+    ub::RdoCur c;
+    {
+      const ub::RdoPre q = s_pre[b];
+      c.mode = f.mode; c.first = first; c.total = total; c.sel_lo = q.sel_lo;
+      c.ms_err = q.ms_err; c.rms_err = q.rms_err; c.smooth = q.smooth; c.solid = false; c.skip = q.skip != 0;
     }
-    // the gate on a trial needs the current block's error, which the spare warp is computing meanwhile: before the
-    // barrier a trial thread only looks its candidate up and sums its table entries
-    if (tid < 256 && tid < n_win) {
-      const uint32_t pi = bi - 1 - tid;
-      const ub::Bits128 prev = to_bits(s_ring[pi & 255u]);
-      uint64_t slo, shi;
-      ub::rdo_get_sel(prev, first, total, slo, shi);
-      const int64_t h = ub::rdo_hist_find(hist, ch.hist_mask, first, slo);
-      const uint32_t match = h >= 0 ? (uint32_t)h : pi;
-      if (match <= pi) { my_err = ub::rdo_fast_error(s_table, f, slo, shi); my_k = tid; my_match = match; }
-    }
-    __syncthreads();
-    const ub::RdoCur c = s_cur;
-    if (!c.skip && tid < 256) {
-      if (my_k != 0xFFFFFFFFu) {
-        const float ms = ub::rdo_ms_err(my_err);
-        if (!(ub::f_sqrt(ms) > ub::f_mul(c.rms_err, p.max_rms_ratio))) {
-          const float t = ub::f_add(ub::f_mul(ms, c.smooth), ub::f_mul((float)(int)ub::rdo_match_cost((bi - my_match) * 16u), p.lambda));
-          my_key = ((unsigned long long)__float_as_uint(t) << 32) | my_k;
+    if (active && !c.skip) {
+      const uint32_t lo_index = (bi - ch.first > p.window) ? bi - p.window : ch.first;
+      const uint32_t n_win = bi - lo_index;
+      // thread k takes candidates k, k+256, ... (k = 0 is the nearest earlier block); the spare warp prices "keep as is"
+      if (tid == 256) s_keep_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist, ch.hist_mask, first, c.sel_lo), bi, p);
+      if (tid < 256) {
+        unsigned long long my_key = ~0ull;
+        for (uint32_t k = tid; k < n_win; k += 256) {
+          const uint32_t pi = bi - 1 - k;
+          const ub::Bits128 prev = (k < 256) ? to_bits(s_ring[pi & 255u]) : to_bits(blocks[pi]);  // window beyond the ring: global
+          uint64_t slo, shi;
+          ub::rdo_get_sel(prev, first, total, slo, shi);
+          const int64_t h = ub::rdo_hist_find(hist, ch.hist_mask, first, slo);
+          const uint32_t match = h >= 0 ? (uint32_t)h : pi;
+          if (match > pi) continue;  // a later block already carries these bits: it was (or will be) tried instead
+          float t;
+          if (!ub::rdo_trial_fast(s_table[b], f, slo, shi, c, bi, match, p, t)) continue;
+          const unsigned long long key = ((unsigned long long)__float_as_uint(t) << 32) | k;  // t >= 0: bit order == value order
+          my_key = key < my_key ? key : my_key;
         }
+        if (my_key != ~0ull) atomicMin(&s_best, my_key);
       }
-      for (uint32_t k = tid + 256; k < n_win; k += 256) {  // window larger than the ring: read the blocks from global
-        const uint32_t pi = bi - 1 - k;
-        const ub::Bits128 prev = to_bits(blocks[pi]);
-        uint64_t slo, shi;
-        ub::rdo_get_sel(prev, first, total, slo, shi);
-        const int64_t h = ub::rdo_hist_find(hist, ch.hist_mask, first, slo);
-        const uint32_t match = h >= 0 ? (uint32_t)h : pi;
-        if (match > pi) continue;
-        float t;
-        if (!ub::rdo_trial_fast(s_table, f, slo, shi, c, bi, match, p, t)) continue;
-        const unsigned long long key = ((unsigned long long)__float_as_uint(t) << 32) | k;
-        my_key = key < my_key ? key : my_key;
-      }
-      if (my_key != ~0ull) atomicMin(&s_best, my_key);
+      __syncthreads();
     }
-    __syncthreads();
     if (tid == 0) {
       ub::Bits128 best = blk;
-      uint64_t key_lo = c.sel_lo;
-      if (!c.skip) {
-        const unsigned long long w = s_best;
-        if (w != ~0ull && __uint_as_float((uint32_t)(w >> 32)) < s_keep_t) {
-          const uint32_t pi = bi - 1 - (uint32_t)(w & 0xFFFFFFFFu);
-          const ub::Bits128 prev = (bi - pi <= 256) ? to_bits(s_ring[pi & 255u]) : to_bits(blocks[pi]);
-          best = ub::rdo_splice(blk, prev, first, total);
-          if (p.refine && f.mode == 0) best = ub::rdo_refine_mode0(s_px, best);
-          blocks[bi] = from_bits(best);
-          modified[bi] = 1;
-          uint64_t hi;
-          ub::rdo_get_sel(best, first, total, key_lo, hi);
+      if (active) {
+        uint64_t key_lo = c.sel_lo;
+        if (!c.skip) {
+          const unsigned long long w = s_best;
+          s_best = ~0ull;
+          if (w != ~0ull && __uint_as_float((uint32_t)(w >> 32)) < s_keep_t) {
+            const uint32_t pi = bi - 1 - (uint32_t)(w & 0xFFFFFFFFu);
+            const ub::Bits128 prev = (bi - pi <= 256) ? to_bits(s_ring[pi & 255u]) : to_bits(blocks[pi]);
+            best = ub::rdo_splice(blk, prev, first, total);
+            uint8_t mark = 1;
+            if (p.refine && f.mode == 0) {
+              if (hazard[bi]) best = ub::rdo_refine_mode0(s_px[b], best);  // a later block will read these endpoint bits
+              else mark = 2;                                               // re-fit postponed to k_rdo_rehint
+            }
+            blocks[bi] = from_bits(best);
+            modified[bi] = mark;
+            uint64_t hi;
+            ub::rdo_get_sel(best, first, total, key_lo, hi);
+          }
         }
+        ub::rdo_hist_set(hist, ch.hist_mask, first, key_lo, bi);
       }
-      ub::rdo_hist_set(hist, ch.hist_mask, first, key_lo, bi);
       s_ring[bi & 255u] = from_bits(best);
     }
+    if (bi + 1 < end) stash(b ^ 1);
     __syncthreads();
   }
 }
@@ -458,7 +489,9 @@ __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, 
       const uint4 v = __ldg(px + i * 4 + y);
       p[4 * y] = v.x; p[4 * y + 1] = v.y; p[4 * y + 2] = v.z; p[4 * y + 3] = v.w;
     }
-    blocks[i] = from_bits(ub::rdo_rehint(p, to_bits(blocks[i]), flags));
+    ub::Bits128 b = to_bits(blocks[i]);
+    if (modified[i] == 2) b = ub::rdo_refine_mode0(p, b);
+    blocks[i] = from_bits(ub::rdo_rehint(p, b, flags));
   }
 }
 
@@ -524,13 +557,15 @@ int rdo_run(uint4* d_blocks, const uint4* d_px, const std::vector<uint64_t>& img
   const uint32_t nc = (uint32_t)chains.size();
 
   RdoChain* d_chains = nullptr; ub::RdoHistEntry* d_hist = nullptr; ub::RdoBlockInfo* d_info = nullptr;
-  uint32_t* d_tables = nullptr; uint8_t* d_mod = nullptr; unsigned int* d_err = nullptr;
-  auto cleanup = [&]() { cudaFree(d_chains); cudaFree(d_hist); cudaFree(d_info); cudaFree(d_tables); cudaFree(d_mod); cudaFree(d_err); };
+  uint32_t* d_tables = nullptr; uint8_t* d_mod = nullptr; unsigned int* d_err = nullptr; ub::RdoPre* d_pre = nullptr; uint8_t* d_hz = nullptr;
+  auto cleanup = [&]() { cudaFree(d_chains); cudaFree(d_hist); cudaFree(d_info); cudaFree(d_tables); cudaFree(d_mod); cudaFree(d_err); cudaFree(d_pre); cudaFree(d_hz); };
   cudaError_t e = cudaSuccess;
   if (e == cudaSuccess) e = cudaMalloc(&d_chains, nc * sizeof(RdoChain));
   if (e == cudaSuccess) e = cudaMalloc(&d_hist, hist_total * sizeof(ub::RdoHistEntry));
   if (e == cudaSuccess) e = cudaMalloc(&d_info, (size_t)nc * RDO_CHUNK * sizeof(ub::RdoBlockInfo));
   if (e == cudaSuccess) e = cudaMalloc(&d_tables, (size_t)nc * RDO_CHUNK * ub::RDO_TABLE_WORDS * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&d_pre, (size_t)nc * RDO_CHUNK * sizeof(ub::RdoPre));
+  if (e == cudaSuccess) e = cudaMalloc(&d_hz, n_total);
   if (e == cudaSuccess) e = cudaMalloc(&d_mod, n_total);
   if (e == cudaSuccess) e = cudaMalloc(&d_err, 4);
   if (e != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc RDO state", e); }
@@ -538,10 +573,12 @@ int rdo_run(uint4* d_blocks, const uint4* d_px, const std::vector<uint64_t>& img
   cudaMemsetAsync(d_hist, 0, hist_total * sizeof(ub::RdoHistEntry), st);
   cudaMemsetAsync(d_mod, 0, n_total, st);
   cudaMemsetAsync(d_err, 0, 4, st);
+  k_rdo_hazard<<<dim3((unsigned)std::min<uint32_t>((longest + 255) / 256, 1024u), nc), 256, 0, st>>>(d_blocks, d_chains, nc, p.window, d_hz);
+  g_launches++;
   for (uint32_t step0 = 0; step0 < longest; step0 += RDO_CHUNK) {
     const uint64_t warps = (uint64_t)nc * RDO_CHUNK;
-    k_rdo_prep<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(d_blocks, d_px, d_chains, nc, step0, d_info, d_tables, d_err);
-    k_rdo_chain<<<nc, RDO_THREADS, 0, st>>>(d_blocks, d_px, d_chains, step0, d_info, d_tables, d_hist, d_mod, p);
+    k_rdo_prep<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(d_blocks, d_px, d_chains, nc, step0, d_info, d_pre, d_tables, d_err, p);
+    k_rdo_chain<<<nc, RDO_THREADS, 0, st>>>(d_blocks, d_px, d_chains, step0, d_info, d_pre, d_tables, d_hist, d_hz, d_mod, p);
     g_launches += 2;
   }
   k_rdo_rehint<<<(unsigned)std::min<uint64_t>((n_total + 127) / 128, (uint64_t)g_ctx.sm_count * 64), 128, 0, st>>>(d_blocks, d_px, d_mod, n_total, prm.pack_flags);

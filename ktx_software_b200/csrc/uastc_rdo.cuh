@@ -279,6 +279,23 @@ UB_FN bool rdo_trial_fast(const uint32_t* table, const RdoBlockInfo& f, uint64_t
   return true;
 }
 
+// The chain-independent part of RdoCur, computed ahead of the walk (a block is only rewritten at its own step, so its
+// own error, smoothness and selector bits are known before the walk reaches it).
+struct RdoPre {
+  float ms_err, rms_err, smooth;
+  uint32_t skip;
+  uint64_t sel_lo;
+};
+UB_FN RdoPre rdo_pre_of(const RdoCur& c) {
+  RdoPre r;
+  r.ms_err = c.ms_err; r.rms_err = c.rms_err; r.smooth = c.smooth; r.skip = c.skip ? 1u : 0u; r.sel_lo = c.sel_lo;
+  return r;
+}
+
+// Modes whose selector field starts below bit 65 read bits that are ENDPOINT bits in a mode-0 block: a mode-0 block's
+// endpoint re-fit may only be postponed past the walk if no such block follows it inside the window.
+UB_FN bool rdo_mode_reads_mode0_endpoints(uint32_t mode) { return mode < UASTC_TOTAL_MODES && mode != UASTC_MODE_SOLID && UBT(rdo_sel_bits)[mode * 2] < 65; }
+
 // cost of keeping the block as it is (:3917-3941): literal cost if its selector bits were never seen, else a match
 UB_FN float rdo_keep_cost(const RdoCur& c, int64_t hist_index, uint32_t block_index, const RdoParams& p) {
   int bits;
