@@ -59,7 +59,9 @@ UB_FN void decode_uastc_pixels(const Candidate& c, uint32_t* out) {
     }
   }
   uint32_t colors[3][32];
+#pragma unroll 1
   for (uint32_t s = 0; s < subsets; s++)
+#pragma unroll 1
     for (uint32_t l = 0; l < levels; l++) {
       const uint32_t w = sel_weight_bits(wb, l);
       uint32_t v = 0;
@@ -71,6 +73,7 @@ UB_FN void decode_uastc_pixels(const Candidate& c, uint32_t* out) {
       colors[s][l] = v;
     }
   const uint32_t pat = cand_pat(c, d);
+#pragma unroll 1
   for (uint32_t i = 0; i < 16; i++) {
     if (planes == 1) {
       out[i] = colors[(pat >> (2 * i)) & 3u][c.w[i]];
@@ -142,6 +145,66 @@ UB_FN bool decode_bc7_pixels(const Bits128& b, uint32_t* out) {
     out[i] = v;
   }
   return true;
+}
+
+// Texels of the BC7 block a Bc7Build describes, without packing it first.  encode_bc7_block's anchor normalisation
+// (swap a subset's endpoints + p-bits, invert its selectors) does not change what the block decodes to, because the
+// BC7 weight tables are symmetric (w[max - i] == 64 - w[i]); everything else it does is serialisation.  So this equals
+// decode_bc7_pixels(bc7_pack(o)) -- the encoder's candidate scoring and the RDO tables use it to skip both steps.
+UB_FN void decode_bc7_build(const Bc7Build& o, uint32_t* out) {
+  const uint32_t m = o.mode;
+  const uint32_t subsets = bc7_subsets(m), ib = bc7_index_bits(m);
+  const uint32_t cp = bc7_color_prec(m), ap = bc7_alpha_prec(m);
+  const bool has_p = (m == 1 || m == 3 || m == 6 || m == 7);
+  uint32_t lo[3], hi[3];
+#pragma unroll
+  for (uint32_t k = 0; k < 3; k++) {
+    uint32_t l = 0xFF000000u, h = 0xFF000000u;
+    if (k < subsets) {
+      const uint32_t pl = (o.pbits >> (2 * k)) & 1u, ph = (m == 1) ? pl : ((o.pbits >> (2 * k + 1)) & 1u);
+      l = 0; h = 0;
+#pragma unroll
+      for (uint32_t c = 0; c < 4; c++) {
+        uint32_t a = 255, b = 255;
+        if (c < 3 || m >= 4) {
+          const uint32_t nb = (c == 3) ? ap : cp;
+          a = px_c(o.lo[k], c); b = px_c(o.hi[k], c);
+          if (has_p) { a = bc7_dq((a << 1) | pl, nb + 1); b = bc7_dq((b << 1) | ph, nb + 1); }
+          else { a = bc7_dq(a, nb); b = bc7_dq(b, nb); }
+        }
+        l |= a << (8 * c); h |= b << (8 * c);
+      }
+    }
+    lo[k] = l; hi[k] = h;
+  }
+  uint32_t pat = 0;
+  if (subsets == 2) pat = spread_mask2(UBT(bc7_part2)[o.partition]);
+  else if (subsets == 3) pat = UBT(bc7_part3)[o.partition];
+  const uint32_t wmask = (1u << ib) - 1u;
+#pragma unroll 1
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t s = (pat >> (2 * i)) & 3u;
+    const uint32_t l = s == 0 ? lo[0] : (s == 1 ? lo[1] : lo[2]), h = s == 0 ? hi[0] : (s == 1 ? hi[1] : hi[2]);
+    const uint32_t w = bc7_w(ib, (uint32_t)(o.sel >> (i * ib)) & wmask);
+    uint32_t v;
+    if (m == 5) {
+      const uint32_t wa = UBT(bc7_weights2)[(uint32_t)(o.asel >> (i * 2)) & 3u];
+      uint32_t p[4];
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) p[c] = bc7_lerp(px_c(l, c), px_c(h, c), w);
+      p[3] = bc7_lerp(px_c(l, 3), px_c(h, 3), wa);
+      const uint32_t rot = o.rotation;
+      if (rot >= 1) {  // swap alpha with channel rot-1
+        const uint32_t t = p[3];
+        if (rot == 1) { p[3] = p[0]; p[0] = t; } else if (rot == 2) { p[3] = p[1]; p[1] = t; } else { p[3] = p[2]; p[2] = t; }
+      }
+      v = p[0] | (p[1] << 8) | (p[2] << 16) | (p[3] << 24);
+    } else {
+      v = bc7_lerp(px_c(l, 0), px_c(h, 0), w) | (bc7_lerp(px_c(l, 1), px_c(h, 1), w) << 8) | (bc7_lerp(px_c(l, 2), px_c(h, 2), w) << 16);
+      v |= ((m >= 4) ? bc7_lerp(px_c(l, 3), px_c(h, 3), w) : 255u) << 24;
+    }
+    out[i] = v;
+  }
 }
 
 }  // namespace ub

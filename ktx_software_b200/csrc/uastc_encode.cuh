@@ -207,8 +207,7 @@ UB_BIG void score_candidate(const uint32_t* px, const Candidate& c, bool has_alp
   candidate_to_unpacked(c, u);
   Bc7Build bb;
   uastc_to_bc7_build(u, bb);
-  const Bits128 bc7 = bc7_pack(bb);
-  decode_bc7_pixels(bc7, dec);
+  decode_bc7_build(bb, dec);  // == decode_bc7_pixels(bc7_pack(bb)), see uastc_decode.cuh
   block_error(px, dec, b_rgb, b_rgba, b_la);
   ue = is_la ? u_la : (has_alpha ? u_rgba : u_rgb);
   be = is_la ? b_la : (has_alpha ? b_rgba : b_rgb);

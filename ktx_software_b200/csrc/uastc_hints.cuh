@@ -198,6 +198,8 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
       for (uint32_t s = 0; s < 2; s++)
 #pragma unroll
         for (uint32_t c = 0; c < 3; c++) unb[s][c] = (int)((avg[s][c] * mul + 1020u) / (8u * 255u));
+      uint32_t memo_key[2][2] = {{0, 0}, {0, 0}}, memo_inten[2][2] = {{0, 0}, {0, 0}};
+      uint64_t memo_err[2][2] = {{0, 0}, {0, 0}};
 #pragma unroll 1
       for (uint32_t bi = 0; bi < last_bias; bi++) {
         const uint32_t bias = use_table ? UBT(etc1_sorted_bias)[bi] : bi;
@@ -221,6 +223,12 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
 #pragma unroll 1
         for (uint32_t s = 0; s < 2; s++) {
           const int* b8 = s ? base8[1] : base8[0];
+          // The result for a sub-block depends only on its base colour (given flip and the decoded texels).  Many
+          // bias modes leave one sub-block's base colour untouched, so remember the first and the latest evaluation.
+          const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
+          uint32_t hit = 2;
+          if (memo_key[s][0] == key) hit = 0; else if (memo_key[s][1] == key) hit = 1;
+          if (hit < 2) { best_inten[s] = memo_inten[s][hit]; err += memo_err[s][hit]; continue; }
           int range = 0;
 #pragma unroll
           for (uint32_t c = 0; c < 3; c++) {
@@ -232,9 +240,9 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
           const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
           // chroma distance of every texel to the (unclamped) base colour, shared by all table entries that do not clamp
           const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
-          uint64_t kj[8];
+          uint64_t kj[8], ksum = 0;
 #pragma unroll 1
-          for (uint32_t j = 0; j < 8; j++) kj[j] = chroma_d(by, dec_y[etc1_texel(flip, s, j)]);
+          for (uint32_t j = 0; j < 8; j++) { kj[j] = chroma_d(by, dec_y[etc1_texel(flip, s, j)]); ksum += kj[j]; }
           uint64_t best_sub = ~0ull;
           uint32_t bi_s = 0;
 #pragma unroll 1
@@ -242,17 +250,30 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
             Ycc2 tab[4];
             const uint32_t clamped = etc1_subblock_ycc(b8, it, tab);
             uint64_t total = 0;
+            if (!clamped) {
+              // all four entries share the base chroma: only luma separates them, and (dy)^2 fits 32 bits
 #pragma unroll 1
-            for (uint32_t j = 0; j < 8; j++) {
-              const Ycc2 c = dec_y[etc1_texel(flip, s, j)];
-              uint64_t m = ~0ull;
+              for (uint32_t j = 0; j < 8; j++) {
+                const int cy = dec_y[etc1_texel(flip, s, j)].y2;
+                uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-              for (uint32_t k = 0; k < 4; k++) {
-                uint64_t e = sq64(tab[k].y2 - c.y2);
-                if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
-                m = e < m ? e : m;
+                for (uint32_t k = 0; k < 4; k++) { const int d = (tab[k].y2 - cy) >> 1; const uint32_t e = (uint32_t)(d * d); m = e < m ? e : m; }
+                total += m;
               }
-              total += m;
+              total = total * 4 + ksum;
+            } else {
+#pragma unroll 1
+              for (uint32_t j = 0; j < 8; j++) {
+                const Ycc2 c = dec_y[etc1_texel(flip, s, j)];
+                uint64_t m = ~0ull;
+#pragma unroll
+                for (uint32_t k = 0; k < 4; k++) {
+                  uint64_t e = sq64(tab[k].y2 - c.y2);
+                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
+                  m = e < m ? e : m;
+                }
+                total += m;
+              }
             }
             // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
             if (!flip && total >= best_sub) break;
@@ -262,21 +283,32 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
           // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones)
           Ycc2 tab[4];
           const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+          uint64_t err_s = 0;
 #pragma unroll 1
           for (uint32_t j = 0; j < 8; j++) {
             const uint32_t t = etc1_texel(flip, s, j);
             const Ycc2 c = dec_y[t];
-            uint64_t m = ~0ull;
             uint32_t bk = 0;
+            if (!clamped) {
+              uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-            for (uint32_t k = 0; k < 4; k++) {
-              uint64_t e = sq64(tab[k].y2 - c.y2);
-              if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
-              if (e < m) { m = e; bk = k; }
+              for (uint32_t k = 0; k < 4; k++) { const int d = (tab[k].y2 - c.y2) >> 1; const uint32_t e = (uint32_t)(d * d); if (e < m) { m = e; bk = k; } }
+            } else {
+              uint64_t m = ~0ull;
+#pragma unroll
+              for (uint32_t k = 0; k < 4; k++) {
+                uint64_t e = sq64(tab[k].y2 - c.y2);
+                if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
+                if (e < m) { m = e; bk = k; }
+              }
             }
             const Ycc2 sy = src_y[t];
-            err += sq64(sy.y2 - tab[bk].y2) + chroma_d(sy, tab[bk]);
+            const Ycc2 tk = tab[bk];
+            err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
           }
+          err += err_s;
+          const uint32_t slot = (memo_key[s][0] == 0) ? 0u : 1u;
+          memo_key[s][slot] = key; memo_inten[s][slot] = bi_s; memo_err[s][slot] = err_s;
         }
         if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
       }

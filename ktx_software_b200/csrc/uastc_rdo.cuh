@@ -204,8 +204,7 @@ UB_BIG void rdo_fill_level(const uint32_t* px, const UnpackedUastc& u, const Rdo
   candidate_to_unpacked(c, t);
   Bc7Build bb;
   uastc_to_bc7_build(t, bb);
-  const Bits128 bc7 = bc7_pack(bb);
-  decode_bc7_pixels(bc7, db);
+  decode_bc7_build(bb, db);
   const uint32_t m1 = (f.planes == 2) ? (255u << (8 * u.ccs)) : 0u;  // the channel plane 1 drives
   for (uint32_t i = 0; i < 16; i++) {
     const uint32_t p = px[i];

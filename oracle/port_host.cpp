@@ -124,3 +124,21 @@ PORT_API void port_rdo(uint8_t* blocks, uint32_t n, const uint8_t* px, float lam
   const uint32_t jobs = ub::rdo_job_ranges(n, total_jobs, &per);
   for (uint32_t j = 0; j < jobs; j++) port_rdo_range(blocks, px, j * per, (j + 1) * per < n ? (j + 1) * per : n, p);
 }
+
+// white-box tap: decode_bc7_build(bb) must equal decode_bc7_pixels(bc7_pack(bb)) for every transcodable block
+PORT_API int64_t port_check_bc7_build_decode(const uint8_t* blocks, uint64_t n) {
+  int64_t bad = 0;
+  for (uint64_t i = 0; i < n; i++) {
+    ub::Bits128 s;
+    memcpy(&s, blocks + i * 16, 16);
+    ub::UnpackedUastc u;
+    if (!ub::unpack_uastc(s, u, false)) continue;
+    ub::Bc7Build bb;
+    ub::uastc_to_bc7_build(u, bb);
+    uint32_t a[16], b[16];
+    ub::decode_bc7_build(bb, a);
+    const ub::Bits128 packed = ub::bc7_pack(bb);
+    if (!ub::decode_bc7_pixels(packed, b) || memcmp(a, b, 64)) bad++;
+  }
+  return bad;
+}
