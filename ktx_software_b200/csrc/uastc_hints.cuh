@@ -128,6 +128,16 @@ UB_FN Ycc2 to_ycc2(uint32_t c) {
 UB_FN uint64_t sq64(int d) { return (uint64_t)((int64_t)d * (int64_t)d); }
 UB_FN uint64_t chroma_d(const Ycc2& a, const Ycc2& b) { return sq64(a.cr - b.cr) + sq64(a.cb - b.cb); }
 
+// Moments of the chroma of 8 texels: sum_j chroma_d(b, texel_j) == 8 (b.cr^2 + b.cb^2) - 2 (b.cr S1cr + b.cb S1cb) + S2
+struct EtcMoments {
+  int64_t s1cr, s1cb, s2;
+  UB_MFN void clear() { s1cr = 0; s1cb = 0; s2 = 0; }
+  UB_MFN void add(const Ycc2& t) { s1cr += t.cr; s1cb += t.cb; s2 += (int64_t)t.cr * t.cr + (int64_t)t.cb * t.cb; }
+  UB_MFN uint64_t chroma_sum(const Ycc2& b) const {
+    return (uint64_t)(8 * ((int64_t)b.cr * b.cr + (int64_t)b.cb * b.cb) - 2 * ((int64_t)b.cr * s1cr + (int64_t)b.cb * s1cb) + s2);
+  }
+};
+
 // The four colours of one ETC1 sub-block for intensity table `inten`.  Adding the same modifier to r, g and b moves only
 // luma (54+183+19 == 256), so entries that do not clamp share the base colour's chroma: bit k of the return value is set
 // only when entry k clamped in some channel and needs its own chroma term.
@@ -171,16 +181,22 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
   o_flip = 0; o_diff = 0; o_i0 = 0; o_i1 = 0; o_bias = 0;
 #pragma unroll 1
   for (uint32_t flip = first_flip; flip < last_flip; flip++) {
-    // per sub-block statistics of the decoded texels: channel sums, min, max
+    // per sub-block statistics of the decoded texels: channel sums, min, max; and, for the non-clamping fast path,
+    // the texels' luma in registers plus the chroma moments that turn sum_j((cr_b - cr_j)^2 + (cb_b - cb_j)^2) into
+    // 8 b^2 - 2 b S1 + S2
     uint32_t avg[2][3];
     int mn[2][3], mx[2][3];
-#pragma unroll
+    int dy[2][8], sy2[2][8];               // decoded luma (not doubled), source luma (doubled)
+    EtcMoments dmom[2], smom[2];
+#pragma unroll 1
     for (uint32_t s = 0; s < 2; s++) {
 #pragma unroll
       for (uint32_t c = 0; c < 3; c++) { avg[s][c] = 0; mn[s][c] = 255; mx[s][c] = 0; }
+      dmom[s].clear(); smom[s].clear();
 #pragma unroll 1
       for (uint32_t j = 0; j < 8; j++) {
-        const uint32_t p = dec[etc1_texel(flip, s, j)];
+        const uint32_t t = etc1_texel(flip, s, j);
+        const uint32_t p = dec[t];
 #pragma unroll
         for (uint32_t c = 0; c < 3; c++) {
           const int v = (int)ch(p, c);
@@ -188,6 +204,9 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
           mn[s][c] = v < mn[s][c] ? v : mn[s][c];
           mx[s][c] = v > mx[s][c] ? v : mx[s][c];
         }
+        const Ycc2 d = dec_y[t], q = src_y[t];
+        dy[s][j] = d.y2 >> 1; sy2[s][j] = q.y2;
+        dmom[s].add(d); smom[s].add(q);
       }
     }
 #pragma unroll 1
@@ -238,38 +257,40 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
             if (b > range) range = b;
           }
           const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
-          // chroma distance of every texel to the (unclamped) base colour, shared by all table entries that do not clamp
           const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
-          uint64_t kj[8], ksum = 0;
-#pragma unroll 1
-          for (uint32_t j = 0; j < 8; j++) { kj[j] = chroma_d(by, dec_y[etc1_texel(flip, s, j)]); ksum += kj[j]; }
+          const int yb = by.y2 >> 1;
+          const int bmin = b8[0] < b8[1] ? (b8[0] < b8[2] ? b8[0] : b8[2]) : (b8[1] < b8[2] ? b8[1] : b8[2]);
+          const int bmax = b8[0] > b8[1] ? (b8[0] > b8[2] ? b8[0] : b8[2]) : (b8[1] > b8[2] ? b8[1] : b8[2]);
+          const uint64_t ksum = dmom[s].chroma_sum(by);
           uint64_t best_sub = ~0ull;
           uint32_t bi_s = 0;
 #pragma unroll 1
           for (uint32_t it = 0; it < limit; it++) {
-            Ycc2 tab[4];
-            const uint32_t clamped = etc1_subblock_ycc(b8, it, tab);
+            const int m0 = UBT(etc1_inten)[it * 4 + 2], m1 = UBT(etc1_inten)[it * 4 + 3];  // table = {-m1, -m0, m0, m1}
             uint64_t total = 0;
-            if (!clamped) {
-              // all four entries share the base chroma: only luma separates them, and (dy)^2 fits 32 bits
-#pragma unroll 1
-              for (uint32_t j = 0; j < 8; j++) {
-                const int cy = dec_y[etc1_texel(flip, s, j)].y2;
-                uint32_t m = 0xFFFFFFFFu;
+            if (bmin - m1 >= 0 && bmax + m1 <= 255) {
+              // No entry clamps: all four share the base chroma and sit at luma yb + 256*m.  The nearest entry to a
+              // texel follows from |dy| against the midpoint 128*(m0+m1); the squared distance fits 32 bits.
+              const int mid = 128 * (m0 + m1), o0 = 256 * m0, o1 = 256 * m1;
 #pragma unroll
-                for (uint32_t k = 0; k < 4; k++) { const int d = (tab[k].y2 - cy) >> 1; const uint32_t e = (uint32_t)(d * d); m = e < m ? e : m; }
-                total += m;
+              for (uint32_t j = 0; j < 8; j++) {
+                int d = dy[s][j] - yb; d = d < 0 ? -d : d;
+                const int x = d - (d < mid ? o0 : o1);
+                total += (uint32_t)(x * x);
               }
               total = total * 4 + ksum;
             } else {
+              Ycc2 tab[4];
+              const uint32_t clamped = etc1_subblock_ycc(b8, it, tab);
 #pragma unroll 1
               for (uint32_t j = 0; j < 8; j++) {
                 const Ycc2 c = dec_y[etc1_texel(flip, s, j)];
+                const uint64_t kj = chroma_d(by, c);
                 uint64_t m = ~0ull;
 #pragma unroll
                 for (uint32_t k = 0; k < 4; k++) {
                   uint64_t e = sq64(tab[k].y2 - c.y2);
-                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
+                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
                   m = e < m ? e : m;
                 }
                 total += m;
@@ -280,31 +301,42 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
             if (total < best_sub) { best_sub = total; bi_s = it; }
           }
           best_inten[s] = bi_s;
-          // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones)
-          Ycc2 tab[4];
-          const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+          // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones;
+          // equal distances keep the lowest entry index)
           uint64_t err_s = 0;
-#pragma unroll 1
-          for (uint32_t j = 0; j < 8; j++) {
-            const uint32_t t = etc1_texel(flip, s, j);
-            const Ycc2 c = dec_y[t];
-            uint32_t bk = 0;
-            if (!clamped) {
-              uint32_t m = 0xFFFFFFFFu;
+          {
+            const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
+            if (bmin - m1 >= 0 && bmax + m1 <= 255) {
+              const int mid = 128 * (m0 + m1);
 #pragma unroll
-              for (uint32_t k = 0; k < 4; k++) { const int d = (tab[k].y2 - c.y2) >> 1; const uint32_t e = (uint32_t)(d * d); if (e < m) { m = e; bk = k; } }
+              for (uint32_t j = 0; j < 8; j++) {
+                const int sd = dy[s][j] - yb, d = sd < 0 ? -sd : sd;
+                // entries by luma: k0 = -m1, k1 = -m0, k2 = +m0, k3 = +m1
+                const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
+                err_s += sq64(sy2[s][j] - (by.y2 + 512 * m));
+              }
+              err_s += smom[s].chroma_sum(by);
             } else {
-              uint64_t m = ~0ull;
+              Ycc2 tab[4];
+              const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+#pragma unroll 1
+              for (uint32_t j = 0; j < 8; j++) {
+                const uint32_t t = etc1_texel(flip, s, j);
+                const Ycc2 c = dec_y[t];
+                const uint64_t kj = chroma_d(by, c);
+                uint64_t m = ~0ull;
+                uint32_t bk = 0;
 #pragma unroll
-              for (uint32_t k = 0; k < 4; k++) {
-                uint64_t e = sq64(tab[k].y2 - c.y2);
-                if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj[j];
-                if (e < m) { m = e; bk = k; }
+                for (uint32_t k = 0; k < 4; k++) {
+                  uint64_t e = sq64(tab[k].y2 - c.y2);
+                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
+                  if (e < m) { m = e; bk = k; }
+                }
+                const Ycc2 sy = src_y[t];
+                const Ycc2 tk = tab[bk];
+                err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
               }
             }
-            const Ycc2 sy = src_y[t];
-            const Ycc2 tk = tab[bk];
-            err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
           }
           err += err_s;
           const uint32_t slot = (memo_key[s][0] == 0) ? 0u : 1u;
