@@ -3,7 +3,7 @@ import ctypes, os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libuastc_b200.so")
+LIB_PATH = os.environ.get("B200_UASTC_LIB") or os.path.join(HERE, "libuastc_b200.so")  # env override: development only
 
 TTF_BC7_RGBA = 6        # ktx_transcode_fmt_e KTX_TTF_BC7_RGBA (lib/include/ktx.h)
 TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA

@@ -212,26 +212,42 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 // is a group of 32 neighbouring blocks that walk the mode list in lock-step.  The 4x4 gather with edge replication
 // (image::extract_block_clamped, ENC/basisu_enc.h:3081) is fused into the load.  MAXC bounds the candidate list:
 // 21 at levels 0-3 (partition estimators on), 170 at level 4.
-template <int MAXC>
-__device__ __forceinline__ void encode_one(const uint32_t* px, uint32_t flags, uint4* dst) {
+#ifndef ENC_THREADS
+#define ENC_THREADS 1024  // threads per encode CTA: one CTA per SM, 32 warps, 64 registers per thread
+#endif
+#ifndef ENC_MIN_CTAS
+#define ENC_MIN_CTAS 1    // resident encode CTAs per SM (register cap = 65536 / (ENC_THREADS * ENC_MIN_CTAS))
+#endif
+// The warps of a CTA walk the three phases of encode_uastc together (barrier between phases): all warps of the CTA
+// -- with one CTA per SM, all warps of the SM -- then execute the same few tens of KB of code at a time, which is
+// what the 32 KB instruction cache can hold; free-running warps spread over the whole ~300 KB kernel.
+template <int MAXC, typename LOAD>
+__device__ __forceinline__ void encode_phased(uint64_t n, uint32_t flags, uint4* __restrict__ out, LOAD load_px) {
   ub::Candidate cands[MAXC];
   uint64_t overall[MAXC];
   float uerr[MAXC];
-  const ub::Bits128 b = ub::encode_uastc_block(px, flags, cands, overall, uerr);
-  uint4 o;
-  o.x = (uint32_t)b.lo; o.y = (uint32_t)(b.lo >> 32); o.z = (uint32_t)b.hi; o.w = (uint32_t)(b.hi >> 32);
-  *dst = o;
+  for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += (uint64_t)gridDim.x * blockDim.x) {  // uniform per CTA
+    const uint64_t i = base + threadIdx.x;
+    const bool live = i < n;
+    uint32_t px[16];
+    ub::EncState st;
+    if (live) load_px(i, px);
+    ub::enc_phase_candidates(px, flags, cands, st, live, true);
+    __syncthreads();
+    ub::enc_phase_select(px, flags, cands, overall, uerr, st, live);
+    __syncthreads();
+    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, true);
+    if (live) out[i] = make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
+    __syncthreads();
+  }
 }
 
 template <int MAXC>
-__global__ void __launch_bounds__(128) k_encode_image(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
+__global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_image(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
                                                       uint4* __restrict__ out, uint32_t bx, uint32_t by, uint32_t flags,
                                                       unsigned int* __restrict__ any_alpha) {
-  const uint32_t n = bx * by;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const uint32_t x0 = (i % bx) * 4, y0 = (i / bx) * 4;
-    uint32_t px[16];
-    uint32_t amin = 255;
+  encode_phased<MAXC>((uint64_t)bx * by, flags, out, [&](uint64_t i, uint32_t* px) {
+    const uint32_t x0 = (uint32_t)(i % bx) * 4, y0 = (uint32_t)(i / bx) * 4;
     if (x0 + 4 <= w && y0 + 4 <= h && !(pitch & 15u)) {
 #pragma unroll
       for (uint32_t y = 0; y < 4; y++) {
@@ -246,24 +262,22 @@ __global__ void __launch_bounds__(128) k_encode_image(const uint8_t* __restrict_
           px[4 * y + x] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
         }
     }
+    uint32_t amin = 255;
 #pragma unroll
     for (uint32_t k = 0; k < 16; k++) amin = min(amin, px[k] >> 24);
     if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
-    encode_one<MAXC>(px, flags, out + i);
-  }
+  });
 }
 
 template <int MAXC>
-__global__ void __launch_bounds__(128) k_encode_blocks(const uint4* __restrict__ src, uint4* __restrict__ out, uint64_t n, uint32_t flags) {
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-    uint32_t px[16];
+__global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(const uint4* __restrict__ src, uint4* __restrict__ out, uint64_t n, uint32_t flags) {
+  encode_phased<MAXC>(n, flags, out, [&](uint64_t i, uint32_t* px) {
 #pragma unroll
     for (uint32_t y = 0; y < 4; y++) {
       const uint4 v = __ldg(src + i * 4 + y);
       px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
     }
-    encode_one<MAXC>(px, flags, out + i);
-  }
+  });
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -495,7 +509,6 @@ __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, 
   }
 }
 
-const int ENC_THREADS = 128;
 const int MAXC_FAST = 21, MAXC_FULL = 170;
 
 unsigned encode_grid(uint64_t n) {

@@ -109,11 +109,15 @@ UB_BIG Bits128 pack_uastc(const Candidate& c, uint32_t solid_rgba, const BlockHi
 }
 
 // All hints of a non-solid block (basisu_uastc_enc.cpp:3607-3637).  nc = normalised winning candidate.
-UB_FN void compute_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, const EncCfg& cfg, BlockHints& h) {
-  if (cfg.bc1_hints) compute_bc1_hints(nc, px, dec, h.bc1_hint0, h.bc1_hint1);
-  const uint32_t d = UBT(uastc_mode_desc)[nc.mode];
-  h.etc2_hints = (md_comps(d) != 3) ? compute_eac_hint(dec, cfg.eac_mul_rad, cfg.eac_table_mask) : 0u;
-  compute_etc1_hints(nc.mode, px, dec, cfg.level, cfg.flags, h.etc1_flip, h.etc1_diff, h.etc1_inten0, h.etc1_inten1, h.etc1_bias);
+UB_FN void compute_hints(const Candidate& nc, const uint32_t* px, const uint32_t* dec, const EncCfg& cfg, BlockHints& h, bool active = true) {
+  if (cfg.bc1_hints) { if (active) compute_bc1_hints(nc, px, dec, h.bc1_hint0, h.bc1_hint1); UB_STAGE_SYNC(cfg); }
+  if (active) {
+    const uint32_t d = UBT(uastc_mode_desc)[nc.mode];
+    h.etc2_hints = (md_comps(d) != 3) ? compute_eac_hint(dec, cfg.eac_mul_rad, cfg.eac_table_mask) : 0u;
+  }
+  UB_STAGE_SYNC(cfg);
+  if (active) compute_etc1_hints(nc.mode, px, dec, cfg.level, cfg.flags, h.etc1_flip, h.etc1_diff, h.etc1_inten0, h.etc1_inten1, h.etc1_bias);
+  UB_STAGE_SYNC(cfg);
 }
 
 UB_FN void block_error(const uint32_t* a, const uint32_t* b, uint64_t& rgb, uint64_t& rgba, uint64_t& la) {
@@ -145,55 +149,65 @@ UB_FN float u64_to_float(uint64_t v) {
 }
 
 // Candidate generation in the reference's order (basisu_uastc_enc.cpp:3290-3351).  Returns the count.
-UB_BIG uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands) {
+// `active` = this thread has a (non-solid) block; every thread of a lock-step CTA walks the same stage list.
+UB_BIG uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands, bool active) {
   uint32_t n = 0;
   const uint32_t mm = cfg.mode_mask;
   const bool est = cfg.estimate_partition;
   uint32_t parts[8];
-  if (is_la) {
+  const bool la = active && is_la, opaque = active && !has_alpha, alpha = active && (has_alpha || cfg.always_try_alpha);
+  {
     uint32_t la_px[16];
-    for (uint32_t i = 0; i < 16; i++) la_px[i] = ch(px[i], 0) | (px[i] & 0xFF000000u);
-    if (mm & (1u << 15)) mode_single_plane(15, 0, 0, la_px, cfg, cands[n++]);
+    if (la) for (uint32_t i = 0; i < 16; i++) la_px[i] = ch(px[i], 0) | (px[i] & 0xFF000000u);
+    if (mm & (1u << 15)) { if (la) mode_single_plane(15, 0, 0, la_px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
     if (mm & (1u << 16)) {
-      if (est) { estimate_partitions(2, 4, 4, la_px, parts, 4); for (uint32_t k = 0; k < 4; k++) mode_single_plane(16, 2, parts[k], la_px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(16, 2, cp, la_px, cfg, cands[n++]);
+      if (est) {
+        if (la) estimate_partitions(2, 4, 4, la_px, parts, 4);
+        UB_STAGE_SYNC(cfg);
+        if (la) for (uint32_t k = 0; k < 4; k++) mode_single_plane(16, 2, parts[k], la_px, cfg, cands[n++]);
+      } else if (la) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(16, 2, cp, la_px, cfg, cands[n++]);
+      UB_STAGE_SYNC(cfg);
     }
-    if (mm & (1u << 17)) mode_dual_plane(17, 0, px, cfg, cands[n++]);
+    if (mm & (1u << 17)) { if (la) mode_dual_plane(17, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
   }
-  if (!has_alpha) {
-    if (mm & (1u << 0)) mode_single_plane(0, 0, 0, px, cfg, cands[n++]);
-    if (mm & (1u << 1)) mode_single_plane(1, 0, 0, px, cfg, cands[n++]);
-    if (mm & (1u << 2)) {
-      if (est) { estimate_partitions(2, 8, 3, px, parts, 1); mode_single_plane(2, 2, parts[0], px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(2, 2, cp, px, cfg, cands[n++]);
-    }
-    if (mm & (1u << 3)) {
-      if (est) { estimate_partitions(3, 4, 3, px, parts, 1); mode_single_plane(3, 3, parts[0], px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 11; cp++) mode_single_plane(3, 3, cp, px, cfg, cands[n++]);
-    }
-    if (mm & (1u << 4)) {
-      if (est) { estimate_partitions(2, 4, 3, px, parts, 1); mode_single_plane(4, 2, parts[0], px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(4, 2, cp, px, cfg, cands[n++]);
-    }
-    if (mm & (1u << 5)) mode_single_plane(5, 0, 0, px, cfg, cands[n++]);
-    if (mm & (1u << 6)) for (uint32_t rot = 0; rot < 3; rot++) mode_dual_plane(6, rot, px, cfg, cands[n++]);
-    if (mm & (1u << 7)) {
-      if (est) { estimate_partitions(7, 4, 3, px, parts, 1); mode_single_plane(7, 7, parts[0], px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 19; cp++) mode_single_plane(7, 7, cp, px, cfg, cands[n++]);
-    }
-    if (mm & (1u << 18)) mode_single_plane(18, 0, 0, px, cfg, cands[n++]);
+  if (mm & (1u << 0)) { if (opaque) mode_single_plane(0, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 1)) { if (opaque) mode_single_plane(1, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 2)) {
+    if (est) { if (opaque) estimate_partitions(2, 8, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(2, 2, parts[0], px, cfg, cands[n++]); }
+    else if (opaque) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(2, 2, cp, px, cfg, cands[n++]);
+    UB_STAGE_SYNC(cfg);
   }
-  if (has_alpha || cfg.always_try_alpha) {
-    if (mm & (1u << 9)) {
-      if (est) { estimate_partitions(2, 4, 4, px, parts, 4); for (uint32_t k = 0; k < 4; k++) mode_single_plane(9, 2, parts[k], px, cfg, cands[n++]); }
-      else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[n++]);
-    }
-    if (mm & (1u << 10)) mode_single_plane(10, 0, 0, px, cfg, cands[n++]);
-    if (mm & (1u << 11)) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(11, rot, px, cfg, cands[n++]);
-    if (mm & (1u << 12)) mode_single_plane(12, 0, 0, px, cfg, cands[n++]);
-    if (mm & (1u << 13)) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(13, rot, px, cfg, cands[n++]);
-    if (mm & (1u << 14)) mode_single_plane(14, 0, 0, px, cfg, cands[n++]);
+  if (mm & (1u << 3)) {
+    if (est) { if (opaque) estimate_partitions(3, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(3, 3, parts[0], px, cfg, cands[n++]); }
+    else if (opaque) for (uint32_t cp = 0; cp < 11; cp++) mode_single_plane(3, 3, cp, px, cfg, cands[n++]);
+    UB_STAGE_SYNC(cfg);
   }
+  if (mm & (1u << 4)) {
+    if (est) { if (opaque) estimate_partitions(2, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(4, 2, parts[0], px, cfg, cands[n++]); }
+    else if (opaque) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(4, 2, cp, px, cfg, cands[n++]);
+    UB_STAGE_SYNC(cfg);
+  }
+  if (mm & (1u << 5)) { if (opaque) mode_single_plane(5, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 6)) { if (opaque) for (uint32_t rot = 0; rot < 3; rot++) mode_dual_plane(6, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 7)) {
+    if (est) { if (opaque) estimate_partitions(7, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(7, 7, parts[0], px, cfg, cands[n++]); }
+    else if (opaque) for (uint32_t cp = 0; cp < 19; cp++) mode_single_plane(7, 7, cp, px, cfg, cands[n++]);
+    UB_STAGE_SYNC(cfg);
+  }
+  if (mm & (1u << 18)) { if (opaque) mode_single_plane(18, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 9)) {
+    if (est) {
+      if (alpha) estimate_partitions(2, 4, 4, px, parts, 4);
+      UB_STAGE_SYNC(cfg);
+      if (alpha) for (uint32_t k = 0; k < 4; k++) mode_single_plane(9, 2, parts[k], px, cfg, cands[n++]);
+    } else if (alpha) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[n++]);
+    UB_STAGE_SYNC(cfg);
+  }
+  if (mm & (1u << 10)) { if (alpha) mode_single_plane(10, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 11)) { if (alpha) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(11, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 12)) { if (alpha) mode_single_plane(12, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 13)) { if (alpha) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(13, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  if (mm & (1u << 14)) { if (alpha) mode_single_plane(14, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
   return n;
 }
 
@@ -248,35 +262,67 @@ UB_BIG uint32_t select_candidate(const uint32_t* px, const Candidate* cands, uin
   return best;
 }
 
-// encode_uastc.  px: 16 texels r | g<<8 | b<<16 | a<<24, raster order.
-UB_FN Bits128 encode_uastc_block(const uint32_t* px, uint32_t flags, Candidate* cands, uint64_t* overall, float* uerr_f) {
+// encode_uastc in three phases (candidates -> selection -> hints + pack).  `live` = this thread has a block; with
+// cta_sync every thread of the CTA calls every phase (live or not) so the stage barriers inside line up.
+struct EncState {
+  bool solid, has_alpha, is_la;
+  uint32_t n, best;
+};
+
+UB_FN void enc_phase_candidates(const uint32_t* px, uint32_t flags, Candidate* cands, EncState& st, bool live, bool cta_sync) {
   bool solid = true, has_alpha = false, is_la = true;
-  for (uint32_t i = 0; i < 16; i++) {
-    const uint32_t v = px[i];
-    if ((v >> 24) < 255) has_alpha = true;
-    if (v != px[0]) solid = false;
-    if (ch(v, 0) != ch(v, 1) || ch(v, 0) != ch(v, 2)) is_la = false;
-  }
+  if (live)
+    for (uint32_t i = 0; i < 16; i++) {
+      const uint32_t v = px[i];
+      if ((v >> 24) < 255) has_alpha = true;
+      if (v != px[0]) solid = false;
+      if (ch(v, 0) != ch(v, 1) || ch(v, 0) != ch(v, 2)) is_la = false;
+    }
+  EncCfg cfg = enc_cfg_from_flags(flags);
+  cfg.cta_sync = cta_sync;
+  if (cfg.only_la_on_transparent && is_la && !has_alpha) is_la = false;
+  st.solid = solid; st.has_alpha = has_alpha; st.is_la = is_la; st.best = 0;
+  st.n = generate_candidates(px, has_alpha, is_la, cfg, cands, live && !solid);
+}
+
+UB_FN void enc_phase_select(const uint32_t* px, uint32_t flags, const Candidate* cands, uint64_t* overall, float* uerr_f, EncState& st, bool live) {
+  if (live && !st.solid) st.best = select_candidate(px, cands, st.n, st.has_alpha, st.is_la, flags, overall, uerr_f);
+}
+
+UB_FN Bits128 enc_phase_finish(const uint32_t* px, uint32_t flags, const Candidate* cands, const EncState& st, bool live, bool cta_sync) {
   BlockHints h;
   memset(&h, 0, sizeof(h));
-  if (solid) {
+  EncCfg cfg = enc_cfg_from_flags(flags);
+  cfg.cta_sync = cta_sync;
+  const bool active = live && !st.solid;
+  uint32_t dec[16];
+  Candidate nc;
+  if (active) {
+    const Candidate& bc = cands[st.best];
+    decode_uastc_pixels(bc, dec);
+    normalize_candidate(bc, nc);
+  }
+  UB_STAGE_SYNC(cfg);
+  compute_hints(nc, px, dec, cfg, h, active);
+  Bits128 r;
+  r.lo = 0; r.hi = 0;
+  if (active) r = pack_uastc(nc, 0, h);
+  else if (live) {
     Candidate c;
     memset(&c, 0, sizeof(c));
     c.mode = UASTC_MODE_SOLID;
     hints_solid_etc1(px[0], h.etc1_diff, h.etc1_inten0, h.etc1_selector, h.etc1_r, h.etc1_g, h.etc1_b);
-    return pack_uastc(c, px[0], h);
+    r = pack_uastc(c, px[0], h);
   }
-  const EncCfg cfg = enc_cfg_from_flags(flags);
-  if (cfg.only_la_on_transparent && is_la && !has_alpha) is_la = false;
-  const uint32_t n = generate_candidates(px, has_alpha, is_la, cfg, cands);
-  const uint32_t best = select_candidate(px, cands, n, has_alpha, is_la, flags, overall, uerr_f);
-  const Candidate& bc = cands[best];
-  uint32_t dec[16];
-  decode_uastc_pixels(bc, dec);
-  Candidate nc;
-  normalize_candidate(bc, nc);
-  compute_hints(nc, px, dec, cfg, h);
-  return pack_uastc(nc, 0, h);
+  return r;
+}
+
+// encode_uastc.  px: 16 texels r | g<<8 | b<<16 | a<<24, raster order.
+UB_FN Bits128 encode_uastc_block(const uint32_t* px, uint32_t flags, Candidate* cands, uint64_t* overall, float* uerr_f) {
+  EncState st;
+  enc_phase_candidates(px, flags, cands, st, true, false);
+  enc_phase_select(px, flags, cands, overall, uerr_f, st, true);
+  return enc_phase_finish(px, flags, cands, st, true, false);
 }
 
 }  // namespace ub

@@ -14,6 +14,7 @@ namespace ub {
 struct EncCfg {
   uint32_t level, flags, mode_mask, uber_level, ls_passes;
   bool estimate_partition, always_try_alpha, bc1_hints, only_la_on_transparent;
+  bool cta_sync;  // device only: the whole CTA calls the encoder phases together and meets at barriers between stages
   uint32_t eac_mul_rad, eac_table_mask;
 };
 
@@ -22,7 +23,7 @@ UB_FN EncCfg enc_cfg_from_flags(uint32_t flags) {
   EncCfg c;
   int level = (int)(flags & 7u);
   if (level > 4) level = 4;
-  c.level = (uint32_t)level; c.flags = flags;
+  c.level = (uint32_t)level; c.flags = flags; c.cta_sync = false;
   c.mode_mask = 0xFFFFFFFFu; c.uber_level = 6; c.estimate_partition = false; c.always_try_alpha = true;
   c.eac_mul_rad = 3; c.eac_table_mask = 0xFFFFFFFFu; c.ls_passes = 2; c.bc1_hints = true; c.only_la_on_transparent = false;
   const uint32_t fast_tables = (1u << 2) | (1u << 8) | (1u << 11) | (1u << 13);

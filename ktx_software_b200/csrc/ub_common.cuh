@@ -26,6 +26,13 @@
 #define UB_CONSTEXPR constexpr
 #endif
 #define UBT(name) ubt_##name
+// Stage boundary inside the encoder: when a CTA runs the encoder in lock-step (EncCfg::cta_sync, uniform over the CTA)
+// its warps wait for each other here, so they stay within the same stage's code.  Must be reached by every thread.
+#ifdef __CUDA_ARCH__
+#define UB_STAGE_SYNC(cfg) do { if ((cfg).cta_sync) __syncthreads(); } while (0)
+#else
+#define UB_STAGE_SYNC(cfg) do { } while (0)
+#endif
 
 namespace ub {
 
