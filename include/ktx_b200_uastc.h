@@ -102,6 +102,17 @@ int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64
 int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
                                 uint32_t pack_flags, void* stream, uint32_t* d_any_alpha);
 
+/* Several device-resident images in ONE launch (a mip chain, cube faces, array layers): small images then share the
+ * launch with big ones instead of each under-filling the GPU.  Same semantics as b200_uastc_encode_image_dev per image. */
+typedef struct b200_dev_image {
+  const void* d_rgba;       /* RGBA8 in device memory, 4-byte aligned */
+  uint32_t width, height;
+  uint32_t row_pitch_bytes; /* 0 = width*4; multiple of 4 */
+  void* d_out;              /* ceil(w/4)*ceil(h/4) x 16 B */
+} b200_dev_image;
+int b200_uastc_encode_images_dev(const b200_dev_image* images, uint32_t n_images, uint32_t pack_flags, void* stream,
+                                 uint32_t* d_any_alpha);
+
 /* The RDO post-pass alone, device-resident: replaces uastc_rdo (ENC/basisu_uastc_enc.cpp:4109) as
  * encode_slices_to_uastc_4x4_ldr calls it per slice (ENC/basisu_comp.cpp:1564-1577).  d_blocks: n_blocks UASTC blocks of ONE
  * image, rewritten in place; d_block_pixels: their n_blocks x 64 B source texels.  Uses params->rdo_* and

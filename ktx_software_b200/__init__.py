@@ -5,5 +5,5 @@ package is the thin host-side mirror used by the tests and the bench: ctypes bin
 libktx's ktxTexture2_TranscodeBasis / ktxTexture2_CompressBasisEx marshalling (ktx2.py).  There is no CPU
 fallback anywhere in this package: if the CUDA library is missing, or no B200 is visible, calls raise.
 """
-from .api import (B200Error, lib, init, transcode, transcode_dev, launch_count, encode_images, encode_blocks, encode_blocks_dev, encode_image_dev, rdo_blocks_dev, TTF_BC7_RGBA, TTF_ASTC_4x4_RGBA,  # noqa: F401
+from .api import (B200Error, lib, init, transcode, transcode_dev, launch_count, encode_images, encode_blocks, encode_blocks_dev, encode_image_dev, encode_images_dev, rdo_blocks_dev, TTF_BC7_RGBA, TTF_ASTC_4x4_RGBA,  # noqa: F401
                   EXPORTED_SYMBOLS)

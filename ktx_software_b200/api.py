@@ -10,7 +10,7 @@ TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
-                    "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev"]
+                    "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -27,6 +27,11 @@ class XcodeSpan(ctypes.Structure):
 
 class Image(ctypes.Structure):
     _fields_ = [("rgba", ctypes.c_void_p), ("width", ctypes.c_uint32), ("height", ctypes.c_uint32), ("row_pitch_bytes", ctypes.c_uint32)]
+
+
+class DevImage(ctypes.Structure):
+    _fields_ = [("d_rgba", ctypes.c_void_p), ("width", ctypes.c_uint32), ("height", ctypes.c_uint32), ("row_pitch_bytes", ctypes.c_uint32),
+                ("d_out", ctypes.c_void_p)]
 
 
 class UastcParams(ctypes.Structure):
@@ -58,6 +63,7 @@ def lib():
         l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_rdo_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.POINTER(UastcParams), ctypes.c_void_p]
+        l.b200_uastc_encode_images_dev.argtypes = [ctypes.POINTER(DevImage), ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         _lib = l
     return _lib
 
@@ -108,6 +114,12 @@ def encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream=0):
 def encode_image_dev(d_rgba, width, height, d_out, pack_flags, stream=0, row_pitch_bytes=0, d_any_alpha=0):
     """Device-pointer encode of one RGBA8 image resident in HBM; the 4x4 gather is fused into the kernel."""
     _check(lib().b200_uastc_encode_image_dev(d_rgba, width, height, row_pitch_bytes, d_out, pack_flags, stream or None, d_any_alpha or None))
+
+
+def encode_images_dev(images, pack_flags, stream=0, d_any_alpha=0):
+    """One launch over several device-resident images: images = [(d_rgba, width, height, d_out), ...] (ints)."""
+    arr = (DevImage * max(1, len(images)))(*[DevImage(p, w, h, 0, o) for p, w, h, o in images])
+    _check(lib().b200_uastc_encode_images_dev(arr, len(images), pack_flags, stream or None, d_any_alpha or None))
 
 
 def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale=0.0, smooth_std_dev=0.0, total_jobs=0):

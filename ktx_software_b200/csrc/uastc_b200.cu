@@ -269,6 +269,54 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_image(cons
   });
 }
 
+// Several images in one launch (a mip chain, the faces of a cube map): block i belongs to the image whose
+// [first_block, first_block + blocks) range holds it.
+struct EncImageDesc {
+  const uint8_t* img;
+  uint4* out;
+  uint32_t w, h, pitch, bx;
+  uint64_t first_block;
+};
+
+template <int MAXC>
+__global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_images(const EncImageDesc* __restrict__ descs, uint32_t n_images, uint64_t total_blocks,
+                                                                             uint32_t flags, unsigned int* __restrict__ any_alpha) {
+  ub::Candidate cands[MAXC];
+  uint64_t overall[MAXC];
+  float uerr[MAXC];
+  for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < total_blocks; base += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t i = base + threadIdx.x;
+    const bool live = i < total_blocks;
+    uint32_t px[16];
+    ub::EncState st;
+    uint4* dst = nullptr;
+    if (live) {
+      uint32_t lo = 0, hi = n_images - 1;  // last image whose first_block <= i
+      while (lo < hi) { const uint32_t mid = (lo + hi + 1) >> 1; if (descs[mid].first_block <= i) lo = mid; else hi = mid - 1; }
+      const EncImageDesc d = descs[lo];
+      const uint64_t k = i - d.first_block;
+      dst = d.out + k;
+      const uint32_t x0 = (uint32_t)(k % d.bx) * 4, y0 = (uint32_t)(k / d.bx) * 4;
+      uint32_t amin = 255;
+      for (uint32_t y = 0; y < 4; y++)
+        for (uint32_t x = 0; x < 4; x++) {
+          const uint32_t sx = min(x0 + x, d.w - 1), sy = min(y0 + y, d.h - 1);
+          const uint32_t v = __ldg((const uint32_t*)(d.img + (size_t)sy * d.pitch + (size_t)sx * 4));
+          px[4 * y + x] = v;
+          amin = min(amin, v >> 24);
+        }
+      if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
+    }
+    ub::enc_phase_candidates(px, flags, cands, st, live, true);
+    __syncthreads();
+    ub::enc_phase_select(px, flags, cands, overall, uerr, st, live);
+    __syncthreads();
+    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, true);
+    if (live) *dst = make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
+    __syncthreads();
+  }
+}
+
 template <int MAXC>
 __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(const uint4* __restrict__ src, uint4* __restrict__ out, uint64_t n, uint32_t flags) {
   encode_phased<MAXC>(n, flags, out, [&](uint64_t i, uint32_t* px) {
@@ -511,8 +559,16 @@ __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, 
 
 const int MAXC_FAST = 21, MAXC_FULL = 170;
 
+// Encode launch shape: 1024-thread CTAs (one per SM, every warp of the SM in the same phase) when there is enough
+// work to give every SM two of them; smaller CTAs for small inputs so that all SMs still get blocks.
+unsigned encode_threads(uint64_t n) {
+  unsigned t = ENC_THREADS;
+  while (t > 128 && (n + t - 1) / t < 2ull * (uint64_t)g_ctx.sm_count) t >>= 1;
+  return t;
+}
 unsigned encode_grid(uint64_t n) {
-  const uint64_t want = (n + ENC_THREADS - 1) / ENC_THREADS;
+  const unsigned t = encode_threads(n);
+  const uint64_t want = (n + t - 1) / t;
   return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)g_ctx.sm_count * 64));
 }
 
@@ -638,8 +694,8 @@ int encode_with_rdo(const b200_image* images, uint32_t n_images, const b200_uast
     e = cudaMemcpyAsync(d_img, im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) break;
     k_gather_blocks<<<(unsigned)std::min<uint64_t>((nb[i] + 255) / 256, (uint64_t)g_ctx.sm_count * 16), 256, 0, st>>>(d_img, im.width, im.height, pitch, d_px + off * 4, bx, by, d_alpha);
-    if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(nb[i]), ENC_THREADS, 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
-    else k_encode_blocks<MAXC_FAST><<<encode_grid(nb[i]), ENC_THREADS, 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
+    if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
+    else k_encode_blocks<MAXC_FAST><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
     g_launches += 2;
     off += nb[i];
   }
@@ -840,8 +896,8 @@ int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64
   cudaStream_t st = (cudaStream_t)stream;
   if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
   const bool full = (pack_flags & 7u) >= 4u;
-  if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(n_blocks), ENC_THREADS, 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
-  else k_encode_blocks<MAXC_FAST><<<encode_grid(n_blocks), ENC_THREADS, 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
+  if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(n_blocks), encode_threads(n_blocks), 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
+  else k_encode_blocks<MAXC_FAST><<<encode_grid(n_blocks), encode_threads(n_blocks), 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
   g_launches++;
   CU(cudaGetLastError());
   if (!stream) CU(cudaStreamSynchronize(st));
@@ -860,11 +916,43 @@ int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t hei
   const uint32_t bx = (width + 3) / 4, by = (height + 3) / 4;
   const uint64_t n = (uint64_t)bx * by;
   if ((pack_flags & 7u) >= 4u)
-    k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
+    k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
   else
-    k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
+    k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
   g_launches++;
   CU(cudaGetLastError());
+  if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+int b200_uastc_encode_images_dev(const b200_dev_image* images, uint32_t n_images, uint32_t pack_flags, void* stream, uint32_t* d_any_alpha) {
+  if (n_images && !images) return fail(B200_E_INVALID_VALUE, "null pointer");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  if (!n_images) return B200_OK;
+  std::vector<EncImageDesc> descs(n_images);
+  uint64_t total = 0;
+  for (uint32_t i = 0; i < n_images; i++) {
+    const b200_dev_image& im = images[i];
+    if (!im.d_rgba || !im.d_out || !im.width || !im.height) return fail(B200_E_INVALID_VALUE, "bad image");
+    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
+    if (pitch < im.width * 4 || (pitch & 3u) || ((uintptr_t)im.d_rgba & 3u)) return fail(B200_E_INVALID_VALUE, "row pitch / base must be 4-byte aligned and hold a row");
+    descs[i] = {(const uint8_t*)im.d_rgba, (uint4*)im.d_out, im.width, im.height, pitch, (im.width + 3) / 4, total};
+    total += (uint64_t)((im.width + 3) / 4) * ((im.height + 3) / 4);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
+  EncImageDesc* d_descs = nullptr;
+  CU(cudaMallocAsync((void**)&d_descs, n_images * sizeof(EncImageDesc), st));
+  cudaError_t e = cudaMemcpyAsync(d_descs, descs.data(), n_images * sizeof(EncImageDesc), cudaMemcpyHostToDevice, st);  // pageable source: staged before return
+  if (e == cudaSuccess) {
+    if ((pack_flags & 7u) >= 4u) k_encode_images<MAXC_FULL><<<encode_grid(total), encode_threads(total), 0, st>>>(d_descs, n_images, total, pack_flags, d_any_alpha);
+    else k_encode_images<MAXC_FAST><<<encode_grid(total), encode_threads(total), 0, st>>>(d_descs, n_images, total, pack_flags, d_any_alpha);
+    g_launches++;
+    e = cudaGetLastError();
+  }
+  cudaFreeAsync(d_descs, st);
+  if (e != cudaSuccess) return fail(B200_E_CUDA, "encode_images_dev", e);
   if (!stream) CU(cudaStreamSynchronize(st));
   return B200_OK;
 }
@@ -951,8 +1039,8 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
     cudaEventRecord(ev_in[b], s_in);
     cudaStreamWaitEvent(s_k, ev_in[b], 0);
     const uint64_t n = (uint64_t)bx * by;
-    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
-    else k_encode_image<MAXC_FAST><<<encode_grid(n), ENC_THREADS, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    else k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
     g_launches++;
     cudaEventRecord(ev_k[b], s_k);
     cudaStreamWaitEvent(s_out, ev_k[b], 0);

@@ -137,3 +137,28 @@ def test_idempotent_and_decodable_at_full_size(K):
     solid = np.zeros((64, 64, 4), np.uint8); solid[:] = (10, 200, 30, 255)
     s, _ = K.encode_images([solid], 2)
     assert (R.block_modes(s[0]) == 8).all()
+
+
+def test_batched_images_one_launch_and_big_cta_path(K):
+    """b200_uastc_encode_images_dev: a large image (enough blocks for the 1024-thread phase-synchronised CTAs) and a
+    ragged mip tail in ONE launch give exactly the bytes the per-image entry gives (which runs the small images with
+    128-thread CTAs), and the big image matches the reference on a sample of block rows."""
+    import torch
+    imgs = [R.img_mix(2048, 2400, 31), R.img_mix(70, 37, 3), R.img_mix(1, 1, 5), R.img_mix(64, 64, 6), R.img_mix(5, 3, 7)]
+    d_imgs = [torch.from_numpy(im).cuda() for im in imgs]
+    nb = [((im.shape[1] + 3) // 4) * ((im.shape[0] + 3) // 4) for im in imgs]
+    outs = [torch.zeros((n, 16), dtype=torch.uint8, device="cuda") for n in nb]
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    K.encode_images_dev([(d.data_ptr(), im.shape[1], im.shape[0], o.data_ptr()) for im, d, o in zip(imgs, d_imgs, outs)], 2, 0,
+                        flag.data_ptr())
+    torch.cuda.synchronize()
+    assert flag.item() == 1
+    for im, d, o, n in zip(imgs, d_imgs, outs, nb):
+        one = torch.zeros((n, 16), dtype=torch.uint8, device="cuda")
+        K.encode_image_dev(d.data_ptr(), im.shape[1], im.shape[0], one.data_ptr(), 2)
+        torch.cuda.synchronize()
+        assert (one == o).all(), im.shape
+    if R.have_ref():
+        px = R.ref_extract_blocks(imgs[0][:64])          # the first 16 block rows
+        assert (outs[0][:px.shape[0]].cpu().numpy() == R.ref_encode_blocks(px, 2)).all()
+    K.encode_images_dev([], 2)
