@@ -215,6 +215,9 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 #ifndef ENC_THREADS
 #define ENC_THREADS 1024  // threads per encode CTA: one CTA per SM, 32 warps, 64 registers per thread
 #endif
+#ifndef ENC_FINE_SYNC
+#define ENC_FINE_SYNC true  // barriers between the per-mode stages inside candidate generation, not only between the phases
+#endif
 #ifndef ENC_MIN_CTAS
 #define ENC_MIN_CTAS 1    // resident encode CTAs per SM (register cap = 65536 / (ENC_THREADS * ENC_MIN_CTAS))
 #endif
@@ -232,11 +235,11 @@ __device__ __forceinline__ void encode_phased(uint64_t n, uint32_t flags, uint4*
     uint32_t px[16];
     ub::EncState st;
     if (live) load_px(i, px);
-    ub::enc_phase_candidates(px, flags, cands, st, live, true);
+    ub::enc_phase_candidates(px, flags, cands, st, live, ENC_FINE_SYNC);
     __syncthreads();
     ub::enc_phase_select(px, flags, cands, overall, uerr, st, live);
     __syncthreads();
-    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, true);
+    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, ENC_FINE_SYNC);
     if (live) out[i] = make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
     __syncthreads();
   }
@@ -307,11 +310,11 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_images(con
         }
       if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
     }
-    ub::enc_phase_candidates(px, flags, cands, st, live, true);
+    ub::enc_phase_candidates(px, flags, cands, st, live, ENC_FINE_SYNC);
     __syncthreads();
     ub::enc_phase_select(px, flags, cands, overall, uerr, st, live);
     __syncthreads();
-    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, true);
+    const ub::Bits128 b = ub::enc_phase_finish(px, flags, cands, st, live, ENC_FINE_SYNC);
     if (live) *dst = make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
     __syncthreads();
   }

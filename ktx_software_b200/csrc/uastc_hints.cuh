@@ -153,191 +153,250 @@ UB_FN uint32_t etc1_subblock_ycc(const int* base8, uint32_t inten, Ycc2* out) {
   return clamped;
 }
 
-UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
-                              uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
+// One ETC1 sub-block's view of a block under a given flip: the 8 decoded texels (selectors are picked on these) and the
+// 8 source texels (the reported error is against these), plus what the search needs of them in aggregate.
+struct Etc1Sub {
+  int dy[8], dcr[8], dcb[8];    // decoded texels: luma (not doubled), chroma
+  int sy2[8], scr[8], scb[8];   // source texels: doubled luma, chroma
+  uint32_t drgb[8];             // decoded texels, packed
+  EtcMoments dmom, smom;
+  int64_t dnorm;                // sum over the decoded texels of 4 y^2 + cr^2 + cb^2
+  int mn[3], mx[3];             // per-channel range of the decoded texels
+  uint32_t sum[3];              // per-channel sum of the decoded texels
+  uint32_t pad_;                // keeps the two sub-blocks of a pair in different shared-memory banks
+};
+
+// Search limits that depend only on mode / level / flags.
+struct Etc1Plan { uint32_t last_bias, last_individ; bool has_bias, use_table, flip_estimate; };
+UB_FN Etc1Plan etc1_plan(uint32_t mode, uint32_t level, uint32_t flags) {
   const bool faster = (flags & 64u) != 0, fastest = (flags & 128u) != 0;
-  const bool has_bias = UBT(uastc_mode_has_etc1_bias)[mode] != 0;
-  uint32_t last_bias = 1;
-  bool use_table = false;
-  const bool flip_estimate = (level <= 1) || faster || fastest;
-  if (has_bias) {
-    use_table = (level <= 3);
+  Etc1Plan p;
+  p.has_bias = UBT(uastc_mode_has_etc1_bias)[mode] != 0;
+  p.last_bias = 1; p.use_table = false;
+  p.flip_estimate = (level <= 1) || faster || fastest;
+  if (p.has_bias) {
+    p.use_table = (level <= 3);
     switch (level) {
-      case 0: last_bias = fastest ? 1 : (faster ? 1 : 2); break;
-      case 1: last_bias = fastest ? 1 : (faster ? 3 : 5); break;
-      case 2: last_bias = fastest ? 1 : (faster ? 10 : 20); break;
-      case 3: last_bias = fastest ? 1 : (faster ? 16 : 32); break;
-      default: last_bias = 32; break;
+      case 0: p.last_bias = fastest ? 1 : (faster ? 1 : 2); break;
+      case 1: p.last_bias = fastest ? 1 : (faster ? 3 : 5); break;
+      case 2: p.last_bias = fastest ? 1 : (faster ? 10 : 20); break;
+      case 3: p.last_bias = fastest ? 1 : (faster ? 16 : 32); break;
+      default: p.last_bias = 32; break;
     }
   }
-  Ycc2 src_y[16], dec_y[16];
+  p.last_individ = (flags & 256u) ? 1u : 2u;
+  return p;
+}
+
+// Base colours (8-bit, per sub-block) of bias trial `bi` in individual (4:4:4 x2) or differential (5:5:5 + 3:3:3) mode.
+UB_FN void etc1_base_colors(const uint32_t* sum0, const uint32_t* sum1, const Etc1Plan& pl, uint32_t individ, uint32_t bi, int (*base8)[3],
+                            uint32_t& bias) {
+  const uint32_t mul = individ ? 15u : 31u;
+  bias = pl.use_table ? UBT(etc1_sorted_bias)[bi] : bi;
+#pragma unroll
+  for (uint32_t c = 0; c < 3; c++) {
+    const int u0 = (int)((sum0[c] * mul + 1020u) / (8u * 255u)), u1 = (int)((sum1[c] * mul + 1020u) / (8u * 255u));
+    const int b0 = pl.has_bias ? etc1_bias_comp(u0, bias, (int)mul, 0, c) : u0;
+    const int b1 = pl.has_bias ? etc1_bias_comp(u1, bias, (int)mul, 1, c) : u1;
+    if (individ) {
+      base8[0][c] = (b0 << 4) | b0;
+      base8[1][c] = (b1 << 4) | b1;
+    } else {
+      const int d = clampi(b1 - b0, -4, 3);
+      const int c1 = clampi(b0 + d, 0, 31);
+      base8[0][c] = (b0 << 3) | (b0 >> 2);
+      base8[1][c] = (c1 << 3) | (c1 >> 2);
+    }
+  }
+}
+
+// One colour of an ETC1 sub-block (base + modifier, clamped) prepared for distance tests against many texels.
+struct EtcEntry {
+  int64_t norm;     // 4 y^2 + cr^2 + cb^2
+  int my, mcr, mcb; // -8 y, -2 cr, -2 cb
+  UB_MFN int64_t dist_less_norm(int ty, int tcr, int tcb) const {  // squared distance to the texel minus the texel's own norm
+    return norm + (int64_t)my * ty + (int64_t)mcr * tcr + (int64_t)mcb * tcb;
+  }
+};
+UB_FN void etc1_table_entries(const int* base8, uint32_t inten, EtcEntry* e) {
+#pragma unroll
+  for (uint32_t k = 0; k < 4; k++) {
+    const int m = UBT(etc1_inten)[inten * 4 + k];
+    const int r = clamp255(base8[0] + m), g = clamp255(base8[1] + m), b = clamp255(base8[2] + m);
+    const int y = r * 54 + g * 183 + b * 19, cr = (r << 8) - y, cb = (b << 8) - y;
+    e[k].norm = 4 * (int64_t)y * y + (int64_t)cr * cr + (int64_t)cb * cb;
+    e[k].my = -8 * y; e[k].mcr = -2 * cr; e[k].mcb = -2 * cb;
+  }
+}
+
+// Best intensity table of one sub-block for base colour b8, and its error against the source texels.  The result
+// depends only on (flip, sub-block, b8), which is what lets callers evaluate each distinct base colour once.
+UB_FN void etc1_eval_subblock(const Etc1Sub& sb, const int* b8, uint32_t flip, uint32_t level, uint32_t& o_inten, uint64_t& o_err) {
+  int range = 0;
+#pragma unroll
+  for (uint32_t c = 0; c < 3; c++) {
+    int a = sb.mx[c] - b8[c]; if (a < 0) a = -a;
+    int b = b8[c] - sb.mn[c]; if (b < 0) b = -b;
+    if (a > range) range = a;
+    if (b > range) range = b;
+  }
+  const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
+  const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
+  const int yb = by.y2 >> 1;
+  const int bmin = b8[0] < b8[1] ? (b8[0] < b8[2] ? b8[0] : b8[2]) : (b8[1] < b8[2] ? b8[1] : b8[2]);
+  const int bmax = b8[0] > b8[1] ? (b8[0] > b8[2] ? b8[0] : b8[2]) : (b8[1] > b8[2] ? b8[1] : b8[2]);
+  const uint64_t ksum = sb.dmom.chroma_sum(by);
+  uint64_t best_sub = ~0ull;
+  uint32_t bi_s = 0;
 #pragma unroll 1
-  for (uint32_t i = 0; i < 16; i++) { src_y[i] = to_ycc2(px[i]); dec_y[i] = to_ycc2(dec[i]); }
-  uint32_t first_flip = 0, last_flip = 2, last_individ = 2;
-  if (flags & 256u) { last_flip = 1; last_individ = 1; }
-  else if (flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
+  for (uint32_t it = 0; it < limit; it++) {
+    const int m0 = UBT(etc1_inten)[it * 4 + 2], m1 = UBT(etc1_inten)[it * 4 + 3];  // table = {-m1, -m0, m0, m1}
+    uint64_t total = 0;
+    if (bmin - m1 >= 0 && bmax + m1 <= 255) {
+      // No entry clamps: all four share the base chroma and sit at luma yb + 256*m.  The nearest entry to a
+      // texel follows from |dy| against the midpoint 128*(m0+m1); the squared distance fits 32 bits.
+      const int mid = 128 * (m0 + m1), o0 = 256 * m0, o1 = 256 * m1;
+#pragma unroll
+      for (uint32_t j = 0; j < 8; j++) {
+        int d = sb.dy[j] - yb; d = d < 0 ? -d : d;
+        const int x = d - (d < mid ? o0 : o1);
+        total += (uint32_t)(x * x);
+      }
+      total = total * 4 + ksum;
+    } else {
+      // Some entry clamps.  |P - T|^2 = |P|^2 - 2 P.T + |T|^2 in the weighted (2y, cr, cb) space: per entry the constant
+      // |P|^2 and three coefficients, per texel three multiply-adds and a compare; sum |T|^2 is a sub-block constant.
+      EtcEntry e[4];
+      etc1_table_entries(b8, it, e);
+      int64_t acc = sb.dnorm;
+#pragma unroll 1
+      for (uint32_t j = 0; j < 8; j++) {
+        const int ty = sb.dy[j], tcr = sb.dcr[j], tcb = sb.dcb[j];
+        int64_t m = e[0].dist_less_norm(ty, tcr, tcb);
+#pragma unroll
+        for (uint32_t k = 1; k < 4; k++) {
+          const int64_t g = e[k].dist_less_norm(ty, tcr, tcb);
+          m = g < m ? g : m;
+        }
+        acc += m;
+      }
+      total = (uint64_t)acc;
+    }
+    // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
+    if (!flip && total >= best_sub) break;
+    if (total < best_sub) { best_sub = total; bi_s = it; }
+  }
+  // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones; equal
+  // distances keep the lowest entry index)
+  uint64_t err_s = 0;
+  const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
+  if (bmin - m1 >= 0 && bmax + m1 <= 255) {
+    const int mid = 128 * (m0 + m1);
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+      const int sd = sb.dy[j] - yb, d = sd < 0 ? -sd : sd;
+      // entries by luma: k0 = -m1, k1 = -m0, k2 = +m0, k3 = +m1
+      const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
+      err_s += sq64(sb.sy2[j] - (by.y2 + 512 * m));
+    }
+    err_s += sb.smom.chroma_sum(by);
+  } else {
+    Ycc2 tab[4];
+    const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+#pragma unroll 1
+    for (uint32_t j = 0; j < 8; j++) {
+      Ycc2 c; c.y2 = sb.dy[j] * 2; c.cr = sb.dcr[j]; c.cb = sb.dcb[j];
+      const uint64_t kj = chroma_d(by, c);
+      uint64_t m = ~0ull;
+      uint32_t bk = 0;
+#pragma unroll
+      for (uint32_t k = 0; k < 4; k++) {
+        uint64_t e = sq64(tab[k].y2 - c.y2);
+        if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
+        if (e < m) { m = e; bk = k; }
+      }
+      Ycc2 sy; sy.y2 = sb.sy2[j]; sy.cr = sb.scr[j]; sy.cb = sb.scb[j];
+      const Ycc2 tk = tab[bk];
+      err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
+    }
+  }
+  o_inten = bi_s; o_err = err_s;
+}
+
+// Texel j of sub-block s under `flip` into the sub-block view; etc1_sub_finish then derives the aggregates.
+UB_FN void etc1_sub_set_texel(Etc1Sub& sb, uint32_t j, uint32_t dec_px, uint32_t src_px) {
+  const Ycc2 d = to_ycc2(dec_px), q = to_ycc2(src_px);
+  sb.dy[j] = d.y2 >> 1; sb.dcr[j] = d.cr; sb.dcb[j] = d.cb;
+  sb.sy2[j] = q.y2; sb.scr[j] = q.cr; sb.scb[j] = q.cb;
+  sb.drgb[j] = dec_px;
+}
+UB_FN void etc1_sub_finish(Etc1Sub& sb) {
+#pragma unroll
+  for (uint32_t c = 0; c < 3; c++) { sb.sum[c] = 0; sb.mn[c] = 255; sb.mx[c] = 0; }
+  sb.dmom.clear(); sb.smom.clear(); sb.dnorm = 0;
+#pragma unroll 1
+  for (uint32_t j = 0; j < 8; j++) {
+    const uint32_t p = sb.drgb[j];
+#pragma unroll
+    for (uint32_t c = 0; c < 3; c++) {
+      const int v = (int)ch(p, c);
+      sb.sum[c] += (uint32_t)v;
+      sb.mn[c] = v < sb.mn[c] ? v : sb.mn[c];
+      sb.mx[c] = v > sb.mx[c] ? v : sb.mx[c];
+    }
+    Ycc2 d; d.y2 = 0; d.cr = sb.dcr[j]; d.cb = sb.dcb[j];
+    Ycc2 q; q.y2 = 0; q.cr = sb.scr[j]; q.cb = sb.scb[j];
+    sb.dmom.add(d); sb.smom.add(q);
+    sb.dnorm += 4 * (int64_t)sb.dy[j] * sb.dy[j] + (int64_t)d.cr * d.cr + (int64_t)d.cb * d.cb;
+  }
+}
+
+// One thread, one block.
+UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
+                              uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
+  const Etc1Plan pl = etc1_plan(mode, level, flags);
+  uint32_t first_flip = 0, last_flip = 2;
+  if (flags & 256u) last_flip = 1;
+  else if (pl.flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
 
   uint64_t best_err = ~0ull;
   o_flip = 0; o_diff = 0; o_i0 = 0; o_i1 = 0; o_bias = 0;
+  Etc1Sub sub[2];
 #pragma unroll 1
   for (uint32_t flip = first_flip; flip < last_flip; flip++) {
-    // per sub-block statistics of the decoded texels: channel sums, min, max; and, for the non-clamping fast path,
-    // the texels' luma in registers plus the chroma moments that turn sum_j((cr_b - cr_j)^2 + (cb_b - cb_j)^2) into
-    // 8 b^2 - 2 b S1 + S2
-    uint32_t avg[2][3];
-    int mn[2][3], mx[2][3];
-    int dy[2][8], sy2[2][8];               // decoded luma (not doubled), source luma (doubled)
-    EtcMoments dmom[2], smom[2];
 #pragma unroll 1
     for (uint32_t s = 0; s < 2; s++) {
-#pragma unroll
-      for (uint32_t c = 0; c < 3; c++) { avg[s][c] = 0; mn[s][c] = 255; mx[s][c] = 0; }
-      dmom[s].clear(); smom[s].clear();
 #pragma unroll 1
       for (uint32_t j = 0; j < 8; j++) {
         const uint32_t t = etc1_texel(flip, s, j);
-        const uint32_t p = dec[t];
-#pragma unroll
-        for (uint32_t c = 0; c < 3; c++) {
-          const int v = (int)ch(p, c);
-          avg[s][c] += (uint32_t)v;
-          mn[s][c] = v < mn[s][c] ? v : mn[s][c];
-          mx[s][c] = v > mx[s][c] ? v : mx[s][c];
-        }
-        const Ycc2 d = dec_y[t], q = src_y[t];
-        dy[s][j] = d.y2 >> 1; sy2[s][j] = q.y2;
-        dmom[s].add(d); smom[s].add(q);
+        etc1_sub_set_texel(sub[s], j, dec[t], px[t]);
       }
+      etc1_sub_finish(sub[s]);
     }
 #pragma unroll 1
-    for (uint32_t individ = 0; individ < last_individ; individ++) {
-      const uint32_t mul = individ ? 15u : 31u;
-      int unb[2][3];
-#pragma unroll
-      for (uint32_t s = 0; s < 2; s++)
-#pragma unroll
-        for (uint32_t c = 0; c < 3; c++) unb[s][c] = (int)((avg[s][c] * mul + 1020u) / (8u * 255u));
+    for (uint32_t individ = 0; individ < pl.last_individ; individ++) {
+      // The result for a sub-block depends only on its base colour (given flip and the decoded texels).  Many bias
+      // modes leave one sub-block's base colour untouched, so remember the first and the latest evaluation.
       uint32_t memo_key[2][2] = {{0, 0}, {0, 0}}, memo_inten[2][2] = {{0, 0}, {0, 0}};
       uint64_t memo_err[2][2] = {{0, 0}, {0, 0}};
 #pragma unroll 1
-      for (uint32_t bi = 0; bi < last_bias; bi++) {
-        const uint32_t bias = use_table ? UBT(etc1_sorted_bias)[bi] : bi;
+      for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
         int base8[2][3];
-#pragma unroll
-        for (uint32_t c = 0; c < 3; c++) {
-          const int b0 = has_bias ? etc1_bias_comp(unb[0][c], bias, (int)mul, 0, c) : unb[0][c];
-          const int b1 = has_bias ? etc1_bias_comp(unb[1][c], bias, (int)mul, 1, c) : unb[1][c];
-          if (individ) {
-            base8[0][c] = (b0 << 4) | b0;
-            base8[1][c] = (b1 << 4) | b1;
-          } else {
-            const int d = clampi(b1 - b0, -4, 3);
-            const int c1 = clampi(b0 + d, 0, 31);
-            base8[0][c] = (b0 << 3) | (b0 >> 2);
-            base8[1][c] = (c1 << 3) | (c1 >> 2);
-          }
-        }
+        uint32_t bias;
+        etc1_base_colors(sub[0].sum, sub[1].sum, pl, individ, bi, base8, bias);
         uint32_t best_inten[2] = {0, 0};
         uint64_t err = 0;
 #pragma unroll 1
         for (uint32_t s = 0; s < 2; s++) {
           const int* b8 = s ? base8[1] : base8[0];
-          // The result for a sub-block depends only on its base colour (given flip and the decoded texels).  Many
-          // bias modes leave one sub-block's base colour untouched, so remember the first and the latest evaluation.
           const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
           uint32_t hit = 2;
           if (memo_key[s][0] == key) hit = 0; else if (memo_key[s][1] == key) hit = 1;
           if (hit < 2) { best_inten[s] = memo_inten[s][hit]; err += memo_err[s][hit]; continue; }
-          int range = 0;
-#pragma unroll
-          for (uint32_t c = 0; c < 3; c++) {
-            int a = mx[s][c] - b8[c]; if (a < 0) a = -a;
-            int b = b8[c] - mn[s][c]; if (b < 0) b = -b;
-            if (a > range) range = a;
-            if (b > range) range = b;
-          }
-          const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
-          const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
-          const int yb = by.y2 >> 1;
-          const int bmin = b8[0] < b8[1] ? (b8[0] < b8[2] ? b8[0] : b8[2]) : (b8[1] < b8[2] ? b8[1] : b8[2]);
-          const int bmax = b8[0] > b8[1] ? (b8[0] > b8[2] ? b8[0] : b8[2]) : (b8[1] > b8[2] ? b8[1] : b8[2]);
-          const uint64_t ksum = dmom[s].chroma_sum(by);
-          uint64_t best_sub = ~0ull;
-          uint32_t bi_s = 0;
-#pragma unroll 1
-          for (uint32_t it = 0; it < limit; it++) {
-            const int m0 = UBT(etc1_inten)[it * 4 + 2], m1 = UBT(etc1_inten)[it * 4 + 3];  // table = {-m1, -m0, m0, m1}
-            uint64_t total = 0;
-            if (bmin - m1 >= 0 && bmax + m1 <= 255) {
-              // No entry clamps: all four share the base chroma and sit at luma yb + 256*m.  The nearest entry to a
-              // texel follows from |dy| against the midpoint 128*(m0+m1); the squared distance fits 32 bits.
-              const int mid = 128 * (m0 + m1), o0 = 256 * m0, o1 = 256 * m1;
-#pragma unroll
-              for (uint32_t j = 0; j < 8; j++) {
-                int d = dy[s][j] - yb; d = d < 0 ? -d : d;
-                const int x = d - (d < mid ? o0 : o1);
-                total += (uint32_t)(x * x);
-              }
-              total = total * 4 + ksum;
-            } else {
-              Ycc2 tab[4];
-              const uint32_t clamped = etc1_subblock_ycc(b8, it, tab);
-#pragma unroll 1
-              for (uint32_t j = 0; j < 8; j++) {
-                const Ycc2 c = dec_y[etc1_texel(flip, s, j)];
-                const uint64_t kj = chroma_d(by, c);
-                uint64_t m = ~0ull;
-#pragma unroll
-                for (uint32_t k = 0; k < 4; k++) {
-                  uint64_t e = sq64(tab[k].y2 - c.y2);
-                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
-                  m = e < m ? e : m;
-                }
-                total += m;
-              }
-            }
-            // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
-            if (!flip && total >= best_sub) break;
-            if (total < best_sub) { best_sub = total; bi_s = it; }
-          }
+          uint32_t bi_s;
+          uint64_t err_s;
+          etc1_eval_subblock(sub[s], b8, flip, level, bi_s, err_s);
           best_inten[s] = bi_s;
-          // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones;
-          // equal distances keep the lowest entry index)
-          uint64_t err_s = 0;
-          {
-            const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
-            if (bmin - m1 >= 0 && bmax + m1 <= 255) {
-              const int mid = 128 * (m0 + m1);
-#pragma unroll
-              for (uint32_t j = 0; j < 8; j++) {
-                const int sd = dy[s][j] - yb, d = sd < 0 ? -sd : sd;
-                // entries by luma: k0 = -m1, k1 = -m0, k2 = +m0, k3 = +m1
-                const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
-                err_s += sq64(sy2[s][j] - (by.y2 + 512 * m));
-              }
-              err_s += smom[s].chroma_sum(by);
-            } else {
-              Ycc2 tab[4];
-              const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
-#pragma unroll 1
-              for (uint32_t j = 0; j < 8; j++) {
-                const uint32_t t = etc1_texel(flip, s, j);
-                const Ycc2 c = dec_y[t];
-                const uint64_t kj = chroma_d(by, c);
-                uint64_t m = ~0ull;
-                uint32_t bk = 0;
-#pragma unroll
-                for (uint32_t k = 0; k < 4; k++) {
-                  uint64_t e = sq64(tab[k].y2 - c.y2);
-                  if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
-                  if (e < m) { m = e; bk = k; }
-                }
-                const Ycc2 sy = src_y[t];
-                const Ycc2 tk = tab[bk];
-                err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
-              }
-            }
-          }
           err += err_s;
           const uint32_t slot = (memo_key[s][0] == 0) ? 0u : 1u;
           memo_key[s][slot] = key; memo_inten[s][slot] = bi_s; memo_err[s][slot] = err_s;
