@@ -218,6 +218,9 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 #ifndef ENC_FINE_SYNC
 #define ENC_FINE_SYNC true  // barriers between the per-mode stages inside candidate generation, not only between the phases
 #endif
+#ifndef ENC_FINE_SYNC
+#define ENC_FINE_SYNC true  // barriers between the per-mode stages inside candidate generation, not only between the phases
+#endif
 #ifndef ENC_MIN_CTAS
 #define ENC_MIN_CTAS 1    // resident encode CTAs per SM (register cap = 65536 / (ENC_THREADS * ENC_MIN_CTAS))
 #endif

@@ -138,21 +138,6 @@ struct EtcMoments {
   }
 };
 
-// The four colours of one ETC1 sub-block for intensity table `inten`.  Adding the same modifier to r, g and b moves only
-// luma (54+183+19 == 256), so entries that do not clamp share the base colour's chroma: bit k of the return value is set
-// only when entry k clamped in some channel and needs its own chroma term.
-UB_FN uint32_t etc1_subblock_ycc(const int* base8, uint32_t inten, Ycc2* out) {
-  uint32_t clamped = 0;
-#pragma unroll
-  for (uint32_t k = 0; k < 4; k++) {
-    const int m = UBT(etc1_inten)[inten * 4 + k];
-    const int r = base8[0] + m, g = base8[1] + m, b = base8[2] + m;
-    if (((uint32_t)r | (uint32_t)g | (uint32_t)b) > 255u) clamped |= 1u << k;
-    out[k] = to_ycc2((uint32_t)clamp255(r) | ((uint32_t)clamp255(g) << 8) | ((uint32_t)clamp255(b) << 16));
-  }
-  return clamped;
-}
-
 // One ETC1 sub-block's view of a block under a given flip: the 8 decoded texels (selectors are picked on these) and the
 // 8 source texels (the reported error is against these), plus what the search needs of them in aggregate.
 struct Etc1Sub {
@@ -301,23 +286,21 @@ UB_FN void etc1_eval_subblock(const Etc1Sub& sb, const int* b8, uint32_t flip, u
     }
     err_s += sb.smom.chroma_sum(by);
   } else {
-    Ycc2 tab[4];
-    const uint32_t clamped = etc1_subblock_ycc(b8, bi_s, tab);
+    EtcEntry e[4];
+    etc1_table_entries(b8, bi_s, e);
 #pragma unroll 1
     for (uint32_t j = 0; j < 8; j++) {
-      Ycc2 c; c.y2 = sb.dy[j] * 2; c.cr = sb.dcr[j]; c.cb = sb.dcb[j];
-      const uint64_t kj = chroma_d(by, c);
-      uint64_t m = ~0ull;
-      uint32_t bk = 0;
+      const int ty = sb.dy[j], tcr = sb.dcr[j], tcb = sb.dcb[j];
+      int64_t m = e[0].dist_less_norm(ty, tcr, tcb);
+      EtcEntry pick = e[0];
 #pragma unroll
-      for (uint32_t k = 0; k < 4; k++) {
-        uint64_t e = sq64(tab[k].y2 - c.y2);
-        if ((clamped >> k) & 1u) e += chroma_d(tab[k], c); else e += kj;
-        if (e < m) { m = e; bk = k; }
+      for (uint32_t k = 1; k < 4; k++) {
+        const int64_t g = e[k].dist_less_norm(ty, tcr, tcb);
+        if (g < m) { m = g; pick = e[k]; }
       }
-      Ycc2 sy; sy.y2 = sb.sy2[j]; sy.cr = sb.scr[j]; sy.cb = sb.scb[j];
-      const Ycc2 tk = tab[bk];
-      err_s += sq64(sy.y2 - tk.y2) + chroma_d(sy, tk);
+      // distance of the source texel to the picked entry: |P|^2 - 2 P.S + |S|^2
+      const int sy = sb.sy2[j] >> 1, scr = sb.scr[j], scb = sb.scb[j];
+      err_s += (uint64_t)(pick.dist_less_norm(sy, scr, scb) + 4 * (int64_t)sy * sy + (int64_t)scr * scr + (int64_t)scb * scb);
     }
   }
   o_inten = bi_s; o_err = err_s;
