@@ -148,66 +148,88 @@ UB_FN float u64_to_float(uint64_t v) {
 #endif
 }
 
-// Candidate generation in the reference's order (basisu_uastc_enc.cpp:3290-3351).  Returns the count.
+// How many candidates a mode contributes (basisu_uastc_enc.cpp:3290-3351): one per tried partition / rotation.
+UB_FN uint32_t mode_candidate_count(uint32_t mode, bool est) {
+  switch (mode) {
+    case 2: case 4: return est ? 1u : 30u;
+    case 3: return est ? 1u : 11u;
+    case 7: return est ? 1u : 19u;
+    case 9: case 16: return est ? 4u : 30u;
+    case 6: return 3u;
+    case 11: case 13: return 4u;
+    default: return 1u;
+  }
+}
+
+// Candidate generation (basisu_uastc_enc.cpp:3290-3351).  Returns the count.
+// The candidate LIST is in the reference's order -- LA modes 15..17, opaque modes 0..7 and 18, alpha modes 9..14 -- because
+// selection keeps the first of equally good candidates.  The WORK is ordered differently: each mode knows its slot in
+// the list up front, and modes of the three block classes that run the same routine share a stage (one-subset,
+// partition estimate, partitioned, dual-plane), so that in a lock-step CTA (stage barriers, see UB_STAGE_SYNC) warps
+// holding opaque blocks and warps holding alpha blocks work side by side instead of waiting out each other's stages.
 // `active` = this thread has a (non-solid) block; every thread of a lock-step CTA walks the same stage list.
 UB_BIG uint32_t generate_candidates(const uint32_t* px, bool has_alpha, bool is_la, const EncCfg& cfg, Candidate* cands, bool active) {
-  uint32_t n = 0;
   const uint32_t mm = cfg.mode_mask;
   const bool est = cfg.estimate_partition;
-  uint32_t parts[8];
   const bool la = active && is_la, opaque = active && !has_alpha, alpha = active && (has_alpha || cfg.always_try_alpha);
-  {
-    uint32_t la_px[16];
-    if (la) for (uint32_t i = 0; i < 16; i++) la_px[i] = ch(px[i], 0) | (px[i] & 0xFF000000u);
-    if (mm & (1u << 15)) { if (la) mode_single_plane(15, 0, 0, la_px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-    if (mm & (1u << 16)) {
-      if (est) {
-        if (la) estimate_partitions(2, 4, 4, la_px, parts, 4);
-        UB_STAGE_SYNC(cfg);
-        if (la) for (uint32_t k = 0; k < 4; k++) mode_single_plane(16, 2, parts[k], la_px, cfg, cands[n++]);
-      } else if (la) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(16, 2, cp, la_px, cfg, cands[n++]);
-      UB_STAGE_SYNC(cfg);
-    }
-    if (mm & (1u << 17)) { if (la) mode_dual_plane(17, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  }
-  if (mm & (1u << 0)) { if (opaque) mode_single_plane(0, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 1)) { if (opaque) mode_single_plane(1, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 2)) {
-    if (est) { if (opaque) estimate_partitions(2, 8, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(2, 2, parts[0], px, cfg, cands[n++]); }
-    else if (opaque) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(2, 2, cp, px, cfg, cands[n++]);
+  uint32_t n = 0;
+#define UB_SLOT(var, mode, group) const bool on##var = ((mm >> (mode)) & 1u) && (group); const uint32_t var = n; if (on##var) n += mode_candidate_count(mode, est);
+  UB_SLOT(a15, 15, la) UB_SLOT(a16, 16, la) UB_SLOT(a17, 17, la)
+  UB_SLOT(a0, 0, opaque) UB_SLOT(a1, 1, opaque) UB_SLOT(a2, 2, opaque) UB_SLOT(a3, 3, opaque) UB_SLOT(a4, 4, opaque)
+  UB_SLOT(a5, 5, opaque) UB_SLOT(a6, 6, opaque) UB_SLOT(a7, 7, opaque) UB_SLOT(a18, 18, opaque)
+  UB_SLOT(a9, 9, alpha) UB_SLOT(a10, 10, alpha) UB_SLOT(a11, 11, alpha) UB_SLOT(a12, 12, alpha) UB_SLOT(a13, 13, alpha) UB_SLOT(a14, 14, alpha)
+#undef UB_SLOT
+  uint32_t la_px[16];
+  if (la) for (uint32_t i = 0; i < 16; i++) la_px[i] = ch(px[i], 0) | (px[i] & 0xFF000000u);
+
+  // one subset, one plane
+  if (ona15) mode_single_plane(15, 0, 0, la_px, cfg, cands[a15]);
+  if (ona0) mode_single_plane(0, 0, 0, px, cfg, cands[a0]);
+  if (ona10) mode_single_plane(10, 0, 0, px, cfg, cands[a10]);
+  UB_STAGE_SYNC(cfg);
+  if (ona1) mode_single_plane(1, 0, 0, px, cfg, cands[a1]);
+  if (ona12) mode_single_plane(12, 0, 0, px, cfg, cands[a12]);
+  UB_STAGE_SYNC(cfg);
+  if (ona5) mode_single_plane(5, 0, 0, px, cfg, cands[a5]);
+  if (ona14) mode_single_plane(14, 0, 0, px, cfg, cands[a14]);
+  UB_STAGE_SYNC(cfg);
+  // partition estimates
+  uint32_t p16[4], p2[1], p3[1], p4[1], p7[1], p9[4];
+  if (est) {
+    if (ona16) estimate_partitions(2, 4, 4, la_px, p16, 4);
+    if (ona2) estimate_partitions(2, 8, 3, px, p2, 1);
+    if (ona9) estimate_partitions(2, 4, 4, px, p9, 4);
+    UB_STAGE_SYNC(cfg);
+    if (ona3) estimate_partitions(3, 4, 3, px, p3, 1);
+    if (ona4) estimate_partitions(2, 4, 3, px, p4, 1);
+    if (ona7) estimate_partitions(7, 4, 3, px, p7, 1);
     UB_STAGE_SYNC(cfg);
   }
-  if (mm & (1u << 3)) {
-    if (est) { if (opaque) estimate_partitions(3, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(3, 3, parts[0], px, cfg, cands[n++]); }
-    else if (opaque) for (uint32_t cp = 0; cp < 11; cp++) mode_single_plane(3, 3, cp, px, cfg, cands[n++]);
-    UB_STAGE_SYNC(cfg);
-  }
-  if (mm & (1u << 4)) {
-    if (est) { if (opaque) estimate_partitions(2, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(4, 2, parts[0], px, cfg, cands[n++]); }
-    else if (opaque) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(4, 2, cp, px, cfg, cands[n++]);
-    UB_STAGE_SYNC(cfg);
-  }
-  if (mm & (1u << 5)) { if (opaque) mode_single_plane(5, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 6)) { if (opaque) for (uint32_t rot = 0; rot < 3; rot++) mode_dual_plane(6, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 7)) {
-    if (est) { if (opaque) estimate_partitions(7, 4, 3, px, parts, 1); UB_STAGE_SYNC(cfg); if (opaque) mode_single_plane(7, 7, parts[0], px, cfg, cands[n++]); }
-    else if (opaque) for (uint32_t cp = 0; cp < 19; cp++) mode_single_plane(7, 7, cp, px, cfg, cands[n++]);
-    UB_STAGE_SYNC(cfg);
-  }
-  if (mm & (1u << 18)) { if (opaque) mode_single_plane(18, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 9)) {
-    if (est) {
-      if (alpha) estimate_partitions(2, 4, 4, px, parts, 4);
-      UB_STAGE_SYNC(cfg);
-      if (alpha) for (uint32_t k = 0; k < 4; k++) mode_single_plane(9, 2, parts[k], px, cfg, cands[n++]);
-    } else if (alpha) for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[n++]);
-    UB_STAGE_SYNC(cfg);
-  }
-  if (mm & (1u << 10)) { if (alpha) mode_single_plane(10, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 11)) { if (alpha) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(11, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 12)) { if (alpha) mode_single_plane(12, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 13)) { if (alpha) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(13, rot, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
-  if (mm & (1u << 14)) { if (alpha) mode_single_plane(14, 0, 0, px, cfg, cands[n++]); UB_STAGE_SYNC(cfg); }
+  // several subsets, one plane
+  if (ona16) { if (est) for (uint32_t k = 0; k < 4; k++) mode_single_plane(16, 2, p16[k], la_px, cfg, cands[a16 + k]);
+               else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(16, 2, cp, la_px, cfg, cands[a16 + cp]); }
+  if (ona2) { if (est) mode_single_plane(2, 2, p2[0], px, cfg, cands[a2]);
+              else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(2, 2, cp, px, cfg, cands[a2 + cp]); }
+  if (ona3) { if (est) mode_single_plane(3, 3, p3[0], px, cfg, cands[a3]);
+              else for (uint32_t cp = 0; cp < 11; cp++) mode_single_plane(3, 3, cp, px, cfg, cands[a3 + cp]); }
+  if (ona9) { if (est) for (uint32_t k = 0; k < 2; k++) mode_single_plane(9, 2, p9[k], px, cfg, cands[a9 + k]);
+              else for (uint32_t cp = 0; cp < 15; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[a9 + cp]); }
+  UB_STAGE_SYNC(cfg);
+  if (ona4) { if (est) mode_single_plane(4, 2, p4[0], px, cfg, cands[a4]);
+              else for (uint32_t cp = 0; cp < 30; cp++) mode_single_plane(4, 2, cp, px, cfg, cands[a4 + cp]); }
+  if (ona7) { if (est) mode_single_plane(7, 7, p7[0], px, cfg, cands[a7]);
+              else for (uint32_t cp = 0; cp < 19; cp++) mode_single_plane(7, 7, cp, px, cfg, cands[a7 + cp]); }
+  if (ona9) { if (est) for (uint32_t k = 2; k < 4; k++) mode_single_plane(9, 2, p9[k], px, cfg, cands[a9 + k]);
+              else for (uint32_t cp = 15; cp < 30; cp++) mode_single_plane(9, 2, cp, px, cfg, cands[a9 + cp]); }
+  UB_STAGE_SYNC(cfg);
+  // two planes (the opaque side's last one-subset mode rides along with the alpha side's second dual-plane mode)
+  if (ona17) mode_dual_plane(17, 0, px, cfg, cands[a17]);
+  if (ona6) for (uint32_t rot = 0; rot < 3; rot++) mode_dual_plane(6, rot, px, cfg, cands[a6 + rot]);
+  if (ona11) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(11, rot, px, cfg, cands[a11 + rot]);
+  UB_STAGE_SYNC(cfg);
+  if (ona18) mode_single_plane(18, 0, 0, px, cfg, cands[a18]);
+  if (ona13) for (uint32_t rot = 0; rot < 4; rot++) mode_dual_plane(13, rot, px, cfg, cands[a13 + rot]);
+  UB_STAGE_SYNC(cfg);
   return n;
 }
 
