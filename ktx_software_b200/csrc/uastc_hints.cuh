@@ -105,6 +105,12 @@ UB_TABLE(int8_t, etc1_bias_delta, 192) = {
   0,0,0,0,1,0,0,1,1,0,1,1,1,1,1,1,1,1,-1,-1,-1,0,0,0,1,1,1,-1,-1,-1,0,0,0,1,1,1,0,0,0,-1,-1,-1,1,1,1,0,0,0};
 UB_TABLE(uint8_t, etc1_sorted_bias, 32) = {13, 0, 22, 29, 27, 12, 26, 9, 30, 31, 8, 10, 25, 2, 23, 5, 15, 7, 3, 11, 6, 17, 28, 18, 1, 19, 20, 21, 24, 4, 14, 16};
 
+// Memo slot of bias trial `bi` for sub-block s: trials whose bias moves the sub-block's base colour by the same
+// per-channel steps share a slot.  [sorted order (levels <= 3) | plain order (level 4)][sub-block][bi]
+UB_TABLE(uint8_t, etc1_bias_slot, 128) = {
+  0,1,2,0,1,3,4,5,0,4,0,6,7,3,8,9,2,10,11,12,13,14,4,0,15,0,0,0,0,13,10,12,0,1,2,3,0,4,3,5,1,0,2,6,7,0,8,0,0,0,9,0,0,10,1,4,11,12,13,14,15,13,14,15,
+  0,1,2,3,4,5,4,6,7,8,9,10,2,7,6,11,10,12,7,7,7,7,11,13,7,14,15,0,15,7,7,15,0,1,2,3,4,2,2,2,5,6,7,2,8,2,9,2,10,11,8,12,4,9,5,13,10,14,15,2,0,15,0,2};
+
 UB_FN int etc1_bias_comp(int v, uint32_t bias, int limit, uint32_t subblock, uint32_t c) {  // apply_etc1_bias, one channel
   const int delta = UBT(etc1_bias_delta)[bias * 6 + subblock * 3 + c];
   if (v == 0) { if (delta == -2) v += 3; else v += delta + 1; }
@@ -358,10 +364,14 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
     }
 #pragma unroll 1
     for (uint32_t individ = 0; individ < pl.last_individ; individ++) {
-      // The result for a sub-block depends only on its base colour (given flip and the decoded texels).  Many bias
-      // modes leave one sub-block's base colour untouched, so remember the first and the latest evaluation.
-      uint32_t memo_key[2][2] = {{0, 0}, {0, 0}}, memo_inten[2][2] = {{0, 0}, {0, 0}};
-      uint64_t memo_err[2][2] = {{0, 0}, {0, 0}};
+      // The result for a sub-block depends only on its base colour (given flip and the decoded texels), and bias
+      // trials that step the sub-block's base colour alike share a memo slot (etc1_bias_slot): evaluate once per slot
+      // unless the colour differs after all (differential mode couples the second sub-block to the first).
+      uint32_t memo_key[2][16];
+      uint8_t memo_inten[2][16];
+      uint64_t memo_err[2][16];
+#pragma unroll 1
+      for (uint32_t i = 0; i < 16; i++) { memo_key[0][i] = 0; memo_key[1][i] = 0; }
 #pragma unroll 1
       for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
         int base8[2][3];
@@ -373,16 +383,14 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
         for (uint32_t s = 0; s < 2; s++) {
           const int* b8 = s ? base8[1] : base8[0];
           const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
-          uint32_t hit = 2;
-          if (memo_key[s][0] == key) hit = 0; else if (memo_key[s][1] == key) hit = 1;
-          if (hit < 2) { best_inten[s] = memo_inten[s][hit]; err += memo_err[s][hit]; continue; }
+          const uint32_t slot = UBT(etc1_bias_slot)[(pl.use_table ? 0u : 64u) + s * 32 + bi];
+          if (memo_key[s][slot] == key) { best_inten[s] = memo_inten[s][slot]; err += memo_err[s][slot]; continue; }
           uint32_t bi_s;
           uint64_t err_s;
           etc1_eval_subblock(sub[s], b8, flip, level, bi_s, err_s);
           best_inten[s] = bi_s;
           err += err_s;
-          const uint32_t slot = (memo_key[s][0] == 0) ? 0u : 1u;
-          memo_key[s][slot] = key; memo_inten[s][slot] = bi_s; memo_err[s][slot] = err_s;
+          memo_key[s][slot] = key; memo_inten[s][slot] = (uint8_t)bi_s; memo_err[s][slot] = err_s;
         }
         if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
       }
