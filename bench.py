@@ -296,7 +296,9 @@ def run_c5(args):
                            "l2": "inputs (1 GiB) larger than L2, no flush needed", "parity_vs_reference": parity},
                 "clocks": cs.summary(),
                 "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": 16 * ne, "d2h_bytes_per_step": 16 * ne,
-                        "blocks": ne, "api": "b200_uastc_transcode (host pinned buffers)", "matches_device_path": e2e_ok},
+                        "blocks": ne, "api": "b200_uastc_transcode (host pinned buffers)", "matches_device_path": e2e_ok,
+                        "ms_per_call": {"encode": 1e3 * e2e_parts[0] / e2e_steps, "transcode_bc7": 1e3 * e2e_parts[1] / e2e_steps,
+                                        "transcode_astc": 1e3 * e2e_parts[2] / e2e_steps}},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                              "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
@@ -421,14 +423,23 @@ def run_c2(args):
     spans = [(0, 0, total_blocks)]
     hu, hb, ha = h_u.numpy().reshape(-1), h_b.numpy().reshape(-1), h_a.numpy().reshape(-1)
 
+    e2e_parts = [0.0, 0.0, 0.0]
+
     def e2e_step():
+        t0 = time.perf_counter()
         K.api._check(K.lib().b200_uastc_encode(arr, len(imgs), ctypes.byref(params), optr, ctypes.byref(any_alpha)))
+        t1 = time.perf_counter()
         K.transcode(hu, K.TTF_BC7_RGBA, spans=spans, dst=hb)
+        t2 = time.perf_counter()
         K.transcode(hu, K.TTF_ASTC_4x4_RGBA, spans=spans, dst=ha)
+        t3 = time.perf_counter()
+        for i, d in enumerate((t1 - t0, t2 - t1, t3 - t2)):
+            e2e_parts[i] += d
 
     e2e_step()
     barrier()
     e2e_steps = max(1, min(args.steps, 3))
+    e2e_parts[:] = [0.0, 0.0, 0.0]
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
@@ -461,7 +472,9 @@ def run_c2(args):
                 "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": in_bytes + 2 * 16 * total_blocks,
                         "d2h_bytes_per_step": 3 * 16 * total_blocks, "steps": e2e_steps,
                         "api": "b200_uastc_encode + b200_uastc_transcode(BC7) + b200_uastc_transcode(ASTC), pinned host buffers",
-                        "matches_device_path": e2e_ok},
+                        "matches_device_path": e2e_ok,
+                        "ms_per_call": {"encode": 1e3 * e2e_parts[0] / e2e_steps, "transcode_bc7": 1e3 * e2e_parts[1] / e2e_steps,
+                                        "transcode_astc": 1e3 * e2e_parts[2] / e2e_steps}},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": enc_bytes / (enc0_ms * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                              "frac": enc_bytes / (enc0_ms * 1e-3) / 1e9 / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,

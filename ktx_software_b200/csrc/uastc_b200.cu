@@ -725,16 +725,35 @@ int encode_with_rdo(const b200_image* images, uint32_t n_images, const b200_uast
 
 // per-thread stream set, created lazily
 struct ThreadStreams {
-  cudaStream_t s[3] = {nullptr, nullptr, nullptr};
+  cudaStream_t s[4] = {nullptr, nullptr, nullptr, nullptr};   // copy in, kernels, copy out, second kernel stream
   int device = -1;
   ~ThreadStreams() { /* streams die with the context */ }
 };
 thread_local ThreadStreams t_streams;
 
+// Per host thread: the staging buffers of the host-buffer entry points live across calls (a cudaMalloc / cudaFree pair per
+// call costs milliseconds and synchronises the device).  Slots 0-2: slab inputs, 3-5: slab outputs, 6: flags.
+struct Staging {
+  void* p[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  size_t n[7] = {0, 0, 0, 0, 0, 0, 0};
+  void* get(int i, size_t bytes) {
+    if (n[i] < bytes) {
+      if (p[i]) cudaFree(p[i]);
+      p[i] = nullptr; n[i] = 0;
+      if (cudaMalloc(&p[i], bytes) != cudaSuccess) return nullptr;
+      n[i] = bytes;
+    }
+    return p[i];
+  }
+  void release() { for (int i = 0; i < 7; i++) { if (p[i]) cudaFree(p[i]); p[i] = nullptr; n[i] = 0; } }
+  ~Staging() { /* at thread exit the context may be gone: the driver reclaims */ }
+};
+thread_local Staging t_stage;
+
 int get_streams(cudaStream_t** out) {
   if (t_streams.device != g_ctx.device) {
     CU(cudaSetDevice(g_ctx.device));
-    for (int i = 0; i < 3; i++) CU(cudaStreamCreateWithFlags(&t_streams.s[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CU(cudaStreamCreateWithFlags(&t_streams.s[i], cudaStreamNonBlocking));
     t_streams.device = g_ctx.device;
   }
   *out = t_streams.s;
@@ -764,6 +783,7 @@ int b200_uastc_init(void) {
 }
 
 void b200_uastc_shutdown(void) {
+  t_stage.release();
   std::lock_guard<std::mutex> lk(g_mu);
   g_ctx.ready = false;
 }
@@ -816,23 +836,21 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
   cudaEvent_t ev_in[RING], ev_k[RING], ev_out[RING];
   uint64_t maxn = 0;
   for (auto& r : runs) maxn = std::max(maxn, std::min(r.n, SLAB));
-  auto cleanup = [&]() {
-    for (int i = 0; i < RING; i++) { if (d_in[i]) cudaFree(d_in[i]); if (d_out[i]) cudaFree(d_out[i]); }
-    if (d_bad) cudaFree(d_bad);
-  };
+  auto cleanup = [&]() {};   // staging buffers stay cached (t_stage)
   int nring = 0;
   uint64_t total_slabs = 0;
   for (auto& r : runs) total_slabs += (r.n + SLAB - 1) / SLAB;
   nring = (int)std::min<uint64_t>(RING, total_slabs);
   for (int i = 0; i < nring; i++) {
-    cudaError_t e1 = cudaMalloc(&d_in[i], maxn * 16), e2 = cudaMalloc(&d_out[i], maxn * 16);
-    if (e1 != cudaSuccess || e2 != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging", e1 != cudaSuccess ? e1 : e2); }
+    d_in[i] = (uint8_t*)t_stage.get(i, maxn * 16); d_out[i] = (uint8_t*)t_stage.get(3 + i, maxn * 16);
+    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
     cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
   }
   // one "first bad block" word per run so the failing span can be named
-  if (cudaMalloc(&d_bad, runs.size() * sizeof(unsigned long long)) != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flags"); }
+  d_bad = (unsigned long long*)t_stage.get(6, runs.size() * sizeof(unsigned long long));
+  if (!d_bad) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flags");
   cudaMemsetAsync(d_bad, 0xFF, runs.size() * sizeof(unsigned long long), ss[1]);
 
   cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
@@ -1017,26 +1035,31 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   unsigned int* d_alpha = nullptr;
   cudaEvent_t ev_in[SLOTS], ev_k[SLOTS], ev_out[SLOTS];
   const int nslots = (int)std::min<size_t>(SLOTS, slabs.size());
-  auto cleanup = [&]() {
-    for (int i = 0; i < SLOTS; i++) { if (d_in[i]) cudaFree(d_in[i]); if (d_out[i]) cudaFree(d_out[i]); }
-    if (d_alpha) cudaFree(d_alpha);
-  };
+  auto cleanup = [&]() {};   // staging buffers stay cached (t_stage)
   for (int i = 0; i < nslots; i++) {
-    cudaError_t e1 = cudaMalloc(&d_in[i], max_in), e2 = cudaMalloc(&d_out[i], max_out);
-    if (e1 != cudaSuccess || e2 != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging", e1 != cudaSuccess ? e1 : e2); }
+    d_in[i] = (uint8_t*)t_stage.get(i, max_in); d_out[i] = (uint8_t*)t_stage.get(3 + i, max_out);
+    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
     cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
   }
-  if (cudaMalloc(&d_alpha, sizeof(unsigned int)) != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flag"); }
-  cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
-  cudaMemsetAsync(d_alpha, 0, sizeof(unsigned int), s_k);
+  d_alpha = (unsigned int*)t_stage.get(6, sizeof(unsigned int));
+  if (!d_alpha) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flag");
+  // Kernels of consecutive slabs go to two streams in turn: the tail of one slab's grid (fewer CTAs left than SMs)
+  // overlaps the head of the next instead of idling SMs.
+  cudaStream_t s_in = ss[0], s_kk[2] = {ss[1], ss[3]}, s_out = ss[2];
+  cudaEvent_t ev_zero;
+  cudaEventCreateWithFlags(&ev_zero, cudaEventDisableTiming);
+  cudaMemsetAsync(d_alpha, 0, sizeof(unsigned int), s_kk[0]);
+  cudaEventRecord(ev_zero, s_kk[0]);
+  cudaStreamWaitEvent(s_kk[1], ev_zero, 0);
   const bool full = (params->pack_flags & 7u) >= 4u;
   cudaError_t err = cudaSuccess;
   for (size_t k = 0; k < slabs.size() && err == cudaSuccess; k++) {
     const Slab& sl = slabs[k];
     const b200_image& im = images[sl.img];
     const int b = (int)(k % nslots);
+    cudaStream_t s_k = s_kk[k & 1];
     const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
     const uint32_t bx = (im.width + 3) / 4, by = (sl.rows_px + 3) / 4;
     if (k >= (size_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
@@ -1055,7 +1078,9 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   }
   unsigned int h_alpha = 0;
   if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_k);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_kk[0]);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_kk[1]);
+  cudaEventDestroy(ev_zero);
   if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
   if (err == cudaSuccess) err = cudaGetLastError();
   if (err == cudaSuccess) err = cudaMemcpy(&h_alpha, d_alpha, sizeof(h_alpha), cudaMemcpyDeviceToHost);
