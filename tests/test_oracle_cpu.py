@@ -197,3 +197,16 @@ def test_rdo_match_cost_staircase():
                 extra += 1; d >>= 1
         return 12 + extra
     assert [cost(d) for d in (0, 3, 4, 16, 511, 512, 1023, 1024, 32767, 32768, 65536)] == [12, 12, 13, 15, 19, 20, 20, 21, 25, 26, 27]
+
+
+def test_bc7_build_decode_equals_pack_then_parse():
+    """Candidate scoring decodes BC7 straight from the transcoder's build (decode_bc7_build) instead of packing the
+    block and parsing it back (decode_bc7_pixels(bc7_pack(build))): the two must give the same texels for every mode."""
+    import ctypes
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))["uastc"]
+    rnd = np.random.default_rng(7).integers(0, 256, (20000, 16), dtype=np.uint8)
+    blocks = np.ascontiguousarray(np.concatenate([g, rnd]))
+    lib = R.port()
+    lib.port_check_bc7_build_decode.restype = ctypes.c_int64
+    lib.port_check_bc7_build_decode.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
+    assert lib.port_check_bc7_build_decode(blocks.ctypes.data, blocks.shape[0]) == 0
