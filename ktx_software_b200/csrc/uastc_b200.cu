@@ -67,9 +67,17 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
 //      offset of a UASTC mode is a compile-time constant -- instead of diverging over the 19-way switch;
 //   3. each result overwrites its block's slot of the shared-memory tile, which leaves as one TMA bulk store.
 // Global traffic is exactly the algorithmic 32 B per block, fully coalesced by construction.
-const int XT_THREADS = 256;
-const int XT_TILE = 1024;
+#ifndef XT_THREADS
+#define XT_THREADS 1024
+#endif
+#ifndef XT_TILE
+#define XT_TILE 4096
+#endif
+#ifndef XT_CTAS_PER_SM
+#define XT_CTAS_PER_SM 1
+#endif
 const int XT_PER_THREAD = XT_TILE / XT_THREADS;
+const size_t XT_SMEM_BYTES = 2 * (size_t)XT_TILE * 16 + (size_t)XT_TILE * 2 + 32 * 4 + 2 * 8;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -115,10 +123,11 @@ __device__ __forceinline__ bool transcode_dispatch(uint32_t mode, const ub::Bits
 template <int TARGET>
 __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
                                                                 unsigned long long* __restrict__ first_bad) {
-  __shared__ __align__(128) uint4 s_in[2][XT_TILE];  // a block's result overwrites its own input slot
-  __shared__ uint16_t s_order[XT_TILE];
-  __shared__ uint32_t s_hist[32];
-  __shared__ __align__(8) uint64_t s_bar[2];
+  extern __shared__ __align__(128) unsigned char xt_smem[];
+  uint4 (*s_in)[XT_TILE] = (uint4 (*)[XT_TILE])xt_smem;  // [2][XT_TILE]; a block's result overwrites its own input slot
+  uint64_t* s_bar = (uint64_t*)(xt_smem + 2 * (size_t)XT_TILE * 16);
+  uint32_t* s_hist = (uint32_t*)(s_bar + 2);
+  uint16_t* s_order = (uint16_t*)(s_hist + 32);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
   const uint64_t n_tiles = (n_blocks + XT_TILE - 1) / XT_TILE;
@@ -126,6 +135,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   if (tile >= n_tiles) return;
   auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)XT_TILE, n_blocks - t * XT_TILE); };
 
+  if (tid < 32) s_hist[tid] = 0;
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
     mbar_init(&s_bar[1], 1);
@@ -147,12 +157,10 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
       mbar_expect_tx(&s_bar[buf ^ 1], bytes);
       bulk_g2s(s_in[buf ^ 1], src + next * XT_TILE, bytes, &s_bar[buf ^ 1]);
     }
-    if (tid < 32) s_hist[tid] = 0;
-    mbar_wait(&s_bar[buf], buf ? phase1 : phase0);
+    mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
-    __syncthreads();
 
-    // ---- bin by mode: rank inside the bin from a warp-aggregated shared atomic
+    // ---- bin by mode: rank inside the bin from a warp-aggregated shared atomic (s_hist is zero on entry)
     uint32_t my_mode[XT_PER_THREAD], my_rank[XT_PER_THREAD];
 #pragma unroll
     for (int k = 0; k < XT_PER_THREAD; k++) {
@@ -168,28 +176,32 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
       my_rank[k] = base + __popc(peers & ((1u << lane) - 1u));
     }
     __syncthreads();
-    if (tid < 32) {  // exclusive scan of the 32 bin counts
-      const uint32_t c = s_hist[tid];
+    // every warp scans the 32 bin counts for itself (lane = bin): no second barrier, no shared-memory round trip
+    uint32_t bin_start;
+    {
+      const uint32_t c = s_hist[lane];
       uint32_t v = c;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v, o); if ((int)lane >= o) v += t; }
-      s_hist[tid] = v - c;
+      bin_start = v - c;
     }
-    __syncthreads();
 #pragma unroll
     for (int k = 0; k < XT_PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
-      if (i < cnt) s_order[s_hist[my_mode[k]] + my_rank[k]] = (uint16_t)(i | (my_mode[k] << 10));
+      const uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, my_mode[k]);
+      if (i < cnt) s_order[start + my_rank[k]] = (uint16_t)i;
     }
     __syncthreads();
+    if (tid < 32) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
 #pragma unroll 1
     for (int k = 0; k < XT_PER_THREAD; k++) {
       const uint32_t j = tid + k * XT_THREADS;
       if (j < cnt) {
-        const uint32_t e = s_order[j], idx = e & 1023u, m = e >> 10;
+        const uint32_t idx = s_order[j];
         const uint4 v = s_in[buf][idx];
+        const uint32_t m = (uint32_t)ub::UBT(uastc_huff_modes)[v.x & 127u];
         ub::Bits128 s, d;
         s.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
         s.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
@@ -584,11 +596,11 @@ int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n
   if (!n) return B200_OK;
   // persistent tiles: up to 6 CTAs (34 KB of shared memory each) per SM, each walking tiles with a grid stride
   const uint64_t tiles = (n + XT_TILE - 1) / XT_TILE;
-  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * 6);
+  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
   if (target == B200_TTF_BC7_RGBA)
-    k_transcode_tiled<0><<<grid, XT_THREADS, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<0><<<grid, XT_THREADS, XT_SMEM_BYTES, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
   else
-    k_transcode_tiled<1><<<grid, XT_THREADS, 0, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<1><<<grid, XT_THREADS, XT_SMEM_BYTES, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
   g_launches++;
   CU(cudaGetLastError());
   return B200_OK;
@@ -778,6 +790,8 @@ int b200_uastc_init(void) {
   CU(cudaSetDevice(dev));
   g_ctx.device = dev;
   g_ctx.sm_count = p.multiProcessorCount;
+  CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XT_SMEM_BYTES));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XT_SMEM_BYTES));
   g_ctx.ready = true;
   return B200_OK;
 }
