@@ -53,46 +53,80 @@ UB_FN EncCfg enc_cfg_from_flags(uint32_t flags) {
   return c;
 }
 
-// ---- fast partition error estimate of one subset (color_cell_compression_est_astc, channel weights all 1)
-UB_FN uint64_t est_astc(uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t n) {
-  uint32_t lo[4] = {255, 255, 255, 255}, hi[4] = {0, 0, 0, 0};
-  for (uint32_t i = 0; i < n; i++)
-    for (uint32_t c = 0; c < ncomps; c++) { const uint32_t v = ch(px[i], c); if (v < lo[c]) lo[c] = v; if (v > hi[c]) hi[c] = v; }
-  if (ncomps == 3) { lo[3] = 255; hi[3] = 255; }
-  uint32_t wc[32];
-  int dots[32];
-  const int ar = (int)hi[0] - (int)lo[0], ag = (int)hi[1] - (int)lo[1], ab = (int)hi[2] - (int)lo[2], aa = (int)hi[3] - (int)lo[3];
-  for (uint32_t i = 0; i < nw; i++) {
-    uint32_t v;
-    if (i == 0) v = pk(lo[0], lo[1], lo[2], lo[3]);
-    else if (i == nw - 1) v = pk(hi[0], hi[1], hi[2], hi[3]);
-    else {
-      const uint32_t w = sel_weight(nw, i);
-      v = pk(interp_linear(lo[0], hi[0], w), interp_linear(lo[1], hi[1], w), interp_linear(lo[2], hi[2], w),
-             ncomps == 4 ? interp_linear(lo[3], hi[3], w) : 255u);
-    }
-    wc[i] = v;
-    dots[i] = (int)ch(v, 0) * ar + (int)ch(v, 1) * ag + (int)ch(v, 2) * ab + (ncomps == 4 ? (int)ch(v, 3) * aa : 0);
-  }
-  uint64_t total = 0;
-  for (uint32_t i = 0; i < n; i++) {
-    const uint32_t c = px[i];
-    const int d = ar * (int)ch(c, 0) + ag * (int)ch(c, 1) + ab * (int)ch(c, 2) + (ncomps == 4 ? aa * (int)ch(c, 3) : 0);
-    uint32_t s = 0;
-    for (int j = (int)nw - 2; j >= 0; j--)
-      if (d >= ((dots[j] + dots[j + 1] + 1) >> 1)) { s = (uint32_t)j + 1; break; }
-    total += (ncomps == 4) ? dist_rgba(wc[s], c) : dist_rgb(wc[s], c);
-  }
-  return total;
+// ---- fast partition error estimate (color_cell_compression_est_astc per subset, channel weights all 1): the subset's
+// bounding box gives the axis and the two end colours, the palette is interpolated between them, every texel takes the
+// palette entry whose projection on the axis is nearest, squared distances are summed.
+UB_FN uint32_t minu4(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __vminu4(a, b);
+#else
+  uint32_t r = 0;
+  for (uint32_t c = 0; c < 4; c++) { const uint32_t x = ch(a, c), y = ch(b, c); r |= (x < y ? x : y) << (8 * c); }
+  return r;
+#endif
+}
+UB_FN uint32_t maxu4(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __vmaxu4(a, b);
+#else
+  uint32_t r = 0;
+  for (uint32_t c = 0; c < 4; c++) { const uint32_t x = ch(a, c), y = ch(b, c); r |= (x > y ? x : y) << (8 * c); }
+  return r;
+#endif
 }
 
-// total estimate of one pattern: `pat` = subset per texel (2 bits each)
+// total estimate of one pattern: `pat` = subset per texel (2 bits each).  All threads of a warp walk the pattern list
+// together, so the membership tests below are uniform branches and the subsets need no gathering.
 UB_FN uint64_t est_pattern(uint32_t nw, uint32_t ncomps, const uint32_t* px, uint32_t pat, uint32_t subsets) {
-  uint64_t total = 0;
+  const uint32_t cmask = (ncomps == 4) ? 0xFFFFFFFFu : 0x00FFFFFFu;   // RGB cells: alpha takes no part
+  uint32_t total = 0;
+#pragma unroll 1
   for (uint32_t s = 0; s < subsets; s++) {
-    uint32_t sub[16], n = 0;
-    for (uint32_t i = 0; i < 16; i++) if (((pat >> (2 * i)) & 3u) == s) sub[n++] = px[i];
-    total += est_astc(nw, ncomps, sub, n);
+    uint32_t lo = 0xFFFFFFFFu, hi = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++)
+      if (((pat >> (2 * i)) & 3u) == s) { lo = minu4(lo, px[i]); hi = maxu4(hi, px[i]); }
+    lo &= cmask; hi &= cmask;
+    const uint32_t axis = hi - lo;   // per byte hi >= lo: no borrows
+    // palette entries (astc_interpolate_linear per channel: (l*257*(64-w) + h*257*w + 32) >> 14) and, between
+    // neighbours, the projection value from which the upper one is nearer
+    uint32_t wc[8];
+    int thr[8];
+    int base[4], delta[4];
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      const int l = (int)(ch(lo, c) * 257u), h = (int)(ch(hi, c) * 257u);
+      base[c] = l * 64 + 32; delta[c] = h - l;
+    }
+    int prev = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < 8; i++) {
+      if (i < nw) {
+        uint32_t v;
+        if (i == 0) v = lo;
+        else if (i == nw - 1) v = hi;
+        else {
+          const int w = (int)sel_weight(nw, i);
+          v = pk((uint32_t)((base[0] + delta[0] * w) >> 14), (uint32_t)((base[1] + delta[1] * w) >> 14),
+                 (uint32_t)((base[2] + delta[2] * w) >> 14), (uint32_t)((base[3] + delta[3] * w) >> 14));
+        }
+        wc[i] = v;
+        const int dot = (int)dot4u(v, axis);
+        thr[i] = (prev + dot + 1) >> 1;   // thr[i]: boundary between entries i-1 and i (thr[0] unused)
+        prev = dot;
+      }
+    }
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++)
+      if (((pat >> (2 * i)) & 3u) == s) {
+        const uint32_t c = px[i] & cmask;
+        const int d = (int)dot4u(c, axis);
+        // the projections of the palette ascend along the axis, so "the highest boundary not above d" is a count
+        uint32_t sel = 0;
+#pragma unroll
+        for (uint32_t j = 1; j < 8; j++) if (j < nw && d >= thr[j]) sel++;
+        total += sqdist4(wc[sel], c);
+      }
   }
   return total;
 }
