@@ -236,6 +236,7 @@ UB_BIG uint32_t find_optimal_solution(Vec4 xl, Vec4 xh, const CccParams& p, cons
 // integer multiple of 1/64 -- integer accumulation followed by one conversion gives the identical double.
 UB_BIG void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t* px, Vec4& xl, Vec4& xh) {
   const uint32_t* wt = lsq_table(p.nw);
+  const uint8_t* wtab = weight_table(p.nw);   // nullptr for two levels (0, 64)
   const uint32_t nc = p.has_alpha ? 4u : 3u;
   double z00 = 0.0, z10 = 0.0, z11 = 0.0;
   uint32_t qi[4] = {0, 0, 0, 0}, t_rb = 0, t_ga = 0;
@@ -245,7 +246,7 @@ UB_BIG void least_squares(const CccParams& p, const uint8_t* sel, const uint32_t
     z00 = d_add(z00, (double)bits_to_float(wt[s * 4 + 0]));
     z10 = d_add(z10, (double)bits_to_float(wt[s * 4 + 1]));
     z11 = d_add(z11, (double)bits_to_float(wt[s * 4 + 2]));
-    const uint32_t w = sel_weight(p.nw, s);  // == 64 * wt[s*4+3]
+    const uint32_t w = wtab ? (uint32_t)wtab[s] : (s ? 64u : 0u);  // == 64 * wt[s*4+3]
     const uint32_t c = px[i];
 #pragma unroll
     for (uint32_t k = 0; k < 4; k++) qi[k] += w * ch(c, k);

@@ -22,45 +22,56 @@ UB_FN uint32_t px_set(uint32_t v, uint32_t c, uint32_t x) { return (v & ~(255u <
 // reference's fp32 summation order over channels and its strict-< choice between p = 0 and p = 1.
 // u_lo/u_hi: 8-bit unquantised endpoints per channel; a channel the reference pins to 1.0f must be passed as 255.
 // wide = true: 7+1 bits (BC7 modes 3 and 6); false: 5+1 bits (BC7 mode 7).
+// One table entry per 8-bit channel value: fp32 error for p = 0 and p = 1, and both quantised codes.
+UB_FN void pbit_entry(const uint32_t* tab, uint32_t u, float& e0, float& e1, uint32_t& codes) {
+#ifdef __CUDA_ARCH__
+  const uint4 v = __ldg((const uint4*)tab + u);
+  e0 = __uint_as_float(v.x); e1 = __uint_as_float(v.y); codes = v.z;
+#else
+  e0 = bits_to_float(tab[u * 4]); e1 = bits_to_float(tab[u * 4 + 1]); codes = tab[u * 4 + 2];
+#endif
+}
+
 UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
-  const uint8_t* code = wide ? UBT(pb8_code) : UBT(pb6_code);
-  const uint32_t* err = wide ? UBT(pb8_err) : UBT(pb6_err);
-  float best0 = 1e+9f, best1 = 1e+9f;
-  out_lo = 0; out_hi = 0; pb = 0;
+  const uint32_t* tab = wide ? UBT(pb8_q) : UBT(pb6_q);
+  uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
+  float e_lo0 = 0, e_lo1 = 0, e_hi0 = 0, e_hi1 = 0;
 #pragma unroll
-  for (uint32_t p = 0; p < 2; p++) {
-    uint32_t qmin = 0, qmax = 0;
-    float e0 = 0, e1 = 0;
-#pragma unroll
-    for (uint32_t c = 0; c < 4; c++) {
-      const uint32_t ia = p * 256 + px_c(u_lo, c), ib = p * 256 + px_c(u_hi, c);
-      qmin |= (uint32_t)code[ia] << (8 * c);
-      qmax |= (uint32_t)code[ib] << (8 * c);
-      if (c < total_comps) { e0 = f_add(e0, bits_to_float(err[ia])); e1 = f_add(e1, bits_to_float(err[ib])); }
-    }
-    if (e0 < best0) { best0 = e0; pb = (pb & ~1u) | p; out_lo = qmin; }
-    if (e1 < best1) { best1 = e1; pb = (pb & ~2u) | (p << 1); out_hi = qmax; }
+  for (uint32_t c = 0; c < 4; c++) {
+    float a0, a1, b0, b1;
+    uint32_t ca, cb;
+    pbit_entry(tab, px_c(u_lo, c), a0, a1, ca);
+    pbit_entry(tab, px_c(u_hi, c), b0, b1, cb);
+    q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
+    q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
+    if (c < total_comps) { e_lo0 = f_add(e_lo0, a0); e_lo1 = f_add(e_lo1, a1); e_hi0 = f_add(e_hi0, b0); e_hi1 = f_add(e_hi1, b1); }
   }
+  // the reference takes p = 0 first (its error is always below the 1e+9 start value) and p = 1 only if strictly better
+  const bool lo1 = e_lo1 < e_lo0, hi1 = e_hi1 < e_hi0;
+  out_lo = lo1 ? q_lo1 : q_lo0;
+  out_hi = hi1 ? q_hi1 : q_hi0;
+  pb = (lo1 ? 1u : 0u) | (hi1 ? 2u : 0u);
 }
 
 // determine_shared_pbits (XC:15532-15582), BC7 mode 1 only (3 comps, 6+1 bits, alpha = 1.0f == 255)
 UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
   u_lo |= 0xFF000000u; u_hi |= 0xFF000000u;
-  float best = 1e+9f;
-  out_lo = 0; out_hi = 0; pb = 0;
+  uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
+  float err0 = 0, err1 = 0;
 #pragma unroll
-  for (uint32_t p = 0; p < 2; p++) {
-    uint32_t qmin = 0, qmax = 0;
-    float err = 0;
-#pragma unroll
-    for (uint32_t c = 0; c < 4; c++) {
-      const uint32_t ia = p * 256 + px_c(u_lo, c), ib = p * 256 + px_c(u_hi, c);
-      qmin |= (uint32_t)UBT(pb7s_code)[ia] << (8 * c);
-      qmax |= (uint32_t)UBT(pb7s_code)[ib] << (8 * c);
-      if (c < 3) err = f_add(err, f_add(bits_to_float(UBT(pb7s_err)[ia]), bits_to_float(UBT(pb7s_err)[ib])));
-    }
-    if (err < best) { best = err; pb = p * 3u; out_lo = qmin; out_hi = qmax; }
+  for (uint32_t c = 0; c < 4; c++) {
+    float a0, a1, b0, b1;
+    uint32_t ca, cb;
+    pbit_entry(UBT(pb7s_q), px_c(u_lo, c), a0, a1, ca);
+    pbit_entry(UBT(pb7s_q), px_c(u_hi, c), b0, b1, cb);
+    q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
+    q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
+    if (c < 3) { err0 = f_add(err0, f_add(a0, b0)); err1 = f_add(err1, f_add(a1, b1)); }
   }
+  const bool p1 = err1 < err0;
+  pb = p1 ? 3u : 0u;
+  out_lo = p1 ? q_lo1 : q_lo0;
+  out_hi = p1 ? q_hi1 : q_hi0;
 }
 
 // Re-pack the UASTC weights (entries of wb bits) of one plane into `ob`-bit BC7 selectors through a tiny value map.

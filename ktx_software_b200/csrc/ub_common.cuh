@@ -16,6 +16,7 @@
 #define UB_FN_NOINLINE __device__ __noinline__
 #define UB_BIG __device__ __noinline__   /* large encoder stages: one out-of-line copy, called from every mode */
 #define UB_TABLE(type, name, n) static __device__ const type ubt_##name[n]
+#define UB_TABLE_ALIGNED16(type, name, n) static __device__ __align__(16) const type ubt_##name[n]
 #define UB_CONSTEXPR __host__ __device__ constexpr
 #else
 #define UB_FN static inline
@@ -23,6 +24,7 @@
 #define UB_FN_NOINLINE static
 #define UB_BIG static
 #define UB_TABLE(type, name, n) static const type ubt_##name[n]
+#define UB_TABLE_ALIGNED16(type, name, n) alignas(16) static const type ubt_##name[n]
 #define UB_CONSTEXPR constexpr
 #endif
 #define UBT(name) ubt_##name

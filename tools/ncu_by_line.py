@@ -27,6 +27,7 @@ for ch in re.split(r'(?m)^"Kernel Name",', out)[1:]:
         if len(p) >= 8 and p[3] == "FUNC" and kfilter in p[-1]:
             if not p[-1].startswith("$"): ksym = (int(p[1], 16), int(p[2], 0), p[-1])
             elif fwant in p[-1]: fsym = (int(p[1], 16), int(p[2], 0), p[-1])
+    if fwant == 'KERNEL': fsym = ksym   # the kernel's own body (everything inlined)
     # line table of the function: walk nvdisasm's text for the kernel's section, track "//## File ..., line N"
     sec = dis.split(".section\t.text." + ksym[2], 1)[1].split(".section", 1)[0]
     cur = ("?", 0); lines = {}
