@@ -239,14 +239,29 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 // The warps of a CTA walk the three phases of encode_uastc together (barrier between phases): all warps of the CTA
 // -- with one CTA per SM, all warps of the SM -- then execute the same few tens of KB of code at a time, which is
 // what the 32 KB instruction cache can hold; free-running warps spread over the whole ~300 KB kernel.
+// Thread index -> block of an image: consecutive groups of 32 threads (a warp) take an 8 x 4 patch of blocks (32 x 16
+// texels) instead of a 32 x 1 strip, so the lanes of a warp see similar content and diverge less.  A permutation of
+// [0, bx * by): whole patches first inside each band of four block rows, then that band's ragged columns; the last
+// by % 4 rows stay in raster order.
+__device__ __forceinline__ uint64_t block_of_thread(uint64_t i, uint32_t bx, uint32_t by) {
+  const uint64_t band = 4ull * bx;
+  if (i >= (uint64_t)(by / 4) * band) return i;
+  const uint32_t r = (uint32_t)(i / band), j = (uint32_t)(i % band), bx8 = bx & ~7u;
+  uint32_t x, y;
+  if (j < 4 * bx8) { x = (j >> 5) * 8 + (j & 7u); y = (j & 31u) >> 3; }
+  else { const uint32_t jj = j - 4 * bx8, rc = bx - bx8; x = bx8 + jj % rc; y = jj / rc; }
+  return (uint64_t)(r * 4 + y) * bx + x;
+}
+
 template <int MAXC, typename LOAD>
-__device__ __forceinline__ void encode_phased(uint64_t n, uint32_t flags, uint4* __restrict__ out, LOAD load_px) {
+__device__ __forceinline__ void encode_phased(uint64_t n, uint32_t flags, uint4* __restrict__ out, LOAD load_px, uint32_t bx = 0, uint32_t by = 0) {
   ub::Candidate cands[MAXC];
   uint64_t overall[MAXC];
   float uerr[MAXC];
   for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n; base += (uint64_t)gridDim.x * blockDim.x) {  // uniform per CTA
-    const uint64_t i = base + threadIdx.x;
-    const bool live = i < n;
+    const uint64_t t = base + threadIdx.x;
+    const bool live = t < n;
+    const uint64_t i = (live && bx) ? block_of_thread(t, bx, by) : t;   // bx = 0: blocks are not laid out as an image
     uint32_t px[16];
     ub::EncState st;
     if (live) load_px(i, px);
@@ -284,7 +299,7 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_image(cons
 #pragma unroll
     for (uint32_t k = 0; k < 16; k++) amin = min(amin, px[k] >> 24);
     if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
-  });
+  }, bx, by);
 }
 
 // Several images in one launch (a mip chain, the faces of a cube map): block i belongs to the image whose
@@ -312,7 +327,7 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_images(con
       uint32_t lo = 0, hi = n_images - 1;  // last image whose first_block <= i
       while (lo < hi) { const uint32_t mid = (lo + hi + 1) >> 1; if (descs[mid].first_block <= i) lo = mid; else hi = mid - 1; }
       const EncImageDesc d = descs[lo];
-      const uint64_t k = i - d.first_block;
+      const uint64_t k = block_of_thread(i - d.first_block, d.bx, (d.h + 3) / 4);
       dst = d.out + k;
       const uint32_t x0 = (uint32_t)(k % d.bx) * 4, y0 = (uint32_t)(k / d.bx) * 4;
       uint32_t amin = 255;
