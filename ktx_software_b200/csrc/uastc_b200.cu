@@ -239,11 +239,12 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 // The warps of a CTA walk the three phases of encode_uastc together (barrier between phases): all warps of the CTA
 // -- with one CTA per SM, all warps of the SM -- then execute the same few tens of KB of code at a time, which is
 // what the 32 KB instruction cache can hold; free-running warps spread over the whole ~300 KB kernel.
-// Thread index -> block of an image: consecutive groups of 32 threads (a warp) take an 8 x 4 patch of blocks (32 x 16
-// texels) instead of a 32 x 1 strip, so the lanes of a warp see similar content and diverge less.  A permutation of
-// [0, bx * by): whole patches first inside each band of four block rows, then that band's ragged columns; the last
-// by % 4 rows stay in raster order.
-__device__ __forceinline__ uint64_t block_of_thread(uint64_t i, uint32_t bx, uint32_t by) {
+// Thread index -> block of an image.  Consecutive groups of 32 threads (a warp) take an 8 x 4 patch of blocks (32 x 16
+// texels) instead of a 32 x 1 strip, so the lanes of a warp see similar content and diverge less; and consecutive
+// groups of 1024 threads (a full-size CTA) take a 32 x 32 tile of blocks, so the warps that meet at the stage barriers
+// carry similar work.  A permutation of [0, bx * by): the 32 x 32 tiles first, then the columns right of the last
+// whole tile, then the rows below the last whole band, both in 8 x 4 patches as far as they go.
+__device__ __forceinline__ uint64_t patch_index(uint64_t i, uint32_t bx, uint32_t by) {   // 8 x 4 patches inside a bx x by rectangle
   const uint64_t band = 4ull * bx;
   if (i >= (uint64_t)(by / 4) * band) return i;
   const uint32_t r = (uint32_t)(i / band), j = (uint32_t)(i % band), bx8 = bx & ~7u;
@@ -251,6 +252,23 @@ __device__ __forceinline__ uint64_t block_of_thread(uint64_t i, uint32_t bx, uin
   if (j < 4 * bx8) { x = (j >> 5) * 8 + (j & 7u); y = (j & 31u) >> 3; }
   else { const uint32_t jj = j - 4 * bx8, rc = bx - bx8; x = bx8 + jj % rc; y = jj / rc; }
   return (uint64_t)(r * 4 + y) * bx + x;
+}
+__device__ __forceinline__ uint64_t block_of_thread(uint64_t i, uint32_t bx, uint32_t by) {
+  const uint32_t tpb = bx / 32, bands = by / 32;            // whole tiles per band, whole bands
+  const uint64_t n_tiled = (uint64_t)tpb * bands * 1024;
+  if (i < n_tiled) {
+    const uint32_t tile = (uint32_t)(i >> 10), within = (uint32_t)(i & 1023u), warp = within >> 5, lane = within & 31u;
+    const uint32_t x = (tile % tpb) * 32 + (warp & 3u) * 8 + (lane & 7u), y = (tile / tpb) * 32 + (warp >> 2) * 4 + (lane >> 3);
+    return (uint64_t)y * bx + x;
+  }
+  uint64_t q = i - n_tiled;
+  const uint32_t rc = bx - tpb * 32, rows_t = bands * 32;   // ragged columns beside the tiles
+  if (q < (uint64_t)rc * rows_t) {
+    const uint64_t k = patch_index(q, rc, rows_t);
+    return (k / rc) * bx + tpb * 32 + (k % rc);
+  }
+  q -= (uint64_t)rc * rows_t;
+  return (uint64_t)rows_t * bx + patch_index(q, bx, by - rows_t);   // rows below the last whole band
 }
 
 template <int MAXC, typename LOAD>
