@@ -299,7 +299,9 @@ def run_c5(args):
                         "blocks": ne, "api": "b200_uastc_transcode (host pinned buffers)", "matches_device_path": e2e_ok},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                             "frac": achieved / pk["hbm_gbs"], "traffic": None, "peak_kind": pk_kind,
+                             "frac": achieved / pk["hbm_gbs"],
+                             # ncu --set full of this workload (profiles/r2i_transcode_tiled_ncu_summary.txt), 2^26 blocks
+                             "traffic": (1.076825e9 + 1.027500e9) if n == (1 << 26) else None, "peak_kind": pk_kind,
                              "kernel": "k_transcode_tiled<BC7>", "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": 32 * n},
                 "cpu_baseline": cpu}
         print(json.dumps(line))
