@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 // The warps of a CTA walk the three phases of encode_uastc together (barrier between phases): all warps of the CTA
 // -- with one CTA per SM, all warps of the SM -- then execute the same few tens of KB of code at a time, which is
 // what the 32 KB instruction cache can hold; free-running warps spread over the whole ~300 KB kernel.
-// Thread index -> block of an image.  Consecutive groups of 32 threads (a warp) take an 8 x 4 patch of blocks (32 x 16
+// Thread index -> block of an image.  Consecutive groups of 32 threads (a warp) take a 4 x 8 patch of blocks (16 x 32
 // texels) instead of a 32 x 1 strip, so the lanes of a warp see similar content and diverge less; and consecutive
 // groups of 1024 threads (a full-size CTA) take a 32 x 32 tile of blocks, so the warps that meet at the stage barriers
 // carry similar work.  A permutation of [0, bx * by): the 32 x 32 tiles first, then the columns right of the last
@@ -253,19 +253,26 @@ __device__ __forceinline__ uint64_t patch_index(uint64_t i, uint32_t bx, uint32_
   else { const uint32_t jj = j - 4 * bx8, rc = bx - bx8; x = bx8 + jj % rc; y = jj / rc; }
   return (uint64_t)(r * 4 + y) * bx + x;
 }
+#ifndef ENC_TILE_W
+#define ENC_TILE_W 32   // blocks per CTA tile row (tile = 1024 blocks)
+#endif
+#ifndef ENC_PATCH_W
+#define ENC_PATCH_W 4   // blocks per warp patch row (patch = 32 blocks: 4 x 8, i.e. 16 x 32 texels)
+#endif
 __device__ __forceinline__ uint64_t block_of_thread(uint64_t i, uint32_t bx, uint32_t by) {
-  const uint32_t tpb = bx / 32, bands = by / 32;            // whole tiles per band, whole bands
+  constexpr uint32_t TW = ENC_TILE_W, TH = 1024 / TW, PW = ENC_PATCH_W, PH = 32 / PW, PPR = TW / PW;
+  const uint32_t tpb = bx / TW, bands = by / TH;            // whole tiles per band, whole bands
   const uint64_t n_tiled = (uint64_t)tpb * bands * 1024;
   if (i < n_tiled) {
     const uint32_t tile = (uint32_t)(i >> 10), within = (uint32_t)(i & 1023u), warp = within >> 5, lane = within & 31u;
-    const uint32_t x = (tile % tpb) * 32 + (warp & 3u) * 8 + (lane & 7u), y = (tile / tpb) * 32 + (warp >> 2) * 4 + (lane >> 3);
+    const uint32_t x = (tile % tpb) * TW + (warp % PPR) * PW + (lane % PW), y = (tile / tpb) * TH + (warp / PPR) * PH + (lane / PW);
     return (uint64_t)y * bx + x;
   }
   uint64_t q = i - n_tiled;
-  const uint32_t rc = bx - tpb * 32, rows_t = bands * 32;   // ragged columns beside the tiles
+  const uint32_t rc = bx - tpb * TW, rows_t = bands * TH;   // ragged columns beside the tiles
   if (q < (uint64_t)rc * rows_t) {
     const uint64_t k = patch_index(q, rc, rows_t);
-    return (k / rc) * bx + tpb * 32 + (k % rc);
+    return (k / rc) * bx + tpb * TW + (k % rc);
   }
   q -= (uint64_t)rc * rows_t;
   return (uint64_t)rows_t * bx + patch_index(q, bx, by - rows_t);   // rows below the last whole band
