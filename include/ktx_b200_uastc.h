@@ -28,6 +28,11 @@ extern "C" {
 /* Transcode targets; numeric values are ktx_transcode_fmt_e's (lib/include/ktx.h:1696-1703). */
 #define B200_TTF_BC7_RGBA 6
 #define B200_TTF_ASTC_4x4_RGBA 10
+/* uncompressed targets (b200_uastc_decode*): KTX_TTF_RGBA32 / RGB565 / BGR565 / RGBA4444 (lib/include/ktx.h:1728-1737) */
+#define B200_TTF_RGBA32 13
+#define B200_TTF_RGB565 14
+#define B200_TTF_BGR565 15
+#define B200_TTF_RGBA4444 16
 
 /* Replaces basisu_encoder_init() (lib/src/basis_encode.cpp:625-633) and basisu_transcoder_init()
  * (lib/src/basis_transcode.cpp:427-436).  Idempotent and thread-safe.  Selects the current CUDA device
@@ -60,6 +65,31 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
  * Asynchronous with respect to the host when a stream is given. */
 int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, uint64_t n_blocks, void* stream,
                              uint64_t* d_first_bad);
+
+/* ---- decode to texels (the uncompressed transcode targets) ------------------------------------------ */
+
+/* One (level, layer, face/slice) image: its UASTC blocks in raster order at src_base + src_offset, and where its
+ * width x height texels go (tight rows of `width` texels, as libktx sizes the transcoded level: it passes
+ * output_row_pitch_in_blocks_or_pixels = 0 and output_rows_in_pixels = 0, lib/src/basis_transcode.cpp:790-793). */
+typedef struct b200_decode_image {
+  uint64_t src_offset;
+  uint64_t dst_offset;
+  uint32_t width, height; /* texels; the image holds ceil(width/4) * ceil(height/4) blocks */
+} b200_decode_image;
+
+/* Replaces the same per-image loop of transcodeUastcLDR4x4 (lib/src/basis_transcode.cpp:743-804) for the targets
+ * KTX_TTF_RGBA32, KTX_TTF_RGB565, KTX_TTF_BGR565 and KTX_TTF_RGBA4444, i.e. transcode_image (XC/basisu_transcoder.cpp:10331)
+ * -> transcode_slice's cRGBA32 / cRGB565 / cBGR565 / cRGBA4444 cases (XC:10208-10292) -> unpack_uastc to pixels
+ * (XC:15378-15529, srgb = false); texels past width / height are clipped as there.  HOST pointers.  On
+ * B200_E_BAD_BLOCK *bad_image (if non-NULL) receives the index of the first image holding an invalid block. */
+int b200_uastc_decode(uint32_t target, const b200_decode_image* images, uint32_t n_images, const uint8_t* src_base,
+                      uint8_t* dst_base, int64_t* bad_image);
+
+/* Device-resident variant, one image: d_src = ceil(w/4)*ceil(h/4) blocks, d_dst = height rows of
+ * dst_row_pitch_texels (0 = width) texels of 4 (RGBA32) or 2 bytes.  d_first_bad as in b200_uastc_transcode_dev.
+ * Asynchronous with respect to the host when a stream is given. */
+int b200_uastc_decode_image_dev(uint32_t target, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                uint32_t dst_row_pitch_texels, void* stream, uint64_t* d_first_bad);
 
 /* ---- encode ---------------------------------------------------------------------------------------- */
 

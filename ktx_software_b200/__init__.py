@@ -6,4 +6,5 @@ libktx's ktxTexture2_TranscodeBasis / ktxTexture2_CompressBasisEx marshalling (k
 fallback anywhere in this package: if the CUDA library is missing, or no B200 is visible, calls raise.
 """
 from .api import (B200Error, lib, init, transcode, transcode_dev, launch_count, encode_images, encode_blocks, encode_blocks_dev, encode_image_dev, encode_images_dev, rdo_blocks_dev, TTF_BC7_RGBA, TTF_ASTC_4x4_RGBA,  # noqa: F401
+                  decode, decode_image_dev, TTF_RGBA32, TTF_RGB565, TTF_BGR565, TTF_RGBA4444,
                   EXPORTED_SYMBOLS)

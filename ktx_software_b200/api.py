@@ -7,10 +7,12 @@ LIB_PATH = os.environ.get("B200_UASTC_LIB") or os.path.join(HERE, "libuastc_b200
 
 TTF_BC7_RGBA = 6        # ktx_transcode_fmt_e KTX_TTF_BC7_RGBA (lib/include/ktx.h)
 TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
+TTF_RGBA32, TTF_RGB565, TTF_BGR565, TTF_RGBA4444 = 13, 14, 15, 16  # the uncompressed targets (ktx.h:1728-1737)
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
-                    "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev"]
+                    "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
+                    "b200_uastc_decode", "b200_uastc_decode_image_dev"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -23,6 +25,10 @@ class B200Error(RuntimeError):
 
 class XcodeSpan(ctypes.Structure):
     _fields_ = [("src_offset", ctypes.c_uint64), ("dst_offset", ctypes.c_uint64), ("n_blocks", ctypes.c_uint64)]
+
+
+class DecodeImage(ctypes.Structure):
+    _fields_ = [("src_offset", ctypes.c_uint64), ("dst_offset", ctypes.c_uint64), ("width", ctypes.c_uint32), ("height", ctypes.c_uint32)]
 
 
 class Image(ctypes.Structure):
@@ -64,6 +70,10 @@ def lib():
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_rdo_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.POINTER(UastcParams), ctypes.c_void_p]
         l.b200_uastc_encode_images_dev.argtypes = [ctypes.POINTER(DevImage), ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        l.b200_uastc_decode.argtypes = [ctypes.c_uint32, ctypes.POINTER(DecodeImage), ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                                        ctypes.POINTER(ctypes.c_int64)]
+        l.b200_uastc_decode_image_dev.argtypes = [ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32,
+                                                  ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         _lib = l
     return _lib
 
@@ -104,6 +114,36 @@ def transcode(src, target, spans=None, dst=None):
 def transcode_dev(target, d_src, d_dst, n_blocks, stream=0, d_first_bad=0):
     """Device-pointer transcode (ints / torch data_ptr()); asynchronous when a stream handle is given."""
     _check(lib().b200_uastc_transcode_dev(target, d_src, d_dst, n_blocks, stream or None, d_first_bad or None))
+
+
+def decode(src, target, images):
+    """Host-buffer decode to texels through the C ABI (b200_uastc_decode).  src: uint8 array of UASTC blocks;
+    images: list of (src_offset, width, height), each image's blocks in raster order.  Returns a list of arrays:
+    uint8 [h,w,4] for TTF_RGBA32, uint16 [h,w] for the 16-bit targets.  B200Error(code=-5) carries .bad_image."""
+    src = np.ascontiguousarray(src, dtype=np.uint8).reshape(-1)
+    bpp = 4 if target == TTF_RGBA32 else 2
+    offs, total = [], 0
+    for _, w, h in images:
+        offs.append(total)
+        total += (w * h * bpp + 15) & ~15
+    dst = np.zeros(max(total, 16), np.uint8)
+    arr = (DecodeImage * max(1, len(images)))(*[DecodeImage(so, do, w, h) for (so, w, h), do in zip(images, offs)])
+    bad = ctypes.c_int64(-1)
+    rc = lib().b200_uastc_decode(target, arr, len(images), src.ctypes.data, dst.ctypes.data, ctypes.byref(bad))
+    if rc != 0:
+        e = B200Error(rc, lib().b200_uastc_last_error().decode())
+        e.bad_image = bad.value
+        raise e
+    out = []
+    for (_, w, h), do in zip(images, offs):
+        raw = dst[do:do + w * h * bpp]
+        out.append(raw.reshape(h, w, 4) if bpp == 4 else raw.view(np.uint16).reshape(h, w))
+    return out
+
+
+def decode_image_dev(target, d_src, d_dst, width, height, row_pitch_texels=0, stream=0, d_first_bad=0):
+    """Device-pointer decode of one image's blocks to width x height texels (b200_uastc_decode_image_dev)."""
+    _check(lib().b200_uastc_decode_image_dev(target, d_src, d_dst, width, height, row_pitch_texels, stream or None, d_first_bad or None))
 
 
 def encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream=0):

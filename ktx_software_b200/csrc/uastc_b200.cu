@@ -17,6 +17,7 @@
 #include "uastc_to_astc.cuh"
 #include "uastc_encode.cuh"
 #include "uastc_rdo.cuh"
+#include "uastc_to_rgba.cuh"
 
 namespace {
 
@@ -76,8 +77,6 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
 #ifndef XT_CTAS_PER_SM
 #define XT_CTAS_PER_SM 1
 #endif
-const int XT_PER_THREAD = XT_TILE / XT_THREADS;
-const size_t XT_SMEM_BYTES = 2 * (size_t)XT_TILE * 16 + (size_t)XT_TILE * 2 + 32 * 4 + 2 * 8;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -120,20 +119,109 @@ __device__ __forceinline__ bool transcode_dispatch(uint32_t mode, const ub::Bits
   }
 }
 
-template <int TARGET>
+__device__ __forceinline__ bool texel_form_dispatch(uint32_t mode, const ub::Bits128& s, ub::TexelForm& f) {
+  switch (mode) {
+#define XC_CASE(M) case M: return ub::texel_form_t<M>(s, f);
+    XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
+    XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
+#undef XC_CASE
+    default: ub::texel_form_clear(f); return false;   // reserved mode code: the form decodes to zeros
+  }
+}
+
+// Uncompressed targets (TARGET 2): the blocks of ONE image in raster order are written as texels into a w x h image
+// (the cRGBA32 / cRGB565 / cBGR565 / cRGBA4444 cases of transcode_slice, XC:10208-10292: rows and columns past the
+// image's own size are clipped).
+struct XtImage {
+  uint32_t w, h;         // texels
+  uint32_t bx;           // blocks per row
+  uint32_t pitch_px;     // destination row pitch in texels
+  uint32_t kind;         // 13 = RGBA32, 14 = RGB565, 15 = BGR565, 16 = RGBA4444 (ktx_transcode_fmt_e values)
+  uint32_t vec_ok;       // destination base and pitch allow 16-byte (RGBA32) / 8-byte (16-bit targets) row stores
+};
+
+#ifndef XT_DECODE_STAGED
+#define XT_DECODE_STAGED 1   // 1: texel rows leave through a shared-memory staging tile (coalesced); 0: straight from registers
+#endif
+__host__ __device__ constexpr int xt_tile(int target) { return (target == 2 && XT_DECODE_STAGED) ? 2048 : XT_TILE; }   // staging holds 64 B per block
+__host__ __device__ constexpr int xt_data_tiles(int target) { return (target == 2 && XT_DECODE_STAGED) ? 6 : 2; }
+constexpr size_t xt_smem_bytes(int target) { return (size_t)xt_data_tiles(target) * xt_tile(target) * 16 + 2 * 8 + 32 * 4 + (size_t)xt_tile(target) * 2; }
+
+__device__ __forceinline__ void store_block_texels(uint8_t* __restrict__ dst, const XtImage& im, uint64_t block_index, const uint32_t* px) {
+  const uint32_t by = (uint32_t)(block_index / im.bx), bxi = (uint32_t)(block_index - (uint64_t)by * im.bx);
+  const uint32_t x0 = bxi * 4, y0 = by * 4;
+  const bool fast = im.vec_ok && x0 + 4 <= im.w && y0 + 4 <= im.h;
+  const uint32_t bpp = im.kind == 13 ? 4u : 2u;
+  uint8_t* row = dst + ((size_t)y0 * im.pitch_px + x0) * bpp;
+#pragma unroll
+  for (int y = 0; y < 4; y++) {
+    uint32_t q[4];
+#pragma unroll
+    for (int x = 0; x < 4; x++) q[x] = im.kind == 13 ? px[4 * y + x] : ub::pack_texel16(px[4 * y + x], im.kind);
+    if (fast) {
+      if (im.kind == 13) *(uint4*)row = make_uint4(q[0], q[1], q[2], q[3]);
+      else *(uint2*)row = make_uint2(q[0] | (q[1] << 16), q[2] | (q[3] << 16));
+    } else if (y0 + y < im.h) {
+#pragma unroll
+      for (int x = 0; x < 4; x++)
+        if (x0 + x < im.w) { if (im.kind == 13) ((uint32_t*)row)[x] = q[x]; else ((uint16_t*)row)[x] = (uint16_t)q[x]; }
+    }
+    row += (size_t)im.pitch_px * bpp;
+  }
+}
+
+// Row pieces of block `slot` of the staging tile -> the image.  Full blocks of an aligned destination take one
+// 16-byte (RGBA32) or 8-byte (16-bit targets) store per texel row; edge blocks and unaligned images go texel by texel.
+__device__ __forceinline__ void store_block_rows(uint8_t* __restrict__ dst, const XtImage& im, uint64_t block_index, const uint4* s_out,
+                                                 uint32_t tile, uint32_t slot) {
+  const uint32_t by = (uint32_t)(block_index / im.bx), bxi = (uint32_t)(block_index - (uint64_t)by * im.bx);
+  const uint32_t x0 = bxi * 4, y0 = by * 4;
+  const bool fast = im.vec_ok && x0 + 4 <= im.w && y0 + 4 <= im.h;
+  if (im.kind == 13) {
+    uint8_t* row = dst + ((size_t)y0 * im.pitch_px + x0) * 4;
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      const uint4 v = s_out[y * tile + slot];
+      if (fast) *(uint4*)row = v;
+      else if (y0 + y < im.h) {
+        const uint32_t q[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int x = 0; x < 4; x++) if (x0 + x < im.w) ((uint32_t*)row)[x] = q[x];
+      }
+      row += (size_t)im.pitch_px * 4;
+    }
+  } else {
+    uint8_t* row = dst + ((size_t)y0 * im.pitch_px + x0) * 2;
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      const uint2 v = ((const uint2*)s_out)[y * tile + slot];
+      if (fast) *(uint2*)row = v;
+      else if (y0 + y < im.h) {
+        const uint32_t q[4] = {v.x & 0xFFFFu, v.x >> 16, v.y & 0xFFFFu, v.y >> 16};
+#pragma unroll
+        for (int x = 0; x < 4; x++) if (x0 + x < im.w) ((uint16_t*)row)[x] = (uint16_t)q[x];
+      }
+      row += (size_t)im.pitch_px * 2;
+    }
+  }
+}
+
+template <int TARGET>   // 0 = BC7, 1 = ASTC (dst = blocks, written through the shared-memory tile), 2 = texels (dst = image, im)
 __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
-                                                                unsigned long long* __restrict__ first_bad) {
+                                                                unsigned long long* __restrict__ first_bad, const XtImage im) {
+  constexpr int TILE = xt_tile(TARGET), PER_THREAD = TILE / XT_THREADS;
   extern __shared__ __align__(128) unsigned char xt_smem[];
-  uint4 (*s_in)[XT_TILE] = (uint4 (*)[XT_TILE])xt_smem;  // [2][XT_TILE]; a block's result overwrites its own input slot
-  uint64_t* s_bar = (uint64_t*)(xt_smem + 2 * (size_t)XT_TILE * 16);
+  uint4 (*s_in)[TILE] = (uint4 (*)[TILE])xt_smem;  // [2][TILE]; a block's result overwrites its own input slot
+  uint4* s_out = (uint4*)(xt_smem + 2 * (size_t)TILE * 16);   // TARGET 2 only: [4 texel rows][TILE] row pieces of 16 (or 8) bytes
+  uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_tiles(TARGET) * (size_t)TILE * 16);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
   uint16_t* s_order = (uint16_t*)(s_hist + 32);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
-  const uint64_t n_tiles = (n_blocks + XT_TILE - 1) / XT_TILE;
+  const uint64_t n_tiles = (n_blocks + TILE - 1) / TILE;
   uint64_t tile = blockIdx.x;
   if (tile >= n_tiles) return;
-  auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)XT_TILE, n_blocks - t * XT_TILE); };
+  auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)TILE, n_blocks - t * TILE); };
 
   if (tid < 32) s_hist[tid] = 0;
   if (tid == 0) {
@@ -143,7 +231,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     fence_proxy_async();
     const uint32_t bytes = tile_count(tile) * 16u;
     mbar_expect_tx(&s_bar[0], bytes);
-    bulk_g2s(s_in[0], src + tile * XT_TILE, bytes, &s_bar[0]);
+    bulk_g2s(s_in[0], src + tile * TILE, bytes, &s_bar[0]);
   }
   __syncthreads();
 
@@ -155,15 +243,15 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
       bulk_wait_read0();
       const uint32_t bytes = tile_count(next) * 16u;
       mbar_expect_tx(&s_bar[buf ^ 1], bytes);
-      bulk_g2s(s_in[buf ^ 1], src + next * XT_TILE, bytes, &s_bar[buf ^ 1]);
+      bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
     }
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
 
     // ---- bin by mode: rank inside the bin from a warp-aggregated shared atomic (s_hist is zero on entry)
-    uint32_t my_mode[XT_PER_THREAD], my_rank[XT_PER_THREAD];
+    uint32_t my_mode[PER_THREAD], my_rank[PER_THREAD];
 #pragma unroll
-    for (int k = 0; k < XT_PER_THREAD; k++) {
+    for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
       const bool live = i < cnt;
       const uint32_t m = live ? (uint32_t)ub::UBT(uastc_huff_modes)[s_in[buf][live ? i : 0].x & 127u] : 31u;
@@ -186,7 +274,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
       bin_start = v - c;
     }
 #pragma unroll
-    for (int k = 0; k < XT_PER_THREAD; k++) {
+    for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
       const uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, my_mode[k]);
       if (i < cnt) s_order[start + my_rank[k]] = (uint16_t)i;
@@ -196,7 +284,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
 #pragma unroll 1
-    for (int k = 0; k < XT_PER_THREAD; k++) {
+    for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t j = tid + k * XT_THREADS;
       if (j < cnt) {
         const uint32_t idx = s_order[j];
@@ -205,16 +293,43 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         ub::Bits128 s, d;
         s.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
         s.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
-        const bool ok = transcode_dispatch<TARGET>(m, s, d);
-        uint4 o;
-        o.x = (uint32_t)d.lo; o.y = (uint32_t)(d.lo >> 32); o.z = (uint32_t)d.hi; o.w = (uint32_t)(d.hi >> 32);
-        s_in[buf][idx] = o;
-        if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)(tile * XT_TILE + idx));
+        bool ok;
+        if (TARGET == 2) {
+          uint32_t px[16];
+          ub::TexelForm f;
+          ok = texel_form_dispatch(m, s, f);   // mode-specialised
+          ub::texels_from_form(f, px);          // shared by all modes: lanes of mixed warps reconverge here
+          // texel rows of the block go to the staging tile in BLOCK order (not sorted order), one piece per row
+          if (!XT_DECODE_STAGED) store_block_texels((uint8_t*)dst, im, tile * TILE + idx, px);
+          else if (im.kind == 13) {
+#pragma unroll
+            for (int y = 0; y < 4; y++) s_out[y * TILE + idx] = make_uint4(px[4 * y], px[4 * y + 1], px[4 * y + 2], px[4 * y + 3]);
+          } else {
+#pragma unroll
+            for (int y = 0; y < 4; y++) {
+              uint32_t q[4];
+#pragma unroll
+              for (int x = 0; x < 4; x++) q[x] = ub::pack_texel16(px[4 * y + x], im.kind);
+              ((uint2*)s_out)[y * TILE + idx] = make_uint2(q[0] | (q[1] << 16), q[2] | (q[3] << 16));
+            }
+          }
+        } else {
+          ok = transcode_dispatch<TARGET>(m, s, d);
+          uint4 o;
+          o.x = (uint32_t)d.lo; o.y = (uint32_t)(d.lo >> 32); o.z = (uint32_t)d.hi; o.w = (uint32_t)(d.hi >> 32);
+          s_in[buf][idx] = o;
+        }
+        if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)(tile * TILE + idx));
       }
     }
-    fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
+    if (TARGET != 2) fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
     __syncthreads();
-    if (tid == 0) bulk_s2g(dst + tile * XT_TILE, s_in[buf], cnt * 16u);
+    if (TARGET != 2 && tid == 0) bulk_s2g(dst + tile * TILE, s_in[buf], cnt * 16u);
+    if (TARGET == 2 && XT_DECODE_STAGED) {
+      // consecutive threads take consecutive blocks of the image: their row pieces are consecutive in global memory
+      for (uint32_t j = tid; j < cnt; j += XT_THREADS) store_block_rows((uint8_t*)dst, im, tile * TILE + j, s_out, TILE, j);
+      // (the barrier after the next tile's binning orders these reads before the next writes of s_out)
+    }
     buf ^= 1;
   }
   if (tid == 0) bulk_wait0();
@@ -638,9 +753,28 @@ int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n
   const uint64_t tiles = (n + XT_TILE - 1) / XT_TILE;
   const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
   if (target == B200_TTF_BC7_RGBA)
-    k_transcode_tiled<0><<<grid, XT_THREADS, XT_SMEM_BYTES, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<0><<<grid, XT_THREADS, xt_smem_bytes(0), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, XtImage{});
   else
-    k_transcode_tiled<1><<<grid, XT_THREADS, XT_SMEM_BYTES, st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad);
+    k_transcode_tiled<1><<<grid, XT_THREADS, xt_smem_bytes(1), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, XtImage{});
+  g_launches++;
+  CU(cudaGetLastError());
+  return B200_OK;
+}
+
+bool is_texel_target(uint32_t t) { return t == B200_TTF_RGBA32 || t == B200_TTF_RGB565 || t == B200_TTF_BGR565 || t == B200_TTF_RGBA4444; }
+uint32_t texel_bytes(uint32_t t) { return t == B200_TTF_RGBA32 ? 4u : 2u; }
+
+// One image's blocks (raster order, ceil(w/4) x ceil(h/4)) -> w x h texels at d_dst, row pitch in texels.
+int launch_decode(uint32_t target, const void* d_src, void* d_dst, uint32_t w, uint32_t h, uint32_t pitch_px, cudaStream_t st, uint64_t* d_first_bad) {
+  if (!w || !h) return B200_OK;
+  XtImage im;
+  im.w = w; im.h = h; im.bx = (w + 3) / 4; im.pitch_px = pitch_px; im.kind = target;
+  const uint32_t row_align = target == B200_TTF_RGBA32 ? 4u : 4u;   // 4 texels = 16 B (RGBA32) or 8 B (16-bit targets)
+  im.vec_ok = (pitch_px % row_align == 0 && ((uintptr_t)d_dst % (target == B200_TTF_RGBA32 ? 16 : 8)) == 0) ? 1u : 0u;
+  const uint64_t n = (uint64_t)im.bx * ((h + 3) / 4);
+  const uint64_t tiles = (n + xt_tile(2) - 1) / xt_tile(2);
+  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
+  k_transcode_tiled<2><<<grid, XT_THREADS, xt_smem_bytes(2), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im);
   g_launches++;
   CU(cudaGetLastError());
   return B200_OK;
@@ -830,8 +964,9 @@ int b200_uastc_init(void) {
   CU(cudaSetDevice(dev));
   g_ctx.device = dev;
   g_ctx.sm_count = p.multiProcessorCount;
-  CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XT_SMEM_BYTES));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XT_SMEM_BYTES));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(0)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(1)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(2)));
   g_ctx.ready = true;
   return B200_OK;
 }
@@ -856,6 +991,104 @@ int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, ui
   rc = launch_transcode(target, d_src, d_dst, n_blocks, st, d_first_bad);
   if (rc) return rc;
   if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+int b200_uastc_decode_image_dev(uint32_t target, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
+                                uint32_t dst_row_pitch_texels, void* stream, uint64_t* d_first_bad) {
+  if (!is_texel_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported decode target");
+  if (width && height && (!d_src || !d_dst)) return fail(B200_E_INVALID_VALUE, "null device pointer");
+  if (dst_row_pitch_texels && dst_row_pitch_texels < width) return fail(B200_E_INVALID_VALUE, "row pitch smaller than the image");
+  if (((uintptr_t)d_dst % texel_bytes(target)) != 0) return fail(B200_E_INVALID_VALUE, "destination not aligned to the texel size");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
+  if (d_first_bad) { k_set_u64<<<1, 1, 0, st>>>((unsigned long long*)d_first_bad, ~0ull); g_launches++; }
+  rc = launch_decode(target, d_src, d_dst, width, height, dst_row_pitch_texels ? dst_row_pitch_texels : width, st, d_first_bad);
+  if (rc) return rc;
+  if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
+}
+
+int b200_uastc_decode(uint32_t target, const b200_decode_image* images, uint32_t n_images, const uint8_t* src_base,
+                      uint8_t* dst_base, int64_t* bad_image) {
+  if (bad_image) *bad_image = -1;
+  if (!is_texel_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported decode target");
+  if (n_images && (!images || !src_base || !dst_base)) return fail(B200_E_INVALID_VALUE, "null pointer");
+  int rc = b200_uastc_init();
+  if (rc) return rc;
+  cudaStream_t* ss;
+  rc = get_streams(&ss);
+  if (rc) return rc;
+  const uint32_t bpp = texel_bytes(target);
+
+  // Slabs = whole block rows of one image: contiguous in the UASTC source and (rows of w texels) in the destination.
+  struct Slab { uint32_t image, w, rows_px; uint64_t so, dofs, n_blocks; };
+  std::vector<Slab> slabs;
+  const uint64_t SLAB_BLOCKS = 1u << 19;   // 8 MiB in, up to 32 MiB out
+  uint64_t max_in = 0, max_out = 0;
+  for (uint32_t i = 0; i < n_images; i++) {
+    const uint32_t w = images[i].width, h = images[i].height;
+    if (!w || !h) continue;
+    const uint32_t bx = (w + 3) / 4, by = (h + 3) / 4;
+    const uint32_t rows_per = (uint32_t)std::max<uint64_t>(1, SLAB_BLOCKS / bx);
+    for (uint32_t r0 = 0; r0 < by; r0 += rows_per) {
+      const uint32_t nr = std::min(rows_per, by - r0);
+      const uint32_t px_rows = std::min(h - r0 * 4, nr * 4);
+      slabs.push_back({i, w, px_rows, images[i].src_offset + (uint64_t)r0 * bx * 16, images[i].dst_offset + (uint64_t)r0 * 4 * w * bpp, (uint64_t)nr * bx});
+      max_in = std::max(max_in, (uint64_t)nr * bx * 16);
+      max_out = std::max(max_out, (uint64_t)px_rows * w * bpp);
+    }
+  }
+  if (slabs.empty()) return B200_OK;
+  const int RING = 3;
+  const int nring = (int)std::min<size_t>(RING, slabs.size());
+  uint8_t* d_in[RING] = {0}; uint8_t* d_out[RING] = {0};
+  cudaEvent_t ev_in[RING], ev_k[RING], ev_out[RING];
+  for (int i = 0; i < nring; i++) {
+    d_in[i] = (uint8_t*)t_stage.get(i, max_in); d_out[i] = (uint8_t*)t_stage.get(3 + i, max_out);
+    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
+  }
+  unsigned long long* d_bad = (unsigned long long*)t_stage.get(6, (size_t)n_images * sizeof(unsigned long long));
+  if (!d_bad) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flags");
+  for (int i = 0; i < nring; i++) {
+    cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
+  }
+  cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
+  cudaMemsetAsync(d_bad, 0xFF, (size_t)n_images * sizeof(unsigned long long), s_k);
+  cudaError_t err = cudaSuccess;
+  for (size_t k = 0; k < slabs.size() && err == cudaSuccess; k++) {
+    const Slab& sl = slabs[k];
+    const int b = (int)(k % nring);
+    if (k >= (size_t)nring) {
+      cudaStreamWaitEvent(s_in, ev_k[b], 0);
+      cudaStreamWaitEvent(s_k, ev_out[b], 0);
+    }
+    err = cudaMemcpyAsync(d_in[b], src_base + sl.so, sl.n_blocks * 16, cudaMemcpyHostToDevice, s_in);
+    if (err != cudaSuccess) break;
+    cudaEventRecord(ev_in[b], s_in);
+    cudaStreamWaitEvent(s_k, ev_in[b], 0);
+    launch_decode(target, d_in[b], d_out[b], sl.w, sl.rows_px, sl.w, s_k, (uint64_t*)(d_bad + sl.image));
+    cudaEventRecord(ev_k[b], s_k);
+    cudaStreamWaitEvent(s_out, ev_k[b], 0);
+    err = cudaMemcpyAsync(dst_base + sl.dofs, d_out[b], (size_t)sl.rows_px * sl.w * bpp, cudaMemcpyDeviceToHost, s_out);
+    cudaEventRecord(ev_out[b], s_out);
+  }
+  std::vector<unsigned long long> h_bad(n_images, ~0ull);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_k);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
+  if (err == cudaSuccess) err = cudaMemcpy(h_bad.data(), d_bad, (size_t)n_images * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  for (int i = 0; i < nring; i++) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); cudaEventDestroy(ev_out[i]); }
+  if (err != cudaSuccess) return fail(B200_E_CUDA, "decode pipeline", err);
+  for (uint32_t i = 0; i < n_images; i++)
+    if (h_bad[i] != ~0ull) {
+      if (bad_image) *bad_image = i;
+      return fail(B200_E_BAD_BLOCK, "invalid UASTC block");
+    }
   return B200_OK;
 }
 

@@ -5,6 +5,7 @@
 #include "../ktx_software_b200/csrc/uastc_to_bc7.cuh"
 #include "../ktx_software_b200/csrc/uastc_to_astc.cuh"
 #include "../ktx_software_b200/csrc/uastc_encode.cuh"
+#include "../ktx_software_b200/csrc/uastc_to_rgba.cuh"
 
 #define PORT_API extern "C" __attribute__((visibility("default")))
 
@@ -20,6 +21,25 @@ PORT_API int64_t port_transcode(const uint8_t* blocks, uint64_t n, uint32_t fmt,
   }
   return bad;
 }
+
+// UASTC -> 16 RGBA8 texels per block (64 B), the KTX_TTF_RGBA32 decode.  Returns -1 or the first invalid block.
+PORT_API int64_t port_decode_rgba(const uint8_t* blocks, uint64_t n, uint8_t* out_px) {
+  int64_t bad = -1;
+  for (uint64_t i = 0; i < n; i++) {
+    ub::Bits128 s;
+    memcpy(&s, blocks + i * 16, 16);
+    uint32_t px[16];
+    const bool ok = ub::decode_block_rgba(s, px);
+    memcpy(out_px + i * 64, px, 64);
+    if (!ok && bad < 0) bad = (int64_t)i;
+  }
+  return bad;
+}
+// texels -> 16-bit targets (kind 14 = RGB565, 15 = BGR565, 16 = RGBA4444)
+PORT_API void port_pack_texels16(const uint32_t* px, uint64_t n, uint32_t kind, uint16_t* out) {
+  for (uint64_t i = 0; i < n; i++) out[i] = (uint16_t)ub::pack_texel16(px[i], kind);
+}
+PORT_API uint32_t port_weight_unquant(uint32_t wb, uint32_t l) { return ub::weight_unquant(wb, l); }
 
 // n blocks of 16 RGBA texels (64 B each) -> n UASTC blocks.
 PORT_API void port_encode_blocks(const uint8_t* px, uint64_t n, uint32_t flags, uint8_t* out) {

@@ -11,6 +11,7 @@
 //   external/basis_universal/transcoder/basisu_transcoder.cpp:16172 transcode_uastc_to_bc7
 //   external/basis_universal/transcoder/basisu_transcoder.cpp:15649 transcode_uastc_to_astc
 //   external/basis_universal/transcoder/basisu_transcoder.cpp:15521 unpack_uastc (to pixels)
+//   external/basis_universal/transcoder/basisu_transcoder.cpp:10331 basisu_lowlevel_uastc_ldr_4x4_transcoder::transcode_image
 #include "basisu_enc.h"
 #include "basisu_uastc_enc.h"
 #include "basisu_bc7enc.h"
@@ -232,4 +233,17 @@ REF_API void ref_get_bc7_optimal(uint8_t* out /* mode6: 256*2*4 (err16,lo,hi) th
 		const basist::endpoint_err& e = basist::g_bc7_mode_5_optimal_endpoints[c];
 		p[0] = e.m_error & 255; p[1] = e.m_error >> 8; p[2] = e.m_lo; p[3] = e.m_hi; p += 4;
 	}
+}
+
+// One image through the low-level UASTC transcoder exactly as libktx calls it (lib/src/basis_transcode.cpp:776-798 ->
+// basisu_lowlevel_uastc_ldr_4x4_transcoder::transcode_image, transcoder/basisu_transcoder.cpp:10331): row pitch and row
+// count left at 0 (= the image's own width / height), so the uncompressed targets are clipped to w x h.
+// tf: transcoder_texture_format (6 BC7, 10 ASTC, 13 RGBA32, 14 RGB565, 15 BGR565, 16 RGBA4444).  Returns 0 on success.
+REF_API int ref_transcode_image(uint32_t tf, const uint8_t* blocks, uint32_t w, uint32_t h, uint8_t* out, uint32_t out_size_in_blocks_or_pixels)
+{
+	ref_init();
+	basist::basisu_lowlevel_uastc_ldr_4x4_transcoder t;
+	const uint32_t bx = (w + 3) / 4, by = (h + 3) / 4;
+	return t.transcode_image((basist::transcoder_texture_format)tf, out, out_size_in_blocks_or_pixels, blocks, bx * by * 16, bx, by, w, h, 0,
+		0, bx * by * 16, 0, true, false, 0, nullptr, 0, -1, -1) ? 0 : 1;
 }

@@ -67,6 +67,56 @@ def port_transcode(blocks, fmt):
     return out, bad
 
 
+def port_decode_rgba(blocks):
+    """blocks [n,16] -> (texels [n,64] as the KTX_TTF_RGBA32 decode lays a block out, first_bad or -1)"""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros((blocks.shape[0], 64), np.uint8)
+    f = port().port_decode_rgba
+    f.restype = ctypes.c_int64
+    f.argtypes = [_u8p, ctypes.c_uint64, _u8p]
+    return out, f(_p(blocks), blocks.shape[0], _p(out))
+
+
+TTF_BYTES_PER_PIXEL = {13: 4, 14: 2, 15: 2, 16: 2}
+
+
+def ref_transcode_image(blocks, w, h, tf):
+    """One w x h image (raster UASTC blocks) through the reference's low-level transcoder the way libktx calls it.
+    tf 6 / 10 -> blocks [n,16]; tf 13 -> uint8 [h,w,4]; tf 14/15/16 -> uint16 [h,w].  Returns (out, ok)."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    bx, by = (w + 3) // 4, (h + 3) // 4
+    assert blocks.shape[0] == bx * by
+    f = ref().ref_transcode_image
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_uint32, _u8p, ctypes.c_uint32, ctypes.c_uint32, _u8p, ctypes.c_uint32]
+    if tf in TTF_BYTES_PER_PIXEL:
+        out = np.zeros(w * h * TTF_BYTES_PER_PIXEL[tf], np.uint8)
+        rc = f(tf, _p(blocks), w, h, _p(out), w * h)
+        out = out.reshape(h, w, 4) if tf == 13 else out.view(np.uint16).reshape(h, w)
+    else:
+        out = np.zeros_like(blocks)
+        rc = f(tf, _p(blocks), w, h, _p(out), bx * by)
+    return out, rc == 0
+
+
+def texels_to_image(texels, w, h):
+    """[n,64] per-block texels (raster inside the block) -> uint8 [h,w,4], clipped like transcode_slice does."""
+    bx, by = (w + 3) // 4, (h + 3) // 4
+    t = np.asarray(texels, np.uint8).reshape(by, bx, 4, 4, 4).transpose(0, 2, 1, 3, 4).reshape(by * 4, bx * 4, 4)
+    return np.ascontiguousarray(t[:h, :w])
+
+
+def pack_image16(img, tf):
+    """uint8 [h,w,4] -> uint16 [h,w] with the product's texel packer (host build)."""
+    px = np.ascontiguousarray(img, np.uint8).reshape(-1, 4).view(np.uint32).reshape(-1)
+    out = np.zeros(px.shape[0], np.uint16)
+    f = port().port_pack_texels16
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
+    f(px.ctypes.data, px.shape[0], tf, out.ctypes.data)
+    return out.reshape(img.shape[0], img.shape[1])
+
+
 def ref_extract_blocks(img):
     """img uint8 [h,w,4] -> [nblocks,64] edge-clamped 4x4 gathers in raster block order"""
     img = np.ascontiguousarray(img, dtype=np.uint8)

@@ -210,3 +210,40 @@ def test_bc7_build_decode_equals_pack_then_parse():
     lib.port_check_bc7_build_decode.restype = ctypes.c_int64
     lib.port_check_bc7_build_decode.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
     assert lib.port_check_bc7_build_decode(blocks.ctypes.data, blocks.shape[0]) == 0
+
+
+# ---- uncompressed transcode targets (KTX_TTF_RGBA32 / RGB565 / BGR565 / RGBA4444), SURVEY 8(f).1
+def test_port_decode_rgba_golden_corpus():
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    out, bad = R.port_decode_rgba(g["uastc"])
+    assert bad == -1 and (out == g["rgba"]).all()
+    for k in range(0, len(g["invalid"]), 7):
+        assert R.port_decode_rgba(g["invalid"][k:k + 1])[1] == 0
+
+
+def test_weight_formula_matches_tables():
+    tabs = {1: [0, 64], 2: [0, 21, 43, 64], 3: [0, 9, 18, 27, 37, 46, 55, 64],
+            4: [0, 4, 8, 12, 17, 21, 25, 29, 35, 39, 43, 47, 52, 56, 60, 64],
+            5: [0, 2, 4, 6, 8, 10, 12, 14, 16, 18, 20, 22, 24, 26, 28, 30, 34, 36, 38, 40, 42, 44, 46, 48, 50, 52, 54, 56, 58, 60, 62, 64]}
+    f = R.port().port_weight_unquant
+    f.restype = ctypes.c_uint32
+    f.argtypes = [ctypes.c_uint32, ctypes.c_uint32]
+    for wb, t in tabs.items():   # g_bc7_weights1/2/3, g_astc_weights4/5 (XC:13957-13961)
+        assert [f(wb, l) for l in range(1 << wb)] == t
+
+
+@needs_ref
+@pytest.mark.parametrize("w,h", [(64, 64), (13, 7), (1, 1), (130, 5)])
+def test_port_decode_image_targets_vs_reference(w, h):
+    """The reference's own image-level path (transcode_image as libktx calls it) pins block order, clipping at ragged
+    edges and the 16-bit packers."""
+    img = R.img_mix(w, h, 11)
+    blocks = R.ref_encode_blocks(R.ref_extract_blocks(img), 2)
+    texels, bad = R.port_decode_rgba(blocks)
+    assert bad == -1
+    mine = R.texels_to_image(texels, w, h)
+    ref32, ok = R.ref_transcode_image(blocks, w, h, 13)
+    assert ok and (mine == ref32).all()
+    for tf in (14, 15, 16):
+        ref16, ok = R.ref_transcode_image(blocks, w, h, tf)
+        assert ok and (R.pack_image16(mine, tf) == ref16).all()
