@@ -74,6 +74,9 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
 #ifndef XT_TILE
 #define XT_TILE 4096
 #endif
+#ifndef XT_SMEM_TABLES
+#define XT_SMEM_TABLES true   // endpoint-unquantisation and p-bit tables are read from a per-CTA shared-memory copy
+#endif
 #ifndef XT_CTAS_PER_SM
 #define XT_CTAS_PER_SM 1
 #endif
@@ -111,7 +114,7 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 template <int TARGET>
 __device__ __forceinline__ bool transcode_dispatch(uint32_t mode, const ub::Bits128& s, ub::Bits128& d) {
   switch (mode) {
-#define XC_CASE(M) case M: return ub::transcode_known_mode<TARGET, M>(s, d);
+#define XC_CASE(M) case M: return ub::transcode_known_mode<TARGET, M, XT_SMEM_TABLES>(s, d);
     XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
     XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
 #undef XC_CASE
@@ -121,7 +124,7 @@ __device__ __forceinline__ bool transcode_dispatch(uint32_t mode, const ub::Bits
 
 __device__ __forceinline__ bool texel_form_dispatch(uint32_t mode, const ub::Bits128& s, ub::TexelForm& f) {
   switch (mode) {
-#define XC_CASE(M) case M: return ub::texel_form_t<M>(s, f);
+#define XC_CASE(M) case M: return ub::texel_form_t<M, XT_SMEM_TABLES>(s, f);
     XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
     XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
 #undef XC_CASE
@@ -224,6 +227,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)TILE, n_blocks - t * TILE); };
 
   if (tid < 32) s_hist[tid] = 0;
+  if (XT_SMEM_TABLES) ub::shared_tables_load(tid, XT_THREADS);
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
     mbar_init(&s_bar[1], 1);

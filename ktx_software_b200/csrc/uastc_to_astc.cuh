@@ -73,7 +73,7 @@ UB_FN Bits128 astc_pack_solid(uint32_t rgba) {  // void-extent block, UNORM16 = 
   return d;
 }
 
-template <int KM>
+template <int KM, bool TS = false>
 UB_FN bool transcode_block_to_astc_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
   if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
@@ -96,8 +96,8 @@ UB_FN bool transcode_block_to_astc_t(const Bits128& src, Bits128& dst) {
         int s0 = 0, s1 = 0;
 #pragma unroll
         for (uint32_t c = 0; c < 3; c++) {
-          s0 += (int)astc_unquant(er, u.ep[(base + 2 * c) % 18]);
-          s1 += (int)astc_unquant(er, u.ep[(base + 2 * c + 1) % 18]);
+          s0 += (int)astc_unquant_s<TS>(er, u.ep[(base + 2 * c) % 18]);
+          s1 += (int)astc_unquant_s<TS>(er, u.ep[(base + 2 * c + 1) % 18]);
         }
         if (s1 < s0) {
           inv |= 1u << s;
@@ -151,9 +151,9 @@ UB_FN bool transcode_block_to_astc(const Bits128& src, Bits128& dst) { return tr
 
 // Mode-dispatched transcode of one block whose mode the caller already decoded (blocks binned by mode, so a warp takes
 // one case).  TARGET 0 = BC7, 1 = ASTC.
-template <int TARGET, int KM>
+template <int TARGET, int KM, bool TS = false>
 UB_FN bool transcode_known_mode(const Bits128& src, Bits128& dst) {
-  return TARGET ? transcode_block_to_astc_t<KM>(src, dst) : transcode_block_to_bc7_t<KM>(src, dst);
+  return TARGET ? transcode_block_to_astc_t<KM, TS>(src, dst) : transcode_block_to_bc7_t<KM, TS>(src, dst);
 }
 
 }  // namespace ub

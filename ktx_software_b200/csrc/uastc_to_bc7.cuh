@@ -23,25 +23,29 @@ UB_FN uint32_t px_set(uint32_t v, uint32_t c, uint32_t x) { return (v & ~(255u <
 // u_lo/u_hi: 8-bit unquantised endpoints per channel; a channel the reference pins to 1.0f must be passed as 255.
 // wide = true: 7+1 bits (BC7 modes 3 and 6); false: 5+1 bits (BC7 mode 7).
 // One table entry per 8-bit channel value: fp32 error for p = 0 and p = 1, and both quantised codes.
-UB_FN void pbit_entry(const uint32_t* tab, uint32_t u, float& e0, float& e1, uint32_t& codes) {
+// which: 0 = 7+1 bits (pb8_q), 1 = 5+1 bits (pb6_q), 2 = 6 bits + shared p-bit (pb7s_q)
+template <bool TS = false>
+UB_FN void pbit_entry(uint32_t which, uint32_t u, float& e0, float& e1, uint32_t& codes) {
+  const uint32_t* tab = which == 0 ? UBT(pb8_q) : (which == 1 ? UBT(pb6_q) : UBT(pb7s_q));
 #ifdef __CUDA_ARCH__
-  const uint4 v = __ldg((const uint4*)tab + u);
+  const uint4 v = TS ? ub_shared_tables.pb[which][u] : __ldg((const uint4*)tab + u);
   e0 = __uint_as_float(v.x); e1 = __uint_as_float(v.y); codes = v.z;
 #else
   e0 = bits_to_float(tab[u * 4]); e1 = bits_to_float(tab[u * 4 + 1]); codes = tab[u * 4 + 2];
 #endif
 }
 
+template <bool TS = false>
 UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
-  const uint32_t* tab = wide ? UBT(pb8_q) : UBT(pb6_q);
+  const uint32_t tab = wide ? 0u : 1u;
   uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
   float e_lo0 = 0, e_lo1 = 0, e_hi0 = 0, e_hi1 = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++) {
     float a0, a1, b0, b1;
     uint32_t ca, cb;
-    pbit_entry(tab, px_c(u_lo, c), a0, a1, ca);
-    pbit_entry(tab, px_c(u_hi, c), b0, b1, cb);
+    pbit_entry<TS>(tab, px_c(u_lo, c), a0, a1, ca);
+    pbit_entry<TS>(tab, px_c(u_hi, c), b0, b1, cb);
     q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
     q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
     if (c < total_comps) { e_lo0 = f_add(e_lo0, a0); e_lo1 = f_add(e_lo1, a1); e_hi0 = f_add(e_hi0, b0); e_hi1 = f_add(e_hi1, b1); }
@@ -54,6 +58,7 @@ UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t
 }
 
 // determine_shared_pbits (XC:15532-15582), BC7 mode 1 only (3 comps, 6+1 bits, alpha = 1.0f == 255)
+template <bool TS = false>
 UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
   u_lo |= 0xFF000000u; u_hi |= 0xFF000000u;
   uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
@@ -62,8 +67,8 @@ UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t
   for (uint32_t c = 0; c < 4; c++) {
     float a0, a1, b0, b1;
     uint32_t ca, cb;
-    pbit_entry(UBT(pb7s_q), px_c(u_lo, c), a0, a1, ca);
-    pbit_entry(UBT(pb7s_q), px_c(u_hi, c), b0, b1, cb);
+    pbit_entry<TS>(2u, px_c(u_lo, c), a0, a1, ca);
+    pbit_entry<TS>(2u, px_c(u_hi, c), b0, b1, cb);
     q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
     q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
     if (c < 3) { err0 = f_add(err0, f_add(a0, b0)); err1 = f_add(err1, f_add(a1, b1)); }
@@ -118,21 +123,23 @@ UB_FN uint32_t bc7_3_to_2(uint32_t p, uint32_t k) {  // bc7_convert_partition_in
   return (k & 1u) ? 1u - r : r;
 }
 
-UB_FN uint32_t ep_unq(const UnpackedUastc& u, uint32_t er, uint32_t i) { return astc_unquant(er, u.ep[i]); }
+template <bool TS = false>
+UB_FN uint32_t ep_unq(const UnpackedUastc& u, uint32_t er, uint32_t i) { return astc_unquant_s<TS>(er, u.ep[i]); }
 
 // Gather the unquantised colour (RGB[A]) of one subset from the RR GG BB (AA) endpoint list.
+template <bool TS = false>
 UB_FN void subset_endpoints(const UnpackedUastc& u, uint32_t er, uint32_t base, uint32_t comps, uint32_t& lo, uint32_t& hi) {
   lo = 0; hi = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++)
     if (c < comps) {
-      lo |= ep_unq(u, er, base + 2 * c) << (8 * c);
-      hi |= ep_unq(u, er, base + 2 * c + 1) << (8 * c);
+      lo |= ep_unq<TS>(u, er, base + 2 * c) << (8 * c);
+      hi |= ep_unq<TS>(u, er, base + 2 * c + 1) << (8 * c);
     }
 }
 
 // Per-mode mapping (XC:15669-16161).
-template <int KM>
+template <int KM, bool TS = false>
 UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
   const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
   const uint32_t desc = (KM >= 0) ? mode_desc_c(KM) : u.desc;
@@ -181,15 +188,15 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
       o.mode = 6;
       uint32_t lo, hi;
       if (comps == 2) {
-        const uint32_t l0 = ep_unq(u, er, 0), l1 = ep_unq(u, er, 1);
-        lo = l0 * 0x010101u | (ep_unq(u, er, 2) << 24);
-        hi = l1 * 0x010101u | (ep_unq(u, er, 3) << 24);
+        const uint32_t l0 = ep_unq<TS>(u, er, 0), l1 = ep_unq<TS>(u, er, 1);
+        lo = l0 * 0x010101u | (ep_unq<TS>(u, er, 2) << 24);
+        hi = l1 * 0x010101u | (ep_unq<TS>(u, er, 3) << 24);
       } else {
-        subset_endpoints(u, er, 0, comps, lo, hi);
+        subset_endpoints<TS>(u, er, 0, comps, lo, hi);
         if (comps == 3) { lo |= 0xFF000000u; hi |= 0xFF000000u; }
       }
       uint32_t pb;
-      unique_pbits(comps == 2 ? 4 : comps, true, lo, hi, o.lo[0], o.hi[0], pb);
+      unique_pbits<TS>(comps == 2 ? 4 : comps, true, lo, hi, o.lo[0], o.hi[0], pb);
       if (comps == 3) { o.lo[0] = px_set(o.lo[0], 3, 127); o.hi[0] = px_set(o.hi[0], 3, 127); }
       o.pbits = pb;
       const int kind = (mode == 18) ? 1 : (mode == 14) ? 2 : ((mode == 5) || (mode == 12)) ? 3 : 0;
@@ -202,7 +209,7 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
 #pragma unroll
       for (uint32_t c = 0; c < 3; c++) { lo |= (uint32_t)u.ep[2 * c] << (8 * c); hi |= (uint32_t)u.ep[2 * c + 1] << (8 * c); }
       uint32_t qlo, qhi, pb;
-      unique_pbits(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
+      unique_pbits<TS>(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
       o.lo[0] = o.lo[1] = qlo & 0xFFFFFFu;
       o.hi[0] = o.hi[1] = qhi & 0xFFFFFFu;
       o.pbits = pb | (pb << 2);
@@ -223,7 +230,7 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
           hi |= ((uint32_t)u.ep[c * 2 + s * 6 + 1] * 17u) << (8 * c);
         }
         uint32_t qlo, qhi, pb;
-        shared_pbits(lo, hi, qlo, qhi, pb);
+        shared_pbits<TS>(lo, hi, qlo, qhi, pb);
         const uint32_t k = inv ? 1 - s : s;
         o.lo[k] = qlo & 0xFFFFFFu;
         o.hi[k] = qhi & 0xFFFFFFu;
@@ -242,8 +249,8 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
         uint32_t lo = 0, hi = 0;
 #pragma unroll
         for (uint32_t c = 0; c < 3; c++) {
-          lo |= ((ep_unq(u, er, c * 2 + s * 6) * 31u + 127u) / 255u) << (8 * c);
-          hi |= ((ep_unq(u, er, c * 2 + 1 + s * 6) * 31u + 127u) / 255u) << (8 * c);
+          lo |= ((ep_unq<TS>(u, er, c * 2 + s * 6) * 31u + 127u) / 255u) << (8 * c);
+          hi |= ((ep_unq<TS>(u, er, c * 2 + 1 + s * 6) * 31u + 127u) / 255u) << (8 * c);
         }
         const uint32_t k = UBT(astc_to_bc7_perm)[perm * 3 + s];
         // k is data dependent: write through selects so lo[]/hi[] stay in registers
@@ -261,9 +268,9 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
 #pragma unroll
       for (uint32_t s = 0; s < 2; s++) {
         uint32_t lo, hi;
-        subset_endpoints(u, er, s * 6, 3, lo, hi);
+        subset_endpoints<TS>(u, er, s * 6, 3, lo, hi);
         uint32_t qlo, qhi, pb;
-        unique_pbits(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
+        unique_pbits<TS>(3, true, lo | 0xFF000000u, hi | 0xFF000000u, qlo, qhi, pb);
         const uint32_t k = inv ? 1 - s : s;
         o.lo[k] = px_set(qlo, 3, 127);
         o.hi[k] = px_set(qhi, 3, 127);
@@ -276,16 +283,16 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
       o.mode = 5;
       o.rotation = (u.ccs + 1) & 3u;
       if (comps == 2) {
-        const uint32_t l = (ep_unq(u, er, 0) * 127u + 127u) / 255u, h = (ep_unq(u, er, 1) * 127u + 127u) / 255u;
-        o.lo[0] = l * 0x010101u | (ep_unq(u, er, 2) << 24);
-        o.hi[0] = h * 0x010101u | (ep_unq(u, er, 3) << 24);
+        const uint32_t l = (ep_unq<TS>(u, er, 0) * 127u + 127u) / 255u, h = (ep_unq<TS>(u, er, 1) * 127u + 127u) / 255u;
+        o.lo[0] = l * 0x010101u | (ep_unq<TS>(u, er, 2) << 24);
+        o.hi[0] = h * 0x010101u | (ep_unq<TS>(u, er, 3) << 24);
       } else {
 #pragma unroll
         for (uint32_t ac = 0; ac < 4; ac++) {
           uint32_t bc = ac;
           if (ac == u.ccs) bc = 3; else if (ac == 3) bc = u.ccs;
           uint32_t l = 255, h = 255;
-          if (ac < comps) { l = ep_unq(u, er, ac * 2); h = ep_unq(u, er, ac * 2 + 1); }
+          if (ac < comps) { l = ep_unq<TS>(u, er, ac * 2); h = ep_unq<TS>(u, er, ac * 2 + 1); }
           if (bc < 3) { l = (l * 127u + 127u) / 255u; h = (h * 127u + 127u) / 255u; }
           o.lo[0] |= l << (8 * bc);
           o.hi[0] |= h << (8 * bc);
@@ -308,8 +315,8 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
         for (uint32_t c = 0; c < 3; c++) {
           // ap is 0/1: select between the two subsets' endpoints without dynamic indexing
           const uint32_t l0 = u.ep[c * 2], l1 = u.ep[c * 2 + 6], h0 = u.ep[c * 2 + 1], h1 = u.ep[c * 2 + 7];
-          o.lo[bp] |= ((astc_unquant(er, ap ? l1 : l0) * 31u + 127u) / 255u) << (8 * c);
-          o.hi[bp] |= ((astc_unquant(er, ap ? h1 : h0) * 31u + 127u) / 255u) << (8 * c);
+          o.lo[bp] |= ((astc_unquant_s<TS>(er, ap ? l1 : l0) * 31u + 127u) / 255u) << (8 * c);
+          o.hi[bp] |= ((astc_unquant_s<TS>(er, ap ? h1 : h0) * 31u + 127u) / 255u) << (8 * c);
         }
       }
       o.sel = remap_selectors(u, desc, 1, 0, 2, 0);
@@ -324,13 +331,13 @@ UB_FN void uastc_to_bc7_build_t(const UnpackedUastc& u, Bc7Build& o) {
       for (uint32_t s = 0; s < 2; s++) {
         uint32_t lo, hi;
         if (comps == 2) {
-          lo = ep_unq(u, er, s * 4) * 0x010101u | (ep_unq(u, er, 2 + s * 4) << 24);
-          hi = ep_unq(u, er, 1 + s * 4) * 0x010101u | (ep_unq(u, er, 3 + s * 4) << 24);
+          lo = ep_unq<TS>(u, er, s * 4) * 0x010101u | (ep_unq<TS>(u, er, 2 + s * 4) << 24);
+          hi = ep_unq<TS>(u, er, 1 + s * 4) * 0x010101u | (ep_unq<TS>(u, er, 3 + s * 4) << 24);
         } else {
-          subset_endpoints(u, er, s * 8, 4, lo, hi);
+          subset_endpoints<TS>(u, er, s * 8, 4, lo, hi);
         }
         uint32_t qlo, qhi, pb;
-        unique_pbits(4, false, lo, hi, qlo, qhi, pb);
+        unique_pbits<TS>(4, false, lo, hi, qlo, qhi, pb);
         const uint32_t k = inv ? 1 - s : s;
         o.lo[k] = qlo; o.hi[k] = qhi;
         o.pbits |= pb << (2 * k);
@@ -440,12 +447,12 @@ UB_FN Bits128 bc7_pack(Bc7Build& o) {
 }
 
 // Full path for one block.  Returns false on an invalid UASTC block (output then zeroed).
-template <int KM>
+template <int KM, bool TS = false>
 UB_FN bool transcode_block_to_bc7_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
   if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
   Bc7Build o;
-  uastc_to_bc7_build_t<KM>(u, o);
+  uastc_to_bc7_build_t<KM, TS>(u, o);
   dst = bc7_pack(o);
   return true;
 }

@@ -54,7 +54,7 @@ UB_FN void texel_form_clear(TexelForm& f) {
 
 // KM >= 0: mode known by the caller (blocks binned by mode), every field offset folds to a constant.
 // Returns false for an invalid block (the form then decodes to zero texels).
-template <int KM>
+template <int KM, bool TS = false>
 UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
   texel_form_clear(f);
   UnpackedUastc u;
@@ -72,8 +72,8 @@ UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
   for (uint32_t s = 0; s < 3; s++) {
     if (s < subsets) {
       if (comps == 2) {   // luminance + alpha (XC:15400-15411)
-        const uint32_t ll = astc_unquant(er, u.ep[s * 4 + 0]), lh = astc_unquant(er, u.ep[s * 4 + 1]);
-        const uint32_t al = astc_unquant(er, u.ep[s * 4 + 2]), ah = astc_unquant(er, u.ep[s * 4 + 3]);
+        const uint32_t ll = astc_unquant_s<TS>(er, u.ep[s * 4 + 0]), lh = astc_unquant_s<TS>(er, u.ep[s * 4 + 1]);
+        const uint32_t al = astc_unquant_s<TS>(er, u.ep[s * 4 + 2]), ah = astc_unquant_s<TS>(er, u.ep[s * 4 + 3]);
         f.l_rb[s] = ll * 0x00010001u; f.h_rb[s] = lh * 0x00010001u;
         f.l_ga[s] = ll | (al << 16);  f.h_ga[s] = lh | (ah << 16);
       } else {
@@ -81,7 +81,7 @@ UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
 #pragma unroll
         for (uint32_t k = 0; k < 4; k++) {
           lo[k] = 255; hi[k] = 255;
-          if (k < comps) { lo[k] = astc_unquant(er, u.ep[s * comps * 2 + k * 2]); hi[k] = astc_unquant(er, u.ep[s * comps * 2 + k * 2 + 1]); }
+          if (k < comps) { lo[k] = astc_unquant_s<TS>(er, u.ep[s * comps * 2 + k * 2]); hi[k] = astc_unquant_s<TS>(er, u.ep[s * comps * 2 + k * 2 + 1]); }
         }
         f.l_rb[s] = lo[0] | (lo[2] << 16); f.h_rb[s] = hi[0] | (hi[2] << 16);
         f.l_ga[s] = lo[1] | (lo[3] << 16); f.h_ga[s] = hi[1] | (hi[3] << 16);

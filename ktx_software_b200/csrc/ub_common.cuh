@@ -182,7 +182,34 @@ UB_CONSTEXPR uint32_t bise_c(uint32_t range, uint32_t k) {  // k: 0 = bits, 1 = 
   return t[range * 3 + k];
 }
 
-UB_FN uint32_t astc_unquant(uint32_t range, uint32_t code) { return UBT(astc_unquant)[range * 256 + code] & 0xFF; }
+// Table space.  TS = true: the hot look-up tables of the streaming transcode kernels (ASTC endpoint unquantisation,
+// BC7 p-bit entries) are read from a per-CTA copy in shared memory (shared_tables_load) -- random 2- and 16-byte
+// look-ups cost a few shared-memory wavefronts there instead of one L1 tag look-up per distinct line.  TS = false
+// (the default, and the only choice on the host): the global tables.
+#ifdef __CUDACC__
+struct SharedTables {
+  uint16_t unq[21 * 256];   // ubt_astc_unquant
+  uint4 pb[3][256];         // ubt_pb8_q, ubt_pb6_q, ubt_pb7s_q
+};
+__shared__ SharedTables ub_shared_tables;   // only kernels that reference it get the 23 KB allocation
+__device__ __forceinline__ void shared_tables_load(uint32_t tid, uint32_t nthreads) {   // followed by a CTA barrier at the caller
+  for (uint32_t i = tid; i < 21 * 256 / 2; i += nthreads) ((uint32_t*)ub_shared_tables.unq)[i] = ((const uint32_t*)UBT(astc_unquant))[i];
+  for (uint32_t i = tid; i < 256; i += nthreads) {
+    ub_shared_tables.pb[0][i] = ((const uint4*)UBT(pb8_q))[i];
+    ub_shared_tables.pb[1][i] = ((const uint4*)UBT(pb6_q))[i];
+    ub_shared_tables.pb[2][i] = ((const uint4*)UBT(pb7s_q))[i];
+  }
+}
+#endif
+
+template <bool TS = false>
+UB_FN uint32_t astc_unquant_s(uint32_t range, uint32_t code) {
+#if defined(__CUDA_ARCH__)
+  if (TS) return ub_shared_tables.unq[range * 256 + code] & 0xFF;
+#endif
+  return UBT(astc_unquant)[range * 256 + code] & 0xFF;
+}
+UB_FN uint32_t astc_unquant(uint32_t range, uint32_t code) { return astc_unquant_s<false>(range, code); }
 
 const uint32_t UASTC_MODE_SOLID = 8;
 const uint32_t UASTC_TOTAL_MODES = 19;
