@@ -28,6 +28,18 @@ extern "C" {
 /* Transcode targets; numeric values are ktx_transcode_fmt_e's (lib/include/ktx.h:1696-1703). */
 #define B200_TTF_BC7_RGBA 6
 #define B200_TTF_ASTC_4x4_RGBA 10
+/* the hint-driven block targets (b200_uastc_transcode_ex): ktx_transcode_fmt_e values (lib/include/ktx.h:1654-1676);
+ * ETC1_RGB, BC1_RGB and BC4_R write 8 bytes per block, the others 16 */
+#define B200_TTF_ETC1_RGB 0
+#define B200_TTF_ETC2_RGBA 1
+#define B200_TTF_BC1_RGB 2
+#define B200_TTF_BC3_RGBA 3
+#define B200_TTF_BC4_R 4
+#define B200_TTF_BC5_RG 5
+/* decode flags the path honours: ktx_transcode_flag_bits_e KTX_TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS and KTX_TF_HIGH_QUALITY
+ * == basist cDecodeFlagsTranscodeAlphaDataToOpaqueFormats / cDecodeFlagsHighQuality (XC/basisu_transcoder.h:253,265) */
+#define B200_DECODE_FLAG_ALPHA_TO_OPAQUE 4u
+#define B200_DECODE_FLAG_HIGH_QUALITY 32u
 /* uncompressed targets (b200_uastc_decode*): KTX_TTF_RGBA32 / RGB565 / BGR565 / RGBA4444 (lib/include/ktx.h:1728-1737) */
 #define B200_TTF_RGBA32 13
 #define B200_TTF_RGB565 14
@@ -65,6 +77,19 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
  * Asynchronous with respect to the host when a stream is given. */
 int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, uint64_t n_blocks, void* stream,
                              uint64_t* d_first_bad);
+
+/* The same two entry points with what libktx forwards to transcode_image beside the target: transcodeFlags and
+ * (alphaContent != eNone) (lib/src/basis_transcode.cpp:788-789), and with the hint-driven targets ETC1_RGB, ETC2_RGBA,
+ * BC1_RGB, BC3_RGBA, BC4_R, BC5_RG: transcode_slice's cETC1 / cETC2_RGBA / cBC1 / cBC3 / cBC4 / cBC5 cases (XC:10141-10180) ->
+ * transcode_uastc_to_etc1 (:16444), _etc2_rgba (:17341), _bc1 (:18365), _bc3 (:18404), _bc4 (:18442), _bc5 (:18470).
+ * dst offsets and sizes count 8 bytes per block for ETC1_RGB, BC1_RGB and BC4_R.  BC4_R takes alpha instead of red when
+ * has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE are set (XC:10417); BC5_RG takes red and alpha (XC:10430).  Not accelerated
+ * (B200_E_INVALID_VALUE, the glue keeps the stock path): ETC1_RGB from the alpha channel.  Device pointers must be
+ * 16-byte aligned. */
+int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans,
+                            uint32_t n_spans, const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span);
+int b200_uastc_transcode_dev_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst,
+                                uint64_t n_blocks, void* stream, uint64_t* d_first_bad);
 
 /* ---- decode to texels (the uncompressed transcode targets) ------------------------------------------ */
 

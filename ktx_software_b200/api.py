@@ -8,11 +8,19 @@ LIB_PATH = os.environ.get("B200_UASTC_LIB") or os.path.join(HERE, "libuastc_b200
 TTF_BC7_RGBA = 6        # ktx_transcode_fmt_e KTX_TTF_BC7_RGBA (lib/include/ktx.h)
 TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
 TTF_RGBA32, TTF_RGB565, TTF_BGR565, TTF_RGBA4444 = 13, 14, 15, 16  # the uncompressed targets (ktx.h:1728-1737)
+# the hint-driven block targets (ktx.h:1654-1676); 8 bytes per block for ETC1_RGB, BC1_RGB, BC4_R, else 16
+TTF_ETC1_RGB, TTF_ETC2_RGBA, TTF_BC1_RGB, TTF_BC3_RGBA, TTF_BC4_R, TTF_BC5_RG = 0, 1, 2, 3, 4, 5
+TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS, TF_HIGH_QUALITY = 4, 32   # ktx_transcode_flag_bits_e
+
+
+def target_block_bytes(target):
+    return 8 if target in (TTF_ETC1_RGB, TTF_BC1_RGB, TTF_BC4_R) else 16
+
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
-                    "b200_uastc_decode", "b200_uastc_decode_image_dev"]
+                    "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -63,6 +71,10 @@ def lib():
                                            ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
         l.b200_uastc_transcode_dev.argtypes = [ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
                                                ctypes.c_void_p, ctypes.c_void_p]
+        l.b200_uastc_transcode_ex.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(XcodeSpan), ctypes.c_uint32,
+                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
+        l.b200_uastc_transcode_dev_ex.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                                                  ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_encode.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(UastcParams),
                                         ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
@@ -91,19 +103,25 @@ def launch_count():
     return int(lib().b200_uastc_launch_count())
 
 
-def transcode(src, target, spans=None, dst=None):
+def transcode(src, target, spans=None, dst=None, decode_flags=None, has_alpha=True):
     """Host-buffer transcode through the C ABI.  src: uint8 array holding UASTC blocks; spans: list of
     (src_offset, dst_offset, n_blocks) or None for one span over the whole buffer.  Returns the dst array.
-    Raises B200Error(code=-5) with .bad_span set when the input holds an invalid block."""
+    decode_flags = None: b200_uastc_transcode (BC7 / ASTC); otherwise b200_uastc_transcode_ex with libktx's transcodeFlags and
+    has_alpha (any block target).  Raises B200Error(code=-5) with .bad_span set when the input holds an invalid block."""
     src = np.ascontiguousarray(src, dtype=np.uint8).reshape(-1)
+    ob = target_block_bytes(target)
     if spans is None:
         spans = [(0, 0, src.size // 16)]
     if dst is None:
-        need = max([d + n * 16 for _, d, n in spans] + [0])
+        need = max([d + n * ob for _, d, n in spans] + [0])
         dst = np.zeros(need, np.uint8)
     arr = (XcodeSpan * max(1, len(spans)))(*[XcodeSpan(s, d, n) for s, d, n in spans])
     bad = ctypes.c_int64(-1)
-    rc = lib().b200_uastc_transcode(target, arr, len(spans), src.ctypes.data, dst.ctypes.data, ctypes.byref(bad))
+    if decode_flags is None and target in (TTF_BC7_RGBA, TTF_ASTC_4x4_RGBA):
+        rc = lib().b200_uastc_transcode(target, arr, len(spans), src.ctypes.data, dst.ctypes.data, ctypes.byref(bad))
+    else:
+        rc = lib().b200_uastc_transcode_ex(target, decode_flags or 0, 1 if has_alpha else 0, arr, len(spans), src.ctypes.data,
+                                           dst.ctypes.data, ctypes.byref(bad))
     if rc != 0:
         e = B200Error(rc, lib().b200_uastc_last_error().decode())
         e.bad_span = bad.value
@@ -114,6 +132,12 @@ def transcode(src, target, spans=None, dst=None):
 def transcode_dev(target, d_src, d_dst, n_blocks, stream=0, d_first_bad=0):
     """Device-pointer transcode (ints / torch data_ptr()); asynchronous when a stream handle is given."""
     _check(lib().b200_uastc_transcode_dev(target, d_src, d_dst, n_blocks, stream or None, d_first_bad or None))
+
+
+def transcode_dev_ex(target, decode_flags, has_alpha, d_src, d_dst, n_blocks, stream=0, d_first_bad=0):
+    """Device-pointer transcode with libktx's transcodeFlags / has_alpha; every block target (b200_uastc_transcode_dev_ex)."""
+    _check(lib().b200_uastc_transcode_dev_ex(target, decode_flags, 1 if has_alpha else 0, d_src, d_dst, n_blocks, stream or None,
+                                             d_first_bad or None))
 
 
 def decode(src, target, images):

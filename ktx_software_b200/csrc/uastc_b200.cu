@@ -18,6 +18,7 @@
 #include "uastc_encode.cuh"
 #include "uastc_rdo.cuh"
 #include "uastc_to_rgba.cuh"
+#include "uastc_to_bcn.cuh"
 
 namespace {
 
@@ -141,6 +142,9 @@ struct XtImage {
   uint32_t pitch_px;     // destination row pitch in texels
   uint32_t kind;         // 13 = RGBA32, 14 = RGB565, 15 = BGR565, 16 = RGBA4444 (ktx_transcode_fmt_e values)
   uint32_t vec_ok;       // destination base and pitch allow 16-byte (RGBA32) / 8-byte (16-bit targets) row stores
+  // TARGET 3 (hint-driven block targets) uses only: kind = 0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG
+  uint32_t hq;           // cDecodeFlagsHighQuality
+  uint32_t chan0, chan1; // channels of BC4 / BC5 (transcode_image, XC:10417-10438)
 };
 
 #ifndef XT_DECODE_STAGED
@@ -148,7 +152,9 @@ struct XtImage {
 #endif
 __host__ __device__ constexpr int xt_tile(int target) { return (target == 2 && XT_DECODE_STAGED) ? 2048 : XT_TILE; }   // staging holds 64 B per block
 __host__ __device__ constexpr int xt_data_tiles(int target) { return (target == 2 && XT_DECODE_STAGED) ? 6 : 2; }
-constexpr size_t xt_smem_bytes(int target) { return (size_t)xt_data_tiles(target) * xt_tile(target) * 16 + 2 * 8 + 32 * 4 + (size_t)xt_tile(target) * 2; }
+// TARGET 3 adds a TILE x 8-byte output tile for the 8-byte targets (their results cannot overwrite the 16-byte input slots)
+__host__ __device__ constexpr size_t xt_data_bytes(int target) { return (size_t)xt_data_tiles(target) * xt_tile(target) * 16 + (target == 3 ? (size_t)xt_tile(target) * 8 : 0); }
+constexpr size_t xt_smem_bytes(int target) { return xt_data_bytes(target) + 2 * 8 + 32 * 4 + (size_t)xt_tile(target) * 2; }
 
 __device__ __forceinline__ void store_block_texels(uint8_t* __restrict__ dst, const XtImage& im, uint64_t block_index, const uint32_t* px) {
   const uint32_t by = (uint32_t)(block_index / im.bx), bxi = (uint32_t)(block_index - (uint64_t)by * im.bx);
@@ -209,14 +215,28 @@ __device__ __forceinline__ void store_block_rows(uint8_t* __restrict__ dst, cons
   }
 }
 
-template <int TARGET>   // 0 = BC7, 1 = ASTC (dst = blocks, written through the shared-memory tile), 2 = texels (dst = image, im)
+__device__ __forceinline__ bool hinted_form_dispatch(uint32_t mode, const ub::Bits128& s, ub::HintedForm& h) {
+  switch (mode) {
+#define XC_CASE(M) case M: return ub::hinted_form_t<M, XT_SMEM_TABLES>(s, h);
+    XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
+    XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
+#undef XC_CASE
+    default: ub::texel_form_clear(h.f); h.mode = ub::UASTC_MODE_SOLID; h.hints = 0; h.bc1_sels = 0; h.solid = 0; return false;
+  }
+}
+
+// 0 = BC7, 1 = ASTC (dst = blocks, written through the shared-memory tile), 2 = texels (dst = image, im),
+// 3 = the hint-driven block targets (im.kind: ETC1 / ETC2 / BC1 / BC3 / BC4 / BC5; 8 or 16 bytes per block)
+template <int TARGET>
 __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
                                                                 unsigned long long* __restrict__ first_bad, const XtImage im) {
   constexpr int TILE = xt_tile(TARGET), PER_THREAD = TILE / XT_THREADS;
   extern __shared__ __align__(128) unsigned char xt_smem[];
   uint4 (*s_in)[TILE] = (uint4 (*)[TILE])xt_smem;  // [2][TILE]; a block's result overwrites its own input slot
   uint4* s_out = (uint4*)(xt_smem + 2 * (size_t)TILE * 16);   // TARGET 2 only: [4 texel rows][TILE] row pieces of 16 (or 8) bytes
-  uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_tiles(TARGET) * (size_t)TILE * 16);
+  uint2* s_out8 = (uint2*)(xt_smem + 2 * (size_t)TILE * 16);  // TARGET 3, 8-byte targets: the output tile
+  uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
+  const bool out8 = TARGET == 3 && ub::hinted_target_bytes(im.kind) == 8;
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
   uint16_t* s_order = (uint16_t*)(s_hist + 32);
 
@@ -243,11 +263,13 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   for (; tile < n_tiles; tile += gridDim.x) {
     const uint32_t cnt = tile_count(tile);
     const uint64_t next = tile + gridDim.x;
-    if (tid == 0 && next < n_tiles) {  // prefetch the next tile into the other buffer once its bulk store has drained it
-      bulk_wait_read0();
-      const uint32_t bytes = tile_count(next) * 16u;
-      mbar_expect_tx(&s_bar[buf ^ 1], bytes);
-      bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
+    if (tid == 0 && (TARGET == 3 || next < n_tiles)) {  // prefetch the next tile into the other buffer once its bulk store has drained it
+      bulk_wait_read0();   // (TARGET 3: also frees the single 8-byte output tile before this iteration refills it)
+      if (next < n_tiles) {
+        const uint32_t bytes = tile_count(next) * 16u;
+        mbar_expect_tx(&s_bar[buf ^ 1], bytes);
+        bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
+      }
     }
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
@@ -317,6 +339,13 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
               ((uint2*)s_out)[y * TILE + idx] = make_uint2(q[0] | (q[1] << 16), q[2] | (q[3] << 16));
             }
           }
+        } else if (TARGET == 3) {
+          ub::HintedForm h;
+          ok = hinted_form_dispatch(m, s, h);   // mode-specialised
+          if (ok) ub::hinted_target_from_form(h, im.kind, im.hq != 0, im.chan0, im.chan1, d);   // shared by all modes
+          else { d.lo = 0; d.hi = 0; }
+          if (out8) s_out8[idx] = make_uint2((uint32_t)d.lo, (uint32_t)(d.lo >> 32));
+          else s_in[buf][idx] = make_uint4((uint32_t)d.lo, (uint32_t)(d.lo >> 32), (uint32_t)d.hi, (uint32_t)(d.hi >> 32));
         } else {
           ok = transcode_dispatch<TARGET>(m, s, d);
           uint4 o;
@@ -328,7 +357,12 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     }
     if (TARGET != 2) fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
     __syncthreads();
-    if (TARGET != 2 && tid == 0) bulk_s2g(dst + tile * TILE, s_in[buf], cnt * 16u);
+    if (TARGET != 2 && !out8 && tid == 0) bulk_s2g(dst + tile * TILE, s_in[buf], cnt * 16u);
+    if (out8 && tid == 0) {   // bulk copies move multiples of 16 bytes: an odd last block leaves by a plain store
+      uint2* o8 = (uint2*)dst + tile * TILE;
+      if (cnt & ~1u) bulk_s2g(o8, s_out8, (cnt & ~1u) * 8u);
+      if (cnt & 1u) o8[cnt - 1] = s_out8[cnt - 1];
+    }
     if (TARGET == 2 && XT_DECODE_STAGED) {
       // consecutive threads take consecutive blocks of the image: their row pieces are consecutive in global memory
       for (uint32_t j = tid; j < cnt; j += XT_THREADS) store_block_rows((uint8_t*)dst, im, tile * TILE + j, s_out, TILE, j);
@@ -765,6 +799,30 @@ int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n
   return B200_OK;
 }
 
+// The hint-driven block targets (ETC1_RGB 0, ETC2_RGBA 1, BC1_RGB 2, BC3_RGBA 3, BC4_R 4, BC5_RG 5): 8 or 16 bytes per block.
+bool is_hinted_target(uint32_t t) { return t <= B200_TTF_BC5_RG; }
+uint32_t out_block_bytes(uint32_t t) { return (t == B200_TTF_ETC1_RGB || t == B200_TTF_BC1_RGB || t == B200_TTF_BC4_R) ? 8u : 16u; }
+bool is_block_target(uint32_t t) { return t == B200_TTF_BC7_RGBA || t == B200_TTF_ASTC_4x4_RGBA || is_hinted_target(t); }
+
+int launch_hinted(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst, uint64_t n, cudaStream_t st,
+                  uint64_t* d_first_bad) {
+  if (!n) return B200_OK;
+  const bool from_alpha = has_alpha && (decode_flags & B200_DECODE_FLAG_ALPHA_TO_OPAQUE);
+  if (target == B200_TTF_ETC1_RGB && from_alpha) return fail(B200_E_INVALID_VALUE, "ETC1 from the alpha channel is not accelerated");
+  if (((uintptr_t)d_dst & 15u) || ((uintptr_t)d_src & 15u)) return fail(B200_E_INVALID_VALUE, "device pointers must be 16-byte aligned");
+  XtImage im{};
+  im.kind = target;
+  im.hq = (decode_flags & B200_DECODE_FLAG_HIGH_QUALITY) ? 1u : 0u;
+  im.chan0 = (target == B200_TTF_BC4_R && from_alpha) ? 3u : 0u;   // transcode_image, XC:10417-10438
+  im.chan1 = 3u;
+  const uint64_t tiles = (n + xt_tile(3) - 1) / xt_tile(3);
+  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
+  k_transcode_tiled<3><<<grid, XT_THREADS, xt_smem_bytes(3), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im);
+  g_launches++;
+  CU(cudaGetLastError());
+  return B200_OK;
+}
+
 bool is_texel_target(uint32_t t) { return t == B200_TTF_RGBA32 || t == B200_TTF_RGB565 || t == B200_TTF_BGR565 || t == B200_TTF_RGBA4444; }
 uint32_t texel_bytes(uint32_t t) { return t == B200_TTF_RGBA32 ? 4u : 2u; }
 
@@ -971,6 +1029,7 @@ int b200_uastc_init(void) {
   CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(0)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(1)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(2)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
   g_ctx.ready = true;
   return B200_OK;
 }
@@ -985,14 +1044,20 @@ const char* b200_uastc_last_error(void) { return g_err.c_str(); }
 uint64_t b200_uastc_launch_count(void) { return g_launches.load(); }
 
 int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, uint64_t n_blocks, void* stream, uint64_t* d_first_bad) {
-  if (target != B200_TTF_BC7_RGBA && target != B200_TTF_ASTC_4x4_RGBA) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
+  return b200_uastc_transcode_dev_ex(target, 0, 1, d_src, d_dst, n_blocks, stream, d_first_bad);
+}
+
+int b200_uastc_transcode_dev_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst, uint64_t n_blocks,
+                                void* stream, uint64_t* d_first_bad) {
+  if (!is_block_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
   if (n_blocks && (!d_src || !d_dst)) return fail(B200_E_INVALID_VALUE, "null device pointer");
   int rc = b200_uastc_init();
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
   if (d_first_bad) { k_set_u64<<<1, 1, 0, st>>>((unsigned long long*)d_first_bad, ~0ull); g_launches++; }
-  rc = launch_transcode(target, d_src, d_dst, n_blocks, st, d_first_bad);
+  rc = is_hinted_target(target) ? launch_hinted(target, decode_flags, has_alpha, d_src, d_dst, n_blocks, st, d_first_bad)
+                                : launch_transcode(target, d_src, d_dst, n_blocks, st, d_first_bad);
   if (rc) return rc;
   if (!stream) CU(cudaStreamSynchronize(st));
   return B200_OK;
@@ -1098,8 +1163,17 @@ int b200_uastc_decode(uint32_t target, const b200_decode_image* images, uint32_t
 
 int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t n_spans, const uint8_t* src_base,
                          uint8_t* dst_base, int64_t* bad_span) {
+  return b200_uastc_transcode_ex(target, 0, 1, spans, n_spans, src_base, dst_base, bad_span);
+}
+
+int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans, uint32_t n_spans,
+                            const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span) {
   if (bad_span) *bad_span = -1;
-  if (target != B200_TTF_BC7_RGBA && target != B200_TTF_ASTC_4x4_RGBA) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
+  if (!is_block_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
+  const bool hinted = is_hinted_target(target);
+  if (hinted && target == B200_TTF_ETC1_RGB && has_alpha && (decode_flags & B200_DECODE_FLAG_ALPHA_TO_OPAQUE))
+    return fail(B200_E_INVALID_VALUE, "ETC1 from the alpha channel is not accelerated");
+  const uint64_t ob = out_block_bytes(target);
   if (n_spans && (!spans || !src_base || !dst_base)) return fail(B200_E_INVALID_VALUE, "null pointer");
   int rc = b200_uastc_init();
   if (rc) return rc;
@@ -1112,9 +1186,11 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
   std::vector<Run> runs;
   for (uint32_t i = 0; i < n_spans; i++) {
     if (!spans[i].n_blocks) continue;
-    if (!runs.empty()) {
+    // (the hint-driven targets keep one run -- one flag -- per span: a valid BC4 / BC5 block can be all zero, so the
+    // zero-block scan below that names the span inside a merged run does not apply to them)
+    if (!runs.empty() && !hinted) {
       Run& r = runs.back();
-      if (r.so + r.n * 16 == spans[i].src_offset && r.dofs + r.n * 16 == spans[i].dst_offset) { r.n += spans[i].n_blocks; continue; }
+      if (r.so + r.n * 16 == spans[i].src_offset && r.dofs + r.n * ob == spans[i].dst_offset) { r.n += spans[i].n_blocks; continue; }
     }
     runs.push_back({spans[i].src_offset, spans[i].dst_offset, spans[i].n_blocks, i});
   }
@@ -1133,7 +1209,7 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
   for (auto& r : runs) total_slabs += (r.n + SLAB - 1) / SLAB;
   nring = (int)std::min<uint64_t>(RING, total_slabs);
   for (int i = 0; i < nring; i++) {
-    d_in[i] = (uint8_t*)t_stage.get(i, maxn * 16); d_out[i] = (uint8_t*)t_stage.get(3 + i, maxn * 16);
+    d_in[i] = (uint8_t*)t_stage.get(i, maxn * 16); d_out[i] = (uint8_t*)t_stage.get(3 + i, maxn * ob);
     if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
     cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
@@ -1161,10 +1237,11 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
       cudaEventRecord(ev_in[b], s_in);
       cudaStreamWaitEvent(s_k, ev_in[b], 0);
       // block indices inside the kernel are slab-relative; the flag only has to say "this run holds a bad block"
-      launch_transcode(target, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
+      if (hinted) launch_hinted(target, decode_flags, has_alpha, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
+      else launch_transcode(target, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
       cudaEventRecord(ev_k[b], s_k);
       cudaStreamWaitEvent(s_out, ev_k[b], 0);
-      err = cudaMemcpyAsync(dst_base + r.dofs + o * 16, d_out[b], n * 16, cudaMemcpyDeviceToHost, s_out);
+      err = cudaMemcpyAsync(dst_base + r.dofs + o * ob, d_out[b], n * ob, cudaMemcpyDeviceToHost, s_out);
       cudaEventRecord(ev_out[b], s_out);
     }
   }
@@ -1187,7 +1264,7 @@ int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t
         // refine: spans of this run are contiguous; a bad block's output is all-zero, which no valid BC7/ASTC
         // block produced here can be (BC7 mode bit / ASTC block mode are never zero).
         uint64_t off = runs[ri].dofs;
-        for (uint32_t si = runs[ri].first_span; si < n_spans; si++) {
+        for (uint32_t si = runs[ri].first_span; si < n_spans && !hinted; si++) {
           if (spans[si].dst_offset != off) break;
           bool found = false;
           const uint64_t* q = (const uint64_t*)(dst_base + off);

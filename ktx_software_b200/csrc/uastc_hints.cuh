@@ -500,8 +500,9 @@ UB_FN Bc1Block bc1_solid(uint32_t fr, uint32_t fg, uint32_t fb) {
   return b;
 }
 
-// encode_bc1 with flags 0 (have_sels = false) or cEncodeBC1UseSelectors (sels given, linear 0..3), one LS pass
-UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels) {
+// encode_bc1 with flags 0 (have_sels = false) or cEncodeBC1UseSelectors (sels given, linear 0..3); ls_passes = 1, or 2 for
+// cEncodeBC1HighQuality (XC:17807)
+UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, uint32_t ls_passes = 1) {
   int avg_r = -1, avg_g = 0, avg_b = 0;
   uint32_t lr = 0, lg = 0, lb = 0, hr = 0, hg = 0, hb = 0;
   if (!have_sels) {
@@ -543,7 +544,7 @@ UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels) {
     hr = bc1_to5(ch(px[high_c], 0)); hg = bc1_to6(ch(px[high_c], 1)); hb = bc1_to5(ch(px[high_c], 2));
     bc1_find_sels(px, lr, lg, lb, hr, hg, hb, sels);
   }
-  {
+  for (uint32_t ls_pass = 0; ls_pass < ls_passes; ls_pass++) {
     float xl[3], xh[3];
     if (!bc1_least_squares(px, sels, xl, xh)) {
       if (avg_r < 0) {

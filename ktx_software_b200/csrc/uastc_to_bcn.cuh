@@ -1,0 +1,286 @@
+// uastc_to_bcn.cuh -- the hint-driven UASTC transcode targets: KTX_TTF_ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R,
+// BC5_RG.  Restates, from external/basis_universal/transcoder/basisu_transcoder.cpp:
+//   transcode_uastc_to_bc1 :18365 (hint0 :18237, hint1 :18335, encode_bc1 :17682, encode_bc1_solid_block :17634),
+//   transcode_uastc_to_bc3 :18404, transcode_uastc_to_bc4 :18442, transcode_uastc_to_bc5 :18470, encode_bc4 :17372,
+//   transcode_uastc_to_etc1 :16355 (apply_etc1_bias :16182, etc1_determine_selectors :16253),
+//   transcode_uastc_to_etc2_rgba :17341 (transcode_uastc_to_etc2_eac_a8 :17264).
+//
+// Form: like the uncompressed targets, a block is first brought into a mode-independent form by mode-specialised
+// code (TexelForm + the hint bits + plane-0 weights already translated to BC1 selectors); everything after that -- the
+// texel interpolation, BC4 / BC1 / ETC1 / EAC packing -- is one piece of code shared by all 19 modes.  A solid-colour
+// block needs no special case for the BCn targets: its 16 equal texels take the solid paths of encode_bc1 / encode_bc4,
+// which produce what encode_bc1_solid_block / write_bc4_solid_block do.
+#pragma once
+#include "uastc_to_rgba.cuh"
+#include "uastc_hints.cuh"
+
+namespace ub {
+
+struct HintedForm {
+  TexelForm f;
+  uint32_t mode;       // 0..18 (8 for an invalid block)
+  uint32_t hints;      // raw hint bits of the block (unpack_uastc :14947-15007)
+  uint32_t bc1_sels;   // plane-0 weights through s_uastc{1..5}_to_bc1 (XC:17365-17369), texel i at bits 2i
+  uint32_t solid;      // r | g<<8 | b<<16 | a<<24 (mode 8)
+};
+
+// Mode-specific part.  Returns false for an invalid block (the form then yields a zero output block).
+template <int KM, bool TS = false>
+UB_FN bool hinted_form_t(const Bits128& src, HintedForm& h) {
+  texel_form_clear(h.f);
+  h.mode = UASTC_MODE_SOLID; h.hints = 0; h.bc1_sels = 0; h.solid = 0;
+  UnpackedUastc u;
+  if (!unpack_uastc_t<KM>(src, u, true)) return false;
+  texel_form_from_unpacked<KM, TS>(u, h.f);
+  const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
+  h.mode = mode; h.hints = u.hints; h.solid = u.solid;
+  if (mode != UASTC_MODE_SOLID) {
+    const uint32_t d = (KM >= 0) ? mode_desc_c(KM) : u.desc;
+    const uint32_t wb = md_weight_bits(d), planes = 1 + md_dual_plane(d);
+    uint32_t s = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++) s |= uastc_to_bc1_sel(wb, bits_get(u.w, (i * planes) * wb, wb)) << (2 * i);
+    h.bc1_sels = s;
+  }
+  return true;
+}
+
+// The hint fields of a block (XC:14960-15007).  Solid blocks: diff, inten0, selector, r, g, b; others: the rest.
+struct HintFields {
+  uint32_t bc1_hint0, bc1_hint1, etc1_flip, etc1_diff, etc1_inten0, etc1_inten1, etc1_bias, etc2_hints;
+  uint32_t etc1_selector, etc1_r, etc1_g, etc1_b;
+  uint32_t has_bias, has_alpha;
+};
+
+UB_FN HintFields parse_hints(uint32_t mode, uint32_t hints) {
+  HintFields o;
+  o.bc1_hint0 = o.bc1_hint1 = o.etc1_flip = o.etc1_diff = o.etc1_inten0 = o.etc1_inten1 = o.etc1_bias = o.etc2_hints = 0;
+  o.etc1_selector = o.etc1_r = o.etc1_g = o.etc1_b = 0;
+  o.has_bias = 0; o.has_alpha = (mode >= 8 && mode <= 17) ? 1u : 0u;   // g_uastc_mode_has_alpha (XC:14060)
+  uint32_t p = 0;
+  if (mode == UASTC_MODE_SOLID) {
+    o.etc1_diff = hints & 1u;
+    o.etc1_inten0 = (hints >> 1) & 7u;
+    o.etc1_selector = (hints >> 4) & 3u;
+    o.etc1_r = (hints >> 6) & 31u; o.etc1_g = (hints >> 11) & 31u; o.etc1_b = (hints >> 16) & 31u;
+    return o;
+  }
+  o.has_bias = UBT(uastc_mode_has_etc1_bias)[mode];
+  if (UBT(uastc_mode_has_bc1_hint0)[mode]) { o.bc1_hint0 = (hints >> p) & 1u; p++; }
+  if (UBT(uastc_mode_has_bc1_hint1)[mode]) { o.bc1_hint1 = (hints >> p) & 1u; p++; }
+  o.etc1_flip = (hints >> p) & 1u; p++;
+  o.etc1_diff = (hints >> p) & 1u; p++;
+  o.etc1_inten0 = (hints >> p) & 7u; p += 3;
+  o.etc1_inten1 = (hints >> p) & 7u; p += 3;
+  if (o.has_bias) { o.etc1_bias = (hints >> p) & 31u; p += 5; }
+  if (o.has_alpha) o.etc2_hints = (hints >> p) & 255u;
+  return o;
+}
+
+// encode_bc4 (XC:17372-17490) of channel `chan` of 16 texels -> the 8-byte block, little-endian.
+UB_FN uint64_t bc4_encode(const uint32_t* px, uint32_t chan) {
+  uint32_t mn = 255u, mx = 0u;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) { const uint32_t v = ch(px[i], chan); mn = minu(mn, v); mx = maxu(mx, v); }
+  uint64_t out = (uint64_t)mx | ((uint64_t)mn << 8);
+  if (mx == mn) return out;
+  const int delta = (int)(mx - mn), bias = 4 - (int)mn * 14;
+  uint64_t bits = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    const int v = (int)ch(px[i], chan) * 14 + bias;
+    const uint32_t k = (uint32_t)(v >= delta * 13) + (v >= delta * 11) + (v >= delta * 9) + (v >= delta * 7) + (v >= delta * 5) + (v >= delta * 3) + (v >= delta);
+    bits |= (uint64_t)((0x02345671u >> (4 * k)) & 7u) << (3 * i);   // s_tran = {1,7,6,5,4,3,2,0}
+  }
+  return out | (bits << 16);
+}
+
+UB_FN uint64_t bc1_bytes(const Bc1Block& b) { return (uint64_t)(b.lo16 & 0xFFFFu) | ((uint64_t)(b.hi16 & 0xFFFFu) << 16) | ((uint64_t)b.sels << 32); }
+
+// transcode_uastc_to_bc1_hint0 (XC:18237): endpoints of subset 0 as the BC1 colours, weights as selectors.
+UB_FN Bc1Block bc1_from_hint0(const HintedForm& h) {
+  const uint32_t l[3] = {h.f.l_rb[0] & 255u, h.f.l_ga[0] & 255u, (h.f.l_rb[0] >> 16) & 255u};
+  const uint32_t e[3] = {h.f.h_rb[0] & 255u, h.f.h_ga[0] & 255u, (h.f.h_rb[0] >> 16) & 255u};
+  Bc1Block b;
+  b.lo16 = ((l[0] * 31 + 127) / 255) << 11 | ((l[1] * 63 + 127) / 255) << 5 | ((l[2] * 31 + 127) / 255);
+  b.hi16 = ((e[0] * 31 + 127) / 255) << 11 | ((e[1] * 63 + 127) / 255) << 5 | ((e[2] * 31 + 127) / 255);
+  if (b.lo16 == b.hi16) {
+    uint32_t mask = 0;
+    if (b.hi16 > 0) b.hi16--; else { b.hi16 = 0; b.lo16 = 1; mask = 0x55; }
+    b.sels = mask * 0x01010101u;
+  } else {
+    b.sels = h.bc1_sels;
+    if (b.lo16 < b.hi16) { const uint32_t t = b.lo16; b.lo16 = b.hi16; b.hi16 = t; b.sels ^= 0x55555555u; }
+  }
+  return b;
+}
+
+// The BC1 colour block of transcode_uastc_to_bc1 / _bc3 (XC:18377-18392, :18428-18438)
+UB_FN uint64_t bc1_from_form(const HintedForm& h, const HintFields& hf, const uint32_t* px, bool high_quality) {
+  if (!high_quality && hf.bc1_hint0) return bc1_bytes(bc1_from_hint0(h));
+  uint8_t sels[16];
+  const uint32_t passes = high_quality ? 2u : 1u;
+  if (hf.bc1_hint1) {
+    // transcode_uastc_to_bc1_hint1: BC1 selector order -> linear order {0,3,1,2} (s_sel_tran, XC:17697)
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++) sels[i] = (uint8_t)((0x9Cu >> (2 * ((h.bc1_sels >> (2 * i)) & 3u))) & 3u);
+    return bc1_bytes(encode_bc1(px, true, sels, passes));
+  }
+  return bc1_bytes(encode_bc1(px, false, sels, passes));
+}
+
+// ---- ETC1 (XC:16355-16441)
+// the four colours of a sub-block: decoder_etc_block::get_block_colors (XC:784), luma-weighted as etc1_determine_selectors does
+UB_FN void etc1_subblock_luma(const uint32_t* base8, uint32_t inten, uint32_t* y) {
+#pragma unroll
+  for (uint32_t k = 0; k < 4; k++) {
+    const int m = UBT(etc1_inten)[inten * 4 + k];
+    y[k] = (uint32_t)clamp255((int)base8[0] + m) * 54u + (uint32_t)clamp255((int)base8[1] + m) * 183u + (uint32_t)clamp255((int)base8[2] + m) * 19u;
+  }
+}
+
+UB_FN uint64_t etc1_from_form(const HintedForm& h, const HintFields& hf, const uint32_t* px) {
+  uint32_t by[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (h.mode == UASTC_MODE_SOLID) {
+    by[3] = ((hf.etc1_diff << 1) | (hf.etc1_inten0 << 5) | (hf.etc1_inten0 << 2)) & 255u;
+    if (hf.etc1_diff) { by[0] = (hf.etc1_r << 3) & 255u; by[1] = (hf.etc1_g << 3) & 255u; by[2] = (hf.etc1_b << 3) & 255u; }
+    else { by[0] = (hf.etc1_r | (hf.etc1_r << 4)) & 255u; by[1] = (hf.etc1_g | (hf.etc1_g << 4)) & 255u; by[2] = (hf.etc1_b | (hf.etc1_b << 4)) & 255u; }
+    // s_etc1_solid_selectors (XC:16313)
+    const uint32_t s = hf.etc1_selector;
+    by[4] = by[5] = (s < 2) ? 255u : 0u;
+    by[6] = by[7] = (s == 0 || s == 3) ? 255u : 0u;
+  } else {
+    const uint32_t flip = hf.etc1_flip, diff = hf.etc1_diff;
+    by[3] = (flip | (diff << 1) | (hf.etc1_inten0 << 5) | (hf.etc1_inten1 << 2)) & 255u;
+    const uint32_t limit = diff ? 31u : 15u;
+    int bc[2][3];
+#pragma unroll
+    for (uint32_t subset = 0; subset < 2; subset++) {
+      uint32_t avg[3] = {0, 0, 0};
+#pragma unroll
+      for (uint32_t j = 0; j < 8; j++) {
+        const uint32_t p = px[etc1_texel(flip, subset, j)];
+        avg[0] += ch(p, 0); avg[1] += ch(p, 1); avg[2] += ch(p, 2);
+      }
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) {
+        int v = (int)((avg[c] * limit + 1020u) / (8u * 255u));
+        if (hf.has_bias) v = etc1_bias_comp(v, hf.etc1_bias, (int)limit, subset, c);
+        bc[subset][c] = v;
+      }
+    }
+    uint32_t base8[2][3];
+    if (diff) {
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) {
+        int d = clampi(bc[1][c] - bc[0][c], -4, 3);
+        // what the decoder sees for sub-block 1: base + delta, clamped to 5 bits (unpack_color5, XC:907)
+        const int c1 = clampi(bc[0][c] + d, 0, 31);
+        base8[0][c] = (uint32_t)((bc[0][c] << 3) | (bc[0][c] >> 2));
+        base8[1][c] = (uint32_t)((c1 << 3) | (c1 >> 2));
+        if (d < 0) d += 8;
+        by[c] = (uint32_t)((bc[0][c] << 3) | d) & 255u;
+      }
+    } else {
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) {
+        by[c] = (uint32_t)(bc[1][c] | (bc[0][c] << 4)) & 255u;
+        base8[0][c] = (uint32_t)((bc[0][c] << 4) | bc[0][c]);
+        base8[1][c] = (uint32_t)((bc[1][c] << 4) | bc[1][c]);
+      }
+    }
+    // etc1_determine_selectors (XC:16253): ETC1 bit index of texel (x, y) = x*4 + y
+    uint32_t lmask = 0, hmask = 0;
+#pragma unroll
+    for (uint32_t subblock = 0; subblock < 2; subblock++) {
+      uint32_t y4[4];
+      etc1_subblock_luma(base8[subblock], subblock ? hf.etc1_inten1 : hf.etc1_inten0, y4);
+      const uint32_t y01 = y4[0] + y4[1], y12 = y4[1] + y4[2], y23 = y4[2] + y4[3];
+#pragma unroll
+      for (uint32_t j = 0; j < 8; j++) {
+        const uint32_t ti = etc1_texel(flip, subblock, j), x = ti & 3u, yy = ti >> 2;
+        const uint32_t p = px[ti];
+        const uint32_t l = ch(p, 0) * 108u + ch(p, 1) * 366u + ch(p, 2) * 38u;
+        const uint32_t t = (0xE1u >> (2 * ((l < y01) + (l < y12) + (l < y23)))) & 3u;   // s_tran = {1,0,2,3}
+        const uint32_t ofs = x * 4 + yy;
+        lmask |= (t & 1u) << ofs;
+        hmask |= (t >> 1) << ofs;
+      }
+    }
+    by[7] = lmask & 255u; by[6] = (lmask >> 8) & 255u; by[5] = hmask & 255u; by[4] = (hmask >> 8) & 255u;
+  }
+  uint64_t o = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 8; i++) o |= (uint64_t)by[i] << (8 * i);
+  return o;
+}
+
+// ---- ETC2 EAC A8 (XC:17264-17339)
+UB_FN uint64_t eac_a8_bytes(uint32_t base, uint32_t table, uint32_t mul, uint64_t sels48) {
+  uint64_t o = (uint64_t)(base & 255u) | ((uint64_t)((table & 15u) | ((mul & 15u) << 4)) << 8);
+#pragma unroll
+  for (uint32_t k = 0; k < 6; k++) o |= ((sels48 >> (40 - 8 * k)) & 255ull) << (8 * (2 + k));   // set_selector_bits: big-endian
+  return o;
+}
+
+UB_FN uint64_t eac_a8_from_form(const HintedForm& h, const HintFields& hf, const uint32_t* px) {
+  const uint64_t SEL4 = 0x924924924924ull;   // g_etc2_eac_a8_sel4 (XC:4781)
+  if (!hf.has_alpha || h.mode == UASTC_MODE_SOLID) return eac_a8_bytes(h.mode == UASTC_MODE_SOLID ? (h.solid >> 24) : 255u, 13, 1, SEL4);
+  uint32_t mn = 255u, mx = 0u;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) { const uint32_t a = px[i] >> 24; mn = minu(mn, a); mx = maxu(mx, a); }
+  if (mn == mx) return eac_a8_bytes(mn, 13, 1, SEL4);
+  const uint32_t table = hf.etc2_hints & 15u;
+  const int mul = (int)(hf.etc2_hints >> 4);
+  const int8_t* T = UBT(etc2_eac) + table * 8;
+  const float range = (float)((int)T[7] - (int)T[3]);
+  const float t = f_div((float)(0 - (int)T[3]), range);
+  const int center = (int)roundf(f_add((float)mn, f_mul(f_sub((float)mx, (float)mn), t)));   // basisu::lerp = a + (b - a) * t
+  int vals[8];
+#pragma unroll
+  for (uint32_t j = 0; j < 8; j++) vals[j] = clamp255(center + (int)T[j] * mul);
+  uint64_t sels = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    const int a = (int)(px[(i & 3u) * 4 + (i >> 2)] >> 24);   // block_pixels[i & 3][i >> 2]: column-major
+    uint32_t best = 0xFFFFFFFFu;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+      int e = vals[j] - a;
+      if (e < 0) e = -e;
+      best = minu(best, ((uint32_t)e << 3) | j);
+    }
+    sels |= (uint64_t)(best & 7u) << (45 - i * 3);
+  }
+  return eac_a8_bytes((uint32_t)center, table, (uint32_t)mul, sels);
+}
+
+// Output bytes per block of a hinted target (0 = not one)
+UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind == 2 || kind == 4) ? 8u : (kind == 1 || kind == 3 || kind == 5) ? 16u : 0u; }
+
+// The shared part.  kind = ktx_transcode_fmt_e (0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG);
+// chan0 / chan1: the channels BC4 / BC5 take (transcode_image, XC:10417-10438).  8-byte targets fill d.lo only.
+UB_FN void hinted_target_from_form(const HintedForm& h, uint32_t kind, bool high_quality, uint32_t chan0, uint32_t chan1, Bits128& d) {
+  uint32_t px[16];
+  texels_from_form(h.f, px);
+  const HintFields hf = parse_hints(h.mode, h.hints);
+  d.lo = 0; d.hi = 0;
+  switch (kind) {
+    case 0: d.lo = etc1_from_form(h, hf, px); break;
+    case 1: d.lo = eac_a8_from_form(h, hf, px); d.hi = etc1_from_form(h, hf, px); break;
+    case 2: d.lo = bc1_from_form(h, hf, px, high_quality); break;
+    case 3: d.lo = bc4_encode(px, 3); d.hi = bc1_from_form(h, hf, px, high_quality); break;
+    case 4: d.lo = bc4_encode(px, chan0); break;
+    default: d.lo = bc4_encode(px, chan0); d.hi = bc4_encode(px, chan1); break;
+  }
+}
+
+// One block, mode not known in advance (host checker, simple kernels).  Returns false for an invalid block (d zeroed).
+UB_FN bool transcode_block_hinted(const Bits128& src, uint32_t kind, bool high_quality, uint32_t chan0, uint32_t chan1, Bits128& d) {
+  HintedForm h;
+  if (!hinted_form_t<-1>(src, h)) { d.lo = 0; d.hi = 0; return false; }
+  hinted_target_from_form(h, kind, high_quality, chan0, chan1, d);
+  return true;
+}
+
+}  // namespace ub

@@ -55,15 +55,12 @@ UB_FN void texel_form_clear(TexelForm& f) {
 // KM >= 0: mode known by the caller (blocks binned by mode), every field offset folds to a constant.
 // Returns false for an invalid block (the form then decodes to zero texels).
 template <int KM, bool TS = false>
-UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
-  texel_form_clear(f);
-  UnpackedUastc u;
-  if (!unpack_uastc_t<KM>(src, u, false)) return false;
+UB_FN void texel_form_from_unpacked(const UnpackedUastc& u, TexelForm& f) {   // f cleared by the caller
   const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
   if (mode == UASTC_MODE_SOLID) {   // both endpoints = the colour, weights 0: interpolates to the colour itself
     f.l_rb[0] = f.h_rb[0] = (u.solid & 0xFFu) | (((u.solid >> 16) & 0xFFu) << 16);
     f.l_ga[0] = f.h_ga[0] = ((u.solid >> 8) & 0xFFu) | ((u.solid >> 24) << 16);
-    return true;
+    return;
   }
   const uint32_t d = (KM >= 0) ? mode_desc_c(KM) : u.desc;
   const uint32_t subsets = md_subsets(d), comps = md_comps(d), er = md_endpoint_range(d), wb = md_weight_bits(d);
@@ -95,6 +92,14 @@ UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
     if (planes == 2) f.w1[i >> 2] |= weight_unquant(wb, bits_get(u.w, (i * planes + 1) * wb, wb)) << (8 * (i & 3u));
   }
   if (planes == 2) f.sel = 255u << (8 * u.ccs);   // channel ccs takes the texel's second weight (XC:15490-15507)
+}
+
+template <int KM, bool TS = false>
+UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
+  texel_form_clear(f);
+  UnpackedUastc u;
+  if (!unpack_uastc_t<KM>(src, u, false)) return false;
+  texel_form_from_unpacked<KM, TS>(u, f);
   return true;
 }
 

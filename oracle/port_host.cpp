@@ -6,6 +6,7 @@
 #include "../ktx_software_b200/csrc/uastc_to_astc.cuh"
 #include "../ktx_software_b200/csrc/uastc_encode.cuh"
 #include "../ktx_software_b200/csrc/uastc_to_rgba.cuh"
+#include "../ktx_software_b200/csrc/uastc_to_bcn.cuh"
 
 #define PORT_API extern "C" __attribute__((visibility("default")))
 
@@ -35,6 +36,36 @@ PORT_API int64_t port_decode_rgba(const uint8_t* blocks, uint64_t n, uint8_t* ou
   }
   return bad;
 }
+// The hint-driven targets (kind = ktx_transcode_fmt_e: 0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG);
+// out holds 8 or 16 bytes per block.  Returns -1 or the index of the first invalid block.
+PORT_API int64_t port_transcode_hinted(const uint8_t* blocks, uint64_t n, uint32_t kind, uint32_t high_quality, uint32_t chan0,
+                                       uint32_t chan1, uint8_t* out) {
+  int64_t bad = -1;
+  const uint32_t ob = ub::hinted_target_bytes(kind);
+  for (uint64_t i = 0; i < n; i++) {
+    ub::Bits128 s, d;
+    memcpy(&s, blocks + i * 16, 16);
+    const bool ok = ub::transcode_block_hinted(s, kind, high_quality != 0, chan0, chan1, d);
+    memcpy(out + i * ob, &d, ob);
+    if (!ok && bad < 0) bad = (int64_t)i;
+  }
+  return bad;
+}
+
+// white-box tap: the ETC2 EAC hint byte of every block (table | multiplier << 4), 0xFFFF where the mode carries none or
+// the block is invalid.  The reference asserts multiplier >= 1, so tests drop random-payload blocks with multiplier 0.
+PORT_API void port_etc2_hints(const uint8_t* blocks, uint64_t n, uint16_t* out) {
+  for (uint64_t i = 0; i < n; i++) {
+    ub::Bits128 s;
+    memcpy(&s, blocks + i * 16, 16);
+    ub::HintedForm h;
+    out[i] = 0xFFFF;
+    if (!ub::hinted_form_t<-1>(s, h) || h.mode == ub::UASTC_MODE_SOLID) continue;
+    const ub::HintFields hf = ub::parse_hints(h.mode, h.hints);
+    if (hf.has_alpha) out[i] = (uint16_t)hf.etc2_hints;
+  }
+}
+
 // texels -> 16-bit targets (kind 14 = RGB565, 15 = BGR565, 16 = RGBA4444)
 PORT_API void port_pack_texels16(const uint32_t* px, uint64_t n, uint32_t kind, uint16_t* out) {
   for (uint64_t i = 0; i < n; i++) out[i] = (uint16_t)ub::pack_texel16(px[i], kind);

@@ -247,3 +247,16 @@ REF_API int ref_transcode_image(uint32_t tf, const uint8_t* blocks, uint32_t w, 
 	return t.transcode_image((basist::transcoder_texture_format)tf, out, out_size_in_blocks_or_pixels, blocks, bx * by * 16, bx, by, w, h, 0,
 		0, bx * by * 16, 0, true, false, 0, nullptr, 0, -1, -1) ? 0 : 1;
 }
+
+// The same with the caller's decode flags (cDecodeFlagsTranscodeAlphaDataToOpaqueFormats = 4, cDecodeFlagsHighQuality = 32)
+// and has_alpha, as libktx forwards transcodeFlags and (alphaContent != eNone) (lib/src/basis_transcode.cpp:788-789).
+// tf additionally: 0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG.
+REF_API int ref_transcode_image_flags(uint32_t tf, const uint8_t* blocks, uint32_t w, uint32_t h, uint8_t* out, uint32_t out_size_in_blocks_or_pixels,
+	uint32_t decode_flags, uint32_t has_alpha)
+{
+	ref_init();
+	basist::basisu_lowlevel_uastc_ldr_4x4_transcoder t;
+	const uint32_t bx = (w + 3) / 4, by = (h + 3) / 4;
+	return t.transcode_image((basist::transcoder_texture_format)tf, out, out_size_in_blocks_or_pixels, blocks, bx * by * 16, bx, by, w, h, 0,
+		0, bx * by * 16, decode_flags, has_alpha != 0, false, 0, nullptr, 0, -1, -1) ? 0 : 1;
+}

@@ -10,6 +10,9 @@ oracle/_ref exist; the GPU box only reads the committed files).
   transcode_golden.npz    ~30k UASTC blocks (reference-encoded adversarial + image blocks at levels 0-3, random
                           payloads behind every mode prefix, invalid blocks) with the reference's BC7 / ASTC output.
   encode_golden.npz       source 4x4 blocks + the reference encoder's output at levels 0-3 (small set).
+  hinted_golden.npz       (`make_golden.py hinted`) reference output of the hint-driven targets ETC1_RGB, ETC2_RGBA, BC1_RGB,
+                          BC3_RGBA, BC4_R, BC5_RG (+ high-quality BC1 / BC3, BC4 from alpha) for every second block of
+                          transcode_golden.npz that the reference's ETC2 path accepts (`index` = positions in its `uastc`).
 """
 import json, os, struct, sys
 import numpy as np
@@ -83,5 +86,24 @@ def main():
     print("encode corpus:", pxs.shape)
 
 
+def make_hinted():
+    g = np.load(os.path.join(HERE, "transcode_golden.npz"))
+    u = g["uastc"]
+    index = np.nonzero(R.etc2_transcodable(u))[0][::2].astype(np.uint32)
+    b = u[index]
+    out = {"index": index}
+    for name, tf in [("etc1", 0), ("etc2", 1), ("bc1", 2), ("bc3", 3), ("bc4", 4), ("bc5", 5)]:
+        out[name], ok = R.ref_transcode_hinted(b, tf)
+        assert ok
+    out["bc1_hq"] = R.ref_transcode_hinted(b, 2, 32)[0]
+    out["bc3_hq"] = R.ref_transcode_hinted(b, 3, 32)[0]
+    out["bc4_alpha"] = R.ref_transcode_hinted(b, 4, 4, True)[0]
+    np.savez_compressed(os.path.join(HERE, "hinted_golden.npz"), **out)
+    print("hinted corpus:", b.shape, "modes:", np.bincount(R.block_modes(b), minlength=19))
+
+
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["hinted"]:
+        make_hinted()
+    else:
+        main()

@@ -99,6 +99,46 @@ def ref_transcode_image(blocks, w, h, tf):
     return out, rc == 0
 
 
+HINTED_TARGET_BYTES = {0: 8, 1: 16, 2: 8, 3: 16, 4: 8, 5: 16}   # ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R, BC5_RG
+
+
+def ref_transcode_hinted(blocks, tf, decode_flags=0, has_alpha=True):
+    """n blocks as one (4n x 4) image through the reference's transcode_image with the caller's decode flags
+    (4 = alpha data to opaque formats, 32 = high quality).  tf in HINTED_TARGET_BYTES -> (out [n, 8|16], ok)."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    n = blocks.shape[0]
+    f = ref().ref_transcode_image_flags
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_uint32, _u8p, ctypes.c_uint32, ctypes.c_uint32, _u8p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]
+    out = np.zeros((n, HINTED_TARGET_BYTES[tf]), np.uint8)
+    rc = f(tf, _p(blocks), n * 4, 4, _p(out), n, decode_flags, 1 if has_alpha else 0)
+    return out, rc == 0
+
+
+def port_transcode_hinted(blocks, tf, decode_flags=0, has_alpha=True):
+    """The product headers' host build; channel selection as transcode_image does it (XC:10417-10438)."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    f = port().port_transcode_hinted
+    f.restype = ctypes.c_int64
+    f.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, _u8p]
+    out = np.zeros((blocks.shape[0], HINTED_TARGET_BYTES[tf]), np.uint8)
+    chan0 = 3 if (tf == 4 and has_alpha and (decode_flags & 4)) else 0
+    bad = f(_p(blocks), blocks.shape[0], tf, 1 if (decode_flags & 32) else 0, chan0, 3, _p(out))
+    return out, bad
+
+
+def etc2_transcodable(blocks):
+    """Mask of blocks the reference's ETC2 path accepts without tripping its `multiplier >= 1` assert (random payloads
+    behind an alpha mode prefix can carry a zero EAC multiplier; the reference encoder never writes one)."""
+    blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1, 16)
+    out = np.zeros(blocks.shape[0], np.uint16)
+    f = port().port_etc2_hints
+    f.restype = None
+    f.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_void_p]
+    f(_p(blocks), blocks.shape[0], out.ctypes.data)
+    return (out == 0xFFFF) | ((out >> 4) >= 1)
+
+
 def texels_to_image(texels, w, h):
     """[n,64] per-block texels (raster inside the block) -> uint8 [h,w,4], clipped like transcode_slice does."""
     bx, by = (w + 3) // 4, (h + 3) // 4

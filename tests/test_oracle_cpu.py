@@ -247,3 +247,51 @@ def test_port_decode_image_targets_vs_reference(w, h):
     for tf in (14, 15, 16):
         ref16, ok = R.ref_transcode_image(blocks, w, h, tf)
         assert ok and (R.pack_image16(mine, tf) == ref16).all()
+
+
+# ---- the hint-driven targets (ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R, BC5_RG): SURVEY 8(f).2
+HINTED = {0: "etc1", 1: "etc2", 2: "bc1", 3: "bc3", 4: "bc4", 5: "bc5"}
+
+
+@pytest.mark.parametrize("tf", sorted(HINTED))
+def test_port_hinted_targets_golden_corpus(tf):
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    h = np.load(os.path.join(GOLD, "hinted_golden.npz"))
+    u = g["uastc"][h["index"]]
+    got, bad = R.port_transcode_hinted(u, tf)
+    assert bad == -1 and (got == h[HINTED[tf]]).all()
+    if tf in (2, 3):
+        assert (R.port_transcode_hinted(u, tf, 32)[0] == h[HINTED[tf] + "_hq"]).all()
+    if tf == 4:
+        assert (R.port_transcode_hinted(u, tf, 4, True)[0] == h["bc4_alpha"]).all()
+        assert (R.port_transcode_hinted(u, tf, 4, False)[0] == h["bc4"]).all()
+    got, bad = R.port_transcode_hinted(g["invalid"][:64], tf)
+    assert bad == 0 and (got == 0).all()
+
+
+@needs_ref
+def test_ref_hinted_golden_is_current():
+    """The committed fixture equals what the reference build in this container produces (pins the fixture)."""
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    h = np.load(os.path.join(GOLD, "hinted_golden.npz"))
+    u = g["uastc"][h["index"]][:4096]
+    for tf, name in HINTED.items():
+        want, ok = R.ref_transcode_hinted(u, tf)
+        assert ok and (want == h[name][:4096]).all(), name
+
+
+@needs_ref
+@pytest.mark.parametrize("maker,seed", [(R.img_mix, 31), (R.img_noise, 32), (R.img_smooth, 33)])
+def test_port_hinted_targets_vs_reference_images(maker, seed):
+    """Reference-encoded images (real hint bits, every level) through every target / flag combination."""
+    px = R.ref_extract_blocks(maker(128, 96, seed))
+    for level in (0, 1, 3):
+        blocks = R.ref_encode_blocks(px, level)
+        for tf in sorted(HINTED):
+            for fl in (0, 32, 4):
+                for has_alpha in (True, False):
+                    if tf == 0 and (fl & 4) and has_alpha:
+                        continue
+                    want, ok = R.ref_transcode_hinted(blocks, tf, fl, has_alpha)
+                    got, bad = R.port_transcode_hinted(blocks, tf, fl, has_alpha)
+                    assert ok and bad == -1 and (got == want).all(), (level, tf, fl, has_alpha)
