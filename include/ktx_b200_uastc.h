@@ -145,6 +145,21 @@ typedef struct b200_uastc_params {
 int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params,
                       uint8_t* const* out_blocks, uint32_t* out_any_alpha);
 
+/* The same call taking the texture's own texel layout, so the glue can hand in pData + image offset without its
+ * copy / swizzle pass (lib/src/basis_encode.cpp:806-833: copy_rgba_to_rgba, copy_rgb_to_rgba, swizzle_to_rgba :93-144): images[i].rgba
+ * then points at num_components bytes per texel (row_pitch_bytes 0 = width * num_components) and swizzle[c] says what
+ * RGBA channel c receives, in libktx's swizzle_e values (basis_encode.cpp:77-84): 1..4 = source component R, G, B, A,
+ * 5 = 0x00, 6 = 0xFF.  The glue's defaults map to: 4 components {1,2,3,4}; 3 components {1,2,3,6}; 2 components (UASTC)
+ * {1,2,5,6}; 1 component {1,1,1,6}; normal map {1,1,1,2}.  A swizzle naming a component the source does not have is
+ * B200_E_INVALID_VALUE (the reference reads the neighbouring texel's bytes there).  format = NULL: RGBA8 as above.
+ * The expansion runs on the device (k_expand_swizzle), so the upload is 1-4 bytes per texel. */
+typedef struct b200_src_format {
+  uint32_t num_components; /* 1..4 */
+  uint8_t swizzle[4];      /* swizzle_e per output channel */
+} b200_src_format;
+int b200_uastc_encode_ex(const b200_image* images, uint32_t n_images, const b200_src_format* format,
+                         const b200_uastc_params* params, uint8_t* const* out_blocks, uint32_t* out_any_alpha);
+
 /* Device-resident variant: d_block_pixels = n_blocks x 64 bytes (4x4 RGBA8 texels, raster within the block, as
  * basis_compressor::extract_source_blocks lays them out, ENC/basisu_comp.cpp:2705-2766); d_out = n_blocks x 16 B. */
 int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64_t n_blocks, uint32_t pack_flags,

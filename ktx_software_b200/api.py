@@ -20,7 +20,7 @@ def target_block_bytes(target):
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
-                    "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex"]
+                    "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -46,6 +46,10 @@ class Image(ctypes.Structure):
 class DevImage(ctypes.Structure):
     _fields_ = [("d_rgba", ctypes.c_void_p), ("width", ctypes.c_uint32), ("height", ctypes.c_uint32), ("row_pitch_bytes", ctypes.c_uint32),
                 ("d_out", ctypes.c_void_p)]
+
+
+class SrcFormat(ctypes.Structure):
+    _fields_ = [("num_components", ctypes.c_uint32), ("swizzle", ctypes.c_uint8 * 4)]
 
 
 class UastcParams(ctypes.Structure):
@@ -77,6 +81,8 @@ def lib():
                                                   ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_encode.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(UastcParams),
                                         ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
+        l.b200_uastc_encode_ex.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(SrcFormat), ctypes.POINTER(UastcParams),
+                                           ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
         l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
@@ -222,6 +228,31 @@ def encode_images(images, pack_flags, **rdo):
     p = make_params(pack_flags, **rdo)
     any_alpha = ctypes.c_uint32(0)
     _check(lib().b200_uastc_encode(arr, len(imgs), ctypes.byref(p), optr, ctypes.byref(any_alpha)))
+    return outs, bool(any_alpha.value)
+
+
+SWIZZLE_CODES = {"r": 1, "g": 2, "b": 3, "a": 4, "0": 5, "1": 6}   # swizzle_e (lib/src/basis_encode.cpp:77-84)
+
+
+def encode_images_ex(images, swizzle, pack_flags, **rdo):
+    """Host-buffer encode of images in the texture's own layout (b200_uastc_encode_ex).  images: uint8 [h,w,c] arrays, c = 1..4
+    (all the same c); swizzle: 4 characters of "rgba01" as in ktxBasisParams::inputSwizzle.  Returns (blocks per image, any_alpha)."""
+    imgs = [np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+    comps = imgs[0].shape[2] if imgs else 4
+    fmt = SrcFormat(comps, (ctypes.c_uint8 * 4)(*[SWIZZLE_CODES[ch] for ch in swizzle]))
+    arr = (Image * max(1, len(imgs)))()
+    outs = []
+    optr = (ctypes.c_void_p * max(1, len(imgs)))()
+    for i, im in enumerate(imgs):
+        h, w = im.shape[:2]
+        assert im.shape[2] == comps
+        arr[i] = Image(im.ctypes.data, w, h, 0)
+        o = np.zeros((((w + 3) // 4) * ((h + 3) // 4), 16), np.uint8)
+        outs.append(o)
+        optr[i] = o.ctypes.data
+    p = make_params(pack_flags, **rdo)
+    any_alpha = ctypes.c_uint32(0)
+    _check(lib().b200_uastc_encode_ex(arr, len(imgs), ctypes.byref(fmt), ctypes.byref(p), optr, ctypes.byref(any_alpha)))
     return outs, bool(any_alpha.value)
 
 

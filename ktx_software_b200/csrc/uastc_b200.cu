@@ -576,6 +576,28 @@ __global__ void __launch_bounds__(256) k_gather_blocks(const uint8_t* __restrict
   }
 }
 
+// Source texels of 1-4 components -> RGBA8 through libktx's component mapping (swizzle_to_rgba / copy_rgb_to_rgba,
+// lib/src/basis_encode.cpp:100-144): output channel c takes source component sel_c - 1 (R..A = 1..4), 0x00 (5) or 0xFF (6).
+// A streaming pass at HBM speed (<= 8 B per texel against the encoder's ~1.3 us of ALU work per block).
+__global__ void __launch_bounds__(256) k_expand_swizzle(const uint8_t* __restrict__ src, uint32_t w, uint32_t rows, uint32_t src_pitch,
+                                                        uint32_t comps, uint32_t sel, uint32_t* __restrict__ dst) {
+  const uint64_t n = (uint64_t)w * rows;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t y = (uint32_t)(i / w), x = (uint32_t)(i - (uint64_t)y * w);
+    const uint8_t* q = src + (size_t)y * src_pitch + (size_t)x * comps;
+    uint32_t b[4] = {0, 0, 0, 0};
+    for (uint32_t k = 0; k < comps; k++) b[k] = q[k];
+    uint32_t o = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 4; c++) {
+      const uint32_t sc = (sel >> (8 * c)) & 255u;
+      const uint32_t v = sc <= 4 ? b[(sc - 1) & 3u] : (sc == 5 ? 0u : 255u);
+      o |= v << (8 * c);
+    }
+    dst[i] = o;
+  }
+}
+
 __device__ __forceinline__ ub::Bits128 to_bits(const uint4& v) {
   ub::Bits128 b;
   b.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
@@ -918,21 +940,28 @@ int rdo_run(uint4* d_blocks, const uint4* d_px, const std::vector<uint64_t>& img
 
 // Encode + RDO for a host call: every image's texel blocks and UASTC blocks stay resident (64 + 16 B per block) so the
 // post-pass can walk them; job ranges are per image, all ranges of all images walk concurrently.
-int encode_with_rdo(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
+unsigned expand_grid(uint64_t texels) { return (unsigned)std::min<uint64_t>((texels + 255) / 256, (uint64_t)g_ctx.sm_count * 32); }
+
+// Source layout of a host encode call: components per texel and the packed component mapping (see k_expand_swizzle)
+struct SrcFmt { uint32_t comps = 4, sel = 0x04030201u; bool identity() const { return comps == 4 && sel == 0x04030201u; } };
+
+int encode_with_rdo(const b200_image* images, uint32_t n_images, const SrcFmt& fmt, const b200_uastc_params* params, uint8_t* const* out_blocks,
                     uint32_t* out_any_alpha, cudaStream_t* ss) {
   std::vector<uint64_t> nb(n_images);
   uint64_t total = 0;
-  size_t max_in = 0;
+  size_t max_in = 0, max_exp = 0;
   for (uint32_t i = 0; i < n_images; i++) {
-    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * 4;
-    if (pitch < (size_t)images[i].width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * fmt.comps;
+    if (pitch < (size_t)images[i].width * fmt.comps) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
     nb[i] = (uint64_t)((images[i].width + 3) / 4) * ((images[i].height + 3) / 4);
     total += nb[i];
     max_in = std::max(max_in, pitch * images[i].height);
+    max_exp = std::max(max_exp, (size_t)images[i].width * 4 * images[i].height);
   }
-  uint8_t* d_img = nullptr; uint4* d_px = nullptr; uint4* d_blk = nullptr; unsigned int* d_alpha = nullptr;
-  auto cleanup = [&]() { cudaFree(d_img); cudaFree(d_px); cudaFree(d_blk); cudaFree(d_alpha); };
+  uint8_t* d_img = nullptr; uint4* d_px = nullptr; uint4* d_blk = nullptr; unsigned int* d_alpha = nullptr; uint8_t* d_exp = nullptr;
+  auto cleanup = [&]() { cudaFree(d_img); cudaFree(d_px); cudaFree(d_blk); cudaFree(d_alpha); cudaFree(d_exp); };
   cudaError_t e = cudaMalloc(&d_img, max_in);
+  if (e == cudaSuccess && !fmt.identity()) e = cudaMalloc(&d_exp, max_exp);
   if (e == cudaSuccess) e = cudaMalloc(&d_px, total * 64);
   if (e == cudaSuccess) e = cudaMalloc(&d_blk, total * 16);
   if (e == cudaSuccess) e = cudaMalloc(&d_alpha, 4);
@@ -943,11 +972,17 @@ int encode_with_rdo(const b200_image* images, uint32_t n_images, const b200_uast
   uint64_t off = 0;
   for (uint32_t i = 0; i < n_images && e == cudaSuccess; i++) {
     const b200_image& im = images[i];
-    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
+    uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * fmt.comps;
     const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
     e = cudaMemcpyAsync(d_img, im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) break;
-    k_gather_blocks<<<(unsigned)std::min<uint64_t>((nb[i] + 255) / 256, (uint64_t)g_ctx.sm_count * 16), 256, 0, st>>>(d_img, im.width, im.height, pitch, d_px + off * 4, bx, by, d_alpha);
+    const uint8_t* d_rgba = d_img;
+    if (!fmt.identity()) {
+      k_expand_swizzle<<<expand_grid((uint64_t)im.width * im.height), 256, 0, st>>>(d_img, im.width, im.height, pitch, fmt.comps, fmt.sel, (uint32_t*)d_exp);
+      g_launches++;
+      d_rgba = d_exp; pitch = im.width * 4;
+    }
+    k_gather_blocks<<<(unsigned)std::min<uint64_t>((nb[i] + 255) / 256, (uint64_t)g_ctx.sm_count * 16), 256, 0, st>>>(d_rgba, im.width, im.height, pitch, d_px + off * 4, bx, by, d_alpha);
     if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
     else k_encode_blocks<MAXC_FAST><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
     g_launches += 2;
@@ -982,8 +1017,8 @@ thread_local ThreadStreams t_streams;
 // Per host thread: the staging buffers of the host-buffer entry points live across calls (a cudaMalloc / cudaFree pair per
 // call costs milliseconds and synchronises the device).  Slots 0-2: slab inputs, 3-5: slab outputs, 6: flags.
 struct Staging {
-  void* p[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  size_t n[7] = {0, 0, 0, 0, 0, 0, 0};
+  void* p[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 7-9: expanded RGBA8 slabs
+  size_t n[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   void* get(int i, size_t bytes) {
     if (n[i] < bytes) {
       if (p[i]) cudaFree(p[i]);
@@ -993,7 +1028,7 @@ struct Staging {
     }
     return p[i];
   }
-  void release() { for (int i = 0; i < 7; i++) { if (p[i]) cudaFree(p[i]); p[i] = nullptr; n[i] = 0; } }
+  void release() { for (int i = 0; i < 10; i++) { if (p[i]) cudaFree(p[i]); p[i] = nullptr; n[i] = 0; } }
   ~Staging() { /* at thread exit the context may be gone: the driver reclaims */ }
 };
 thread_local Staging t_stage;
@@ -1363,7 +1398,23 @@ int b200_uastc_rdo_blocks_dev(void* d_blocks, const void* d_block_pixels, uint64
 
 int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
                       uint32_t* out_any_alpha) {
+  return b200_uastc_encode_ex(images, n_images, nullptr, params, out_blocks, out_any_alpha);
+}
+
+int b200_uastc_encode_ex(const b200_image* images, uint32_t n_images, const b200_src_format* format, const b200_uastc_params* params,
+                         uint8_t* const* out_blocks, uint32_t* out_any_alpha) {
   if (out_any_alpha) *out_any_alpha = 0;
+  SrcFmt fmt;
+  if (format) {
+    if (format->num_components < 1 || format->num_components > 4) return fail(B200_E_INVALID_VALUE, "num_components must be 1..4");
+    fmt.comps = format->num_components; fmt.sel = 0;
+    for (int c = 0; c < 4; c++) {
+      const uint32_t sc = format->swizzle[c];
+      if (sc < 1 || sc > 6) return fail(B200_E_INVALID_VALUE, "swizzle entries are swizzle_e values 1..6");
+      if (sc <= 4 && sc > fmt.comps) return fail(B200_E_INVALID_VALUE, "swizzle names a component the source does not have");
+      fmt.sel |= sc << (8 * c);
+    }
+  }
   if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
   if (n_images && (!images || !out_blocks)) return fail(B200_E_INVALID_VALUE, "null pointer");
   for (uint32_t i = 0; i < n_images; i++)
@@ -1374,7 +1425,7 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   rc = get_streams(&ss);
   if (rc) return rc;
   if (!n_images) return B200_OK;
-  if (params->rdo_enable) return encode_with_rdo(images, n_images, params, out_blocks, out_any_alpha, ss);
+  if (params->rdo_enable) return encode_with_rdo(images, n_images, fmt, params, out_blocks, out_any_alpha, ss);
 
   // Slab list: every image is cut into runs of whole block rows (contiguous in the RGBA source and in the UASTC
   // output) of at most SLAB_BYTES of input, so upload, encode and download of neighbouring slabs overlap on three
@@ -1382,31 +1433,33 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
   const size_t SLAB_BYTES = 32u << 20;
   struct Slab { uint32_t img, y0, rows_px; size_t in_bytes, out_off, out_bytes; };
   std::vector<Slab> slabs;
-  size_t max_in = 0, max_out = 0;
+  size_t max_in = 0, max_out = 0, max_exp = 0;
   for (uint32_t i = 0; i < n_images; i++) {
     const b200_image& im = images[i];
-    const size_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : (size_t)im.width * 4;
-    if (pitch < (size_t)im.width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+    const size_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : (size_t)im.width * fmt.comps;
+    if (pitch < (size_t)im.width * fmt.comps) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
     const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
-    uint32_t rows_per = (uint32_t)std::max<size_t>(1, SLAB_BYTES / (pitch * 4));
+    uint32_t rows_per = (uint32_t)std::max<size_t>(1, SLAB_BYTES / (std::max(pitch, (size_t)im.width * 4) * 4));
     for (uint32_t r0 = 0; r0 < by; r0 += rows_per) {
       const uint32_t r1 = std::min(by, r0 + rows_per);
       const uint32_t y0 = r0 * 4, y1 = std::min(im.height, r1 * 4);
       Slab sl{i, y0, y1 - y0, pitch * (y1 - y0), (size_t)r0 * bx * 16, (size_t)(r1 - r0) * bx * 16};
       max_in = std::max(max_in, sl.in_bytes);
       max_out = std::max(max_out, sl.out_bytes);
+      max_exp = std::max(max_exp, (size_t)im.width * 4 * (y1 - y0));
       slabs.push_back(sl);
     }
   }
   const int SLOTS = 3;
-  uint8_t* d_in[SLOTS] = {0}; uint8_t* d_out[SLOTS] = {0};
+  uint8_t* d_in[SLOTS] = {0}; uint8_t* d_out[SLOTS] = {0}; uint8_t* d_exp[SLOTS] = {0};
   unsigned int* d_alpha = nullptr;
   cudaEvent_t ev_in[SLOTS], ev_k[SLOTS], ev_out[SLOTS];
   const int nslots = (int)std::min<size_t>(SLOTS, slabs.size());
   auto cleanup = [&]() {};   // staging buffers stay cached (t_stage)
   for (int i = 0; i < nslots; i++) {
     d_in[i] = (uint8_t*)t_stage.get(i, max_in); d_out[i] = (uint8_t*)t_stage.get(3 + i, max_out);
-    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
+    if (!fmt.identity()) d_exp[i] = (uint8_t*)t_stage.get(7 + i, max_exp);
+    if (!d_in[i] || !d_out[i] || (!fmt.identity() && !d_exp[i])) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
     cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
@@ -1428,7 +1481,7 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
     const b200_image& im = images[sl.img];
     const int b = (int)(k % nslots);
     cudaStream_t s_k = s_kk[k & 1];
-    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
+    uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * fmt.comps;
     const uint32_t bx = (im.width + 3) / 4, by = (sl.rows_px + 3) / 4;
     if (k >= (size_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
     err = cudaMemcpyAsync(d_in[b], im.rgba + (size_t)sl.y0 * pitch, sl.in_bytes, cudaMemcpyHostToDevice, s_in);
@@ -1436,8 +1489,14 @@ int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_ua
     cudaEventRecord(ev_in[b], s_in);
     cudaStreamWaitEvent(s_k, ev_in[b], 0);
     const uint64_t n = (uint64_t)bx * by;
-    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
-    else k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    const uint8_t* d_rgba = d_in[b];
+    if (!fmt.identity()) {   // component expansion / swizzle on the device: the upload carries the texture's own 1-4 bytes per texel
+      k_expand_swizzle<<<expand_grid((uint64_t)im.width * sl.rows_px), 256, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, fmt.comps, fmt.sel, (uint32_t*)d_exp[b]);
+      g_launches++;
+      d_rgba = d_exp[b]; pitch = im.width * 4;
+    }
+    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_rgba, im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
+    else k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_rgba, im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
     g_launches++;
     cudaEventRecord(ev_k[b], s_k);
     cudaStreamWaitEvent(s_out, ev_k[b], 0);

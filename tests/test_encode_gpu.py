@@ -162,3 +162,60 @@ def test_batched_images_one_launch_and_big_cta_path(K):
         px = R.ref_extract_blocks(imgs[0][:64])          # the first 16 block rows
         assert (outs[0][:px.shape[0]].cpu().numpy() == R.ref_encode_blocks(px, 2)).all()
     K.encode_images_dev([], 2)
+
+
+# ---- b200_uastc_encode_ex: the texture's own texel layout + libktx's component mapping applied on the device
+def _np_swizzle(img, swz):
+    """numpy restatement of swizzle_to_rgba / copy_rgb_to_rgba (lib/src/basis_encode.cpp:100-144)."""
+    h, w, c = img.shape
+    out = np.zeros((h, w, 4), np.uint8)
+    for k, ch in enumerate(swz):
+        if ch in "rgba":
+            out[..., k] = img[..., "rgba".index(ch)]
+        else:
+            out[..., k] = 0 if ch == "0" else 255
+    return out
+
+
+def test_encode_ex_cts_goldens_native_components(K):
+    """The reference CTS `ktx create --encode uastc` goldens, fed in their own 1-4 component layout with the glue's
+    default mapping (lib/src/basis_encode.cpp:696-699,732-745)."""
+    cts = json.load(open(os.path.join(GOLD, "cts_uastc.json")))["encode"]
+    default = {1: "rrr1", 2: "rg01", 3: "rgb1", 4: "rgba"}
+    n = 0
+    for sub, c in cts.items():
+        if not c.get("raw"):
+            continue
+        raw = np.frombuffer(bytes.fromhex(c["raw"]), np.uint8).reshape(c["height"], c["width"], c["comps"])
+        outs, _ = K.encode_images_ex([raw], default[c["comps"]], 2)
+        want = np.frombuffer(bytes.fromhex(c["uastc"]), np.uint8).reshape(-1, 16)
+        assert (outs[0] == want).all(), sub
+        n += 1
+    if n == 0:
+        pytest.skip("CTS raw inputs not recorded in the fixture")
+
+
+@pytest.mark.parametrize("comps,swz", [(1, "rrr1"), (1, "r001"), (2, "rg01"), (2, "rrrg"), (3, "rgb1"), (3, "bgr0"), (4, "rgba"),
+                                       (4, "bgra"), (4, "aaa1"), (4, "rg01")])
+def test_encode_ex_matches_host_swizzle(K, comps, swz):
+    """Device-side expansion == the glue's host copy followed by the RGBA entry point; ragged sizes, a mip tail, alpha flag."""
+    imgs = [R.img_mix(70, 37, 3)[..., :comps].copy(), R.img_mix(2, 2, 4)[..., :comps].copy(), R.img_noise(33, 64, 5)[..., :comps].copy()]
+    got, a0 = K.encode_images_ex(imgs, swz, 1)
+    want, a1 = K.encode_images([_np_swizzle(im, swz) for im in imgs], 1)
+    assert a0 == a1
+    for g, w in zip(got, want):
+        assert (g == w).all()
+
+
+def test_encode_ex_slabs_rdo_and_errors(K):
+    big = R.img_mix(4096, 2304, 9)[..., :3].copy()     # several 32 MiB slabs after expansion
+    got, _ = K.encode_images_ex([big], "rgb1", 0)
+    want, _ = K.encode_images([_np_swizzle(big, "rgb1")], 0)
+    assert (got[0] == want[0]).all()
+    small = R.img_mix(96, 64, 11)[..., :2].copy()
+    got, _ = K.encode_images_ex([small], "rrrg", 2, rdo=True, rdo_lambda=1.0)
+    want, _ = K.encode_images([_np_swizzle(small, "rrrg")], 2, rdo=True, rdo_lambda=1.0)
+    assert (got[0] == want[0]).all()
+    with pytest.raises(K.B200Error) as ei:   # a component the source does not have
+        K.encode_images_ex([small], "rgb1", 0)
+    assert ei.value.code == -2
