@@ -272,6 +272,51 @@ def run_c5(args):
     e2e_val = 32.0 * ne * world / t.item() / 1e9
     e2e_ok = bool((h_dst[:1 << 14].numpy() == d_dst[:1 << 14].cpu().numpy()).all())
 
+    # The other block targets on a 2^24-block slice of the same input, device-resident, with the reference
+    # transcoder timed beside each on a bounded sample.  bytes = 16 read + 8 or 16 written per block.
+    targets = {}
+    if rank == 0:
+        nt = min(n, 1 << 24)
+        names = [("astc", K.TTF_ASTC_4x4_RGBA), ("bc1", K.TTF_BC1_RGB), ("bc3", K.TTF_BC3_RGBA), ("bc4", K.TTF_BC4_R), ("bc5", K.TTF_BC5_RG),
+                 ("etc1", K.TTF_ETC1_RGB), ("etc2", K.TTF_ETC2_RGBA)]
+        for name, tf in names:
+            ob = K.target_block_bytes(tf)
+            for _ in range(2):
+                K.transcode_dev_ex(tf, 0, True, d_src.data_ptr(), d_dst.data_ptr(), nt, stream.cuda_stream, d_bad.data_ptr())
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 5
+            a.record()
+            for _ in range(reps):
+                K.transcode_dev_ex(tf, 0, True, d_src.data_ptr(), d_dst.data_ptr(), nt, stream.cuda_stream, d_bad.data_ptr())
+            b.record(); torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / reps
+            ent = {"gbs": (16.0 + ob) * nt / ms / 1e6, "ms": ms, "blocks": nt, "bytes_per_block": 16 + ob,
+                   "frac_of_hbm_peak": (16.0 + ob) * nt / ms / 1e6 / pk["hbm_gbs"]}
+            if R.have_ref():
+                ns = 1 << 16
+                hb = np.ascontiguousarray(d_src[:ns].cpu().numpy())
+                got = d_dst.reshape(-1)[:ns * ob].cpu().numpy().reshape(ns, ob)
+                if tf == K.TTF_ASTC_4x4_RGBA:
+                    want = R.ref_transcode(hb, 1)[0]
+                else:
+                    want = R.ref_transcode_hinted(hb, tf)[0]
+                ent["parity_vs_reference"] = bool((got == want).all())
+                if tf != K.TTF_ASTC_4x4_RGBA:
+                    cores = os.cpu_count() or 1
+                    nb = 1 << 20
+                    big = np.ascontiguousarray(d_src[:nb].cpu().numpy())
+                    chunks = np.array_split(big, cores)
+                    from concurrent.futures import ThreadPoolExecutor
+                    with ThreadPoolExecutor(cores) as ex:
+                        list(ex.map(lambda c: R.ref_transcode_hinted(c, tf), chunks))   # warm
+                        t0 = time.perf_counter()
+                        list(ex.map(lambda c: R.ref_transcode_hinted(c, tf), chunks))
+                        dt = time.perf_counter() - t0
+                    ent["cpu_reference_gbs"] = (16.0 + ob) * nb / dt / 1e9
+                    ent["cpu_reference_sample"] = "%d blocks, transcode_image over %d threads" % (nb, cores)
+            targets[name] = ent
+        d_bad.fill_(-1)
+
     if rank == 0:
         cpu = None
         if R.have_ref():
@@ -303,6 +348,7 @@ def run_c5(args):
                              # ncu --set full of this workload (profiles/r2i_transcode_tiled_ncu_summary.txt), 2^26 blocks
                              "traffic": (1.076825e9 + 1.027500e9) if n == (1 << 26) else None, "peak_kind": pk_kind,
                              "kernel": "k_transcode_tiled<BC7>", "kernel_ms": kern_ms, "algorithmic_bytes_per_launch": 32 * n},
+                "other_targets": targets,
                 "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:

@@ -226,8 +226,10 @@ __device__ __forceinline__ bool hinted_form_dispatch(uint32_t mode, const ub::Bi
 }
 
 // 0 = BC7, 1 = ASTC (dst = blocks, written through the shared-memory tile), 2 = texels (dst = image, im),
-// 3 = the hint-driven block targets (im.kind: ETC1 / ETC2 / BC1 / BC3 / BC4 / BC5; 8 or 16 bytes per block)
-template <int TARGET>
+// 3 = the hint-driven block targets (KIND = ktx_transcode_fmt_e 0..5: ETC1 / ETC2 / BC1 / BC3 / BC4 / BC5; 8 or 16 bytes per
+// block).  KIND is a template parameter so each target's kernel holds only its own packer (one kernel with a run-time
+// switch over six packers paid the register and spill cost of the largest, encode_bc1, in every target).
+template <int TARGET, int KIND = 0>
 __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
                                                                 unsigned long long* __restrict__ first_bad, const XtImage im) {
   constexpr int TILE = xt_tile(TARGET), PER_THREAD = TILE / XT_THREADS;
@@ -236,7 +238,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   uint4* s_out = (uint4*)(xt_smem + 2 * (size_t)TILE * 16);   // TARGET 2 only: [4 texel rows][TILE] row pieces of 16 (or 8) bytes
   uint2* s_out8 = (uint2*)(xt_smem + 2 * (size_t)TILE * 16);  // TARGET 3, 8-byte targets: the output tile
   uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
-  const bool out8 = TARGET == 3 && ub::hinted_target_bytes(im.kind) == 8;
+  constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
   uint16_t* s_order = (uint16_t*)(s_hist + 32);
 
@@ -342,7 +344,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         } else if (TARGET == 3) {
           ub::HintedForm h;
           ok = hinted_form_dispatch(m, s, h);   // mode-specialised
-          if (ok) ub::hinted_target_from_form(h, im.kind, im.hq != 0, im.chan0, im.chan1, d);   // shared by all modes
+          if (ok) ub::hinted_target_from_form(h, (uint32_t)KIND, im.hq != 0, im.chan0, im.chan1, d);   // shared by all modes
           else { d.lo = 0; d.hi = 0; }
           if (out8) s_out8[idx] = make_uint2((uint32_t)d.lo, (uint32_t)(d.lo >> 32));
           else s_in[buf][idx] = make_uint4((uint32_t)d.lo, (uint32_t)(d.lo >> 32), (uint32_t)d.hi, (uint32_t)(d.hi >> 32));
@@ -839,7 +841,11 @@ int launch_hinted(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, co
   im.chan1 = 3u;
   const uint64_t tiles = (n + xt_tile(3) - 1) / xt_tile(3);
   const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
-  k_transcode_tiled<3><<<grid, XT_THREADS, xt_smem_bytes(3), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im);
+  switch (target) {
+#define XH_CASE(KIND) case KIND: k_transcode_tiled<3, KIND><<<grid, XT_THREADS, xt_smem_bytes(3), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im); break;
+    XH_CASE(0) XH_CASE(1) XH_CASE(2) XH_CASE(3) XH_CASE(4) XH_CASE(5)
+#undef XH_CASE
+  }
   g_launches++;
   CU(cudaGetLastError());
   return B200_OK;
@@ -1064,7 +1070,12 @@ int b200_uastc_init(void) {
   CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(0)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(1)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(2)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
   g_ctx.ready = true;
   return B200_OK;
 }
