@@ -154,7 +154,7 @@ __host__ __device__ constexpr int xt_tile(int target) { return (target == 2 && X
 __host__ __device__ constexpr int xt_data_tiles(int target) { return (target == 2 && XT_DECODE_STAGED) ? 6 : 2; }
 // TARGET 3 adds a TILE x 8-byte output tile for the 8-byte targets (their results cannot overwrite the 16-byte input slots)
 __host__ __device__ constexpr size_t xt_data_bytes(int target) { return (size_t)xt_data_tiles(target) * xt_tile(target) * 16 + (target == 3 ? (size_t)xt_tile(target) * 8 : 0); }
-constexpr size_t xt_smem_bytes(int target) { return xt_data_bytes(target) + 2 * 8 + 32 * 4 + (size_t)xt_tile(target) * 2; }
+constexpr size_t xt_smem_bytes(int target) { return xt_data_bytes(target) + 2 * 8 + 64 * 4 + (size_t)xt_tile(target) * 2; }
 
 __device__ __forceinline__ void store_block_texels(uint8_t* __restrict__ dst, const XtImage& im, uint64_t block_index, const uint32_t* px) {
   const uint32_t by = (uint32_t)(block_index / im.bx), bxi = (uint32_t)(block_index - (uint64_t)by * im.bx);
@@ -240,7 +240,11 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
   constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
-  uint16_t* s_order = (uint16_t*)(s_hist + 32);
+  uint16_t* s_order = (uint16_t*)(s_hist + 64);
+  // BC1 / BC3: the cost of a block is set by which BC1 path its hint bits select (hint0: endpoints + weights as they are;
+  // hint1: one least-squares fit on the block's weights; none: the full encode_bc1), so the bins are (path, mode) pairs --
+  // 3 x 19 of them, scanned as two bins per lane -- and a warp runs one path of one mode.
+  constexpr bool WIDE = TARGET == 3 && (KIND == 2 || KIND == 3);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
   const uint64_t n_tiles = (n_blocks + TILE - 1) / TILE;
@@ -248,7 +252,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   if (tile >= n_tiles) return;
   auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)TILE, n_blocks - t * TILE); };
 
-  if (tid < 32) s_hist[tid] = 0;
+  if (tid < 64) s_hist[tid] = 0;
   if (XT_SMEM_TABLES) ub::shared_tables_load(tid, XT_THREADS);
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
@@ -282,7 +286,18 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
       const bool live = i < cnt;
-      const uint32_t m = live ? (uint32_t)ub::UBT(uastc_huff_modes)[s_in[buf][live ? i : 0].x & 127u] : 31u;
+      const uint32_t w0 = s_in[buf][live ? i : 0].x;
+      uint32_t m = live ? (uint32_t)ub::UBT(uastc_huff_modes)[w0 & 127u] : 31u;
+      if (WIDE) {   // m becomes the (path, mode) bin: 0..56, 62 = invalid mode code, 63 = no block
+        if (!live) m = 63u;
+        else if (m >= ub::UASTC_TOTAL_MODES) m = 62u;
+        else {
+          const uint32_t len = ub::md_huff_len(ub::UBT(uastc_mode_desc)[m]);
+          const uint32_t has0 = ub::UBT(uastc_mode_has_bc1_hint0)[m], has1 = ub::UBT(uastc_mode_has_bc1_hint1)[m];
+          const uint32_t h0 = has0 ? ((w0 >> len) & 1u) : 0u, h1 = has1 ? ((w0 >> (len + has0)) & 1u) : 0u;
+          m += 19u * ((!im.hq && h0) ? 0u : (h1 ? 1u : 2u));
+        }
+      }
       const uint32_t peers = __match_any_sync(0xFFFFFFFFu, m);
       const uint32_t leader = __ffs(peers) - 1;
       uint32_t base = 0;
@@ -293,22 +308,31 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     }
     __syncthreads();
     // every warp scans the 32 bin counts for itself (lane = bin): no second barrier, no shared-memory round trip
-    uint32_t bin_start;
+    uint32_t bin_start, bin_start_hi = 0;
     {
       const uint32_t c = s_hist[lane];
       uint32_t v = c;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v, o); if ((int)lane >= o) v += t; }
       bin_start = v - c;
+      if (WIDE) {   // bins 32..63 follow
+        const uint32_t total_lo = __shfl_sync(0xFFFFFFFFu, v, 31);
+        const uint32_t c1 = s_hist[32 + lane];
+        uint32_t v1 = c1;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v1, o); if ((int)lane >= o) v1 += t; }
+        bin_start_hi = total_lo + v1 - c1;
+      }
     }
 #pragma unroll
     for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
-      const uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, my_mode[k]);
+      uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, my_mode[k] & 31u);
+      if (WIDE) { const uint32_t hi = __shfl_sync(0xFFFFFFFFu, bin_start_hi, my_mode[k] & 31u); if (my_mode[k] >= 32u) start = hi; }
       if (i < cnt) s_order[start + my_rank[k]] = (uint16_t)i;
     }
     __syncthreads();
-    if (tid < 32) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
+    if (tid < 64) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
 #pragma unroll 1

@@ -77,22 +77,52 @@ UB_FN HintFields parse_hints(uint32_t mode, uint32_t hints) {
   return o;
 }
 
-// encode_bc4 (XC:17372-17490) of channel `chan` of 16 texels -> the 8-byte block, little-endian.
-UB_FN uint64_t bc4_encode(const uint32_t* px, uint32_t chan) {
+// One channel of the 16 texels (what unpack_uastc :15378-15514 yields for it), without interpolating the other three:
+// BC4 / BC5 need one or two channels only.
+UB_FN void channel_from_form(const TexelForm& f, uint32_t chan, uint32_t* v) {
+  const uint32_t sh = (chan & 2u) ? 16u : 0u;   // r: rb low half, g: ga low, b: rb high, a: ga high
+  const bool ga = (chan & 1u) != 0;
+  uint32_t l[3], h[3];
+#pragma unroll
+  for (uint32_t s = 0; s < 3; s++) { l[s] = ((ga ? f.l_ga[s] : f.l_rb[s]) >> sh) & 255u; h[s] = ((ga ? f.h_ga[s] : f.h_rb[s]) >> sh) & 255u; }
+  const bool second = ((f.sel >> (8 * chan)) & 1u) != 0;   // dual plane and this channel takes the second weight
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t s = (f.pat >> (2 * i)) & 3u;
+    const uint32_t a = s == 0 ? l[0] : (s == 1 ? l[1] : l[2]), b = s == 0 ? h[0] : (s == 1 ? h[1] : h[2]);
+    const uint32_t w = ((second ? f.w1[i >> 2] : f.w0[i >> 2]) >> (8 * (i & 3u))) & 255u;
+    const uint32_t t = a * (64u - w) + b * w;
+    v[i] = (t + ((t + 32u) >> 8)) >> 6;   // astc_interpolate, see uastc_to_rgba.cuh
+  }
+}
+
+// encode_bc4 (XC:17372-17490) of 16 channel values -> the 8-byte block, little-endian.
+UB_FN uint64_t bc4_encode_values(const uint32_t* val) {
   uint32_t mn = 255u, mx = 0u;
 #pragma unroll
-  for (uint32_t i = 0; i < 16; i++) { const uint32_t v = ch(px[i], chan); mn = minu(mn, v); mx = maxu(mx, v); }
+  for (uint32_t i = 0; i < 16; i++) { mn = minu(mn, val[i]); mx = maxu(mx, val[i]); }
   uint64_t out = (uint64_t)mx | ((uint64_t)mn << 8);
   if (mx == mn) return out;
   const int delta = (int)(mx - mn), bias = 4 - (int)mn * 14;
   uint64_t bits = 0;
 #pragma unroll
   for (uint32_t i = 0; i < 16; i++) {
-    const int v = (int)ch(px[i], chan) * 14 + bias;
+    const int v = (int)val[i] * 14 + bias;
     const uint32_t k = (uint32_t)(v >= delta * 13) + (v >= delta * 11) + (v >= delta * 9) + (v >= delta * 7) + (v >= delta * 5) + (v >= delta * 3) + (v >= delta);
     bits |= (uint64_t)((0x02345671u >> (4 * k)) & 7u) << (3 * i);   // s_tran = {1,7,6,5,4,3,2,0}
   }
   return out | (bits << 16);
+}
+UB_FN uint64_t bc4_encode(const uint32_t* px, uint32_t chan) {   // channel `chan` of 16 RGBA texels
+  uint32_t v[16];
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) v[i] = ch(px[i], chan);
+  return bc4_encode_values(v);
+}
+UB_FN uint64_t bc4_from_form(const TexelForm& f, uint32_t chan) {
+  uint32_t v[16];
+  channel_from_form(f, chan, v);
+  return bc4_encode_values(v);
 }
 
 UB_FN uint64_t bc1_bytes(const Bc1Block& b) { return (uint64_t)(b.lo16 & 0xFFFFu) | ((uint64_t)(b.hi16 & 0xFFFFu) << 16) | ((uint64_t)b.sels << 32); }
@@ -261,17 +291,18 @@ UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind ==
 // The shared part.  kind = ktx_transcode_fmt_e (0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG);
 // chan0 / chan1: the channels BC4 / BC5 take (transcode_image, XC:10417-10438).  8-byte targets fill d.lo only.
 UB_FN void hinted_target_from_form(const HintedForm& h, uint32_t kind, bool high_quality, uint32_t chan0, uint32_t chan1, Bits128& d) {
+  d.lo = 0; d.hi = 0;
+  if (kind == 4) { d.lo = bc4_from_form(h.f, chan0); return; }
+  if (kind == 5) { d.lo = bc4_from_form(h.f, chan0); d.hi = bc4_from_form(h.f, chan1); return; }
   uint32_t px[16];
   texels_from_form(h.f, px);
   const HintFields hf = parse_hints(h.mode, h.hints);
-  d.lo = 0; d.hi = 0;
   switch (kind) {
     case 0: d.lo = etc1_from_form(h, hf, px); break;
     case 1: d.lo = eac_a8_from_form(h, hf, px); d.hi = etc1_from_form(h, hf, px); break;
     case 2: d.lo = bc1_from_form(h, hf, px, high_quality); break;
     case 3: d.lo = bc4_encode(px, 3); d.hi = bc1_from_form(h, hf, px, high_quality); break;
-    case 4: d.lo = bc4_encode(px, chan0); break;
-    default: d.lo = bc4_encode(px, chan0); d.hi = bc4_encode(px, chan1); break;
+    default: break;
   }
 }
 

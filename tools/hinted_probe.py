@@ -9,7 +9,10 @@ h = np.load(os.path.join(os.path.dirname(__file__), "..", "tests", "golden", "hi
 u = g["uastc"][:16384]   # reference-encoded part of the corpus
 n = 1 << 24
 rep = torch.from_numpy(np.tile(u, (n // u.shape[0], 1))).cuda()
+want = sys.argv[1:]
 for tf, name in [(6, "bc7"), (10, "astc"), (2, "bc1"), (3, "bc3"), (4, "bc4"), (5, "bc5"), (0, "etc1"), (1, "etc2")]:
+    if want and name not in want:
+        continue
     ob = K.target_block_bytes(tf)
     dst = torch.empty(n * ob, dtype=torch.uint8, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
