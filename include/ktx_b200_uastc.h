@@ -36,6 +36,8 @@ extern "C" {
 #define B200_TTF_BC3_RGBA 3
 #define B200_TTF_BC4_R 4
 #define B200_TTF_BC5_RG 5
+#define B200_TTF_ETC2_EAC_R11 20  /* 8 bytes per block  (lib/include/ktx.h:1718) */
+#define B200_TTF_ETC2_EAC_RG11 21 /* 16 bytes per block (lib/include/ktx.h:1722) */
 /* decode flags the path honours: ktx_transcode_flag_bits_e KTX_TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS and KTX_TF_HIGH_QUALITY
  * == basist cDecodeFlagsTranscodeAlphaDataToOpaqueFormats / cDecodeFlagsHighQuality (XC/basisu_transcoder.h:253,265) */
 #define B200_DECODE_FLAG_ALPHA_TO_OPAQUE 4u
@@ -80,10 +82,12 @@ int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, ui
 
 /* The same two entry points with what libktx forwards to transcode_image beside the target: transcodeFlags and
  * (alphaContent != eNone) (lib/src/basis_transcode.cpp:788-789), and with the hint-driven targets ETC1_RGB, ETC2_RGBA,
- * BC1_RGB, BC3_RGBA, BC4_R, BC5_RG: transcode_slice's cETC1 / cETC2_RGBA / cBC1 / cBC3 / cBC4 / cBC5 cases (XC:10141-10180) ->
- * transcode_uastc_to_etc1 (:16444), _etc2_rgba (:17341), _bc1 (:18365), _bc3 (:18404), _bc4 (:18442), _bc5 (:18470).
- * dst offsets and sizes count 8 bytes per block for ETC1_RGB, BC1_RGB and BC4_R.  BC4_R takes alpha instead of red when
- * has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE are set (XC:10417); BC5_RG takes red and alpha (XC:10430).  Not accelerated
+ * BC1_RGB, BC3_RGBA, BC4_R, BC5_RG, ETC2_EAC_R11, ETC2_EAC_RG11: transcode_slice's cETC1 / cETC2_RGBA / cBC1 / cBC3 / cBC4 / cBC5 /
+ * cETC2_EAC_R11 / cETC2_EAC_RG11 cases (XC:10141-10207) -> transcode_uastc_to_etc1 (:16444), _etc2_rgba (:17341), _bc1 (:18365),
+ * _bc3 (:18404), _bc4 (:18442), _bc5 (:18470), _etc2_eac_r11 (:18792), _etc2_eac_rg11 (:18819).
+ * dst offsets and sizes count 8 bytes per block for ETC1_RGB, BC1_RGB, BC4_R and ETC2_EAC_R11.  BC4_R and ETC2_EAC_R11 take
+ * alpha instead of red when has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE are set (XC:10417, :10515); BC5_RG and
+ * ETC2_EAC_RG11 take red and alpha (XC:10430, :10526).  Not accelerated
  * (B200_E_INVALID_VALUE, the glue keeps the stock path): ETC1_RGB from the alpha channel.  Device pointers must be
  * 16-byte aligned. */
 int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans,

@@ -10,11 +10,12 @@ TTF_ASTC_4x4_RGBA = 10  # KTX_TTF_ASTC_4x4_RGBA
 TTF_RGBA32, TTF_RGB565, TTF_BGR565, TTF_RGBA4444 = 13, 14, 15, 16  # the uncompressed targets (ktx.h:1728-1737)
 # the hint-driven block targets (ktx.h:1654-1676); 8 bytes per block for ETC1_RGB, BC1_RGB, BC4_R, else 16
 TTF_ETC1_RGB, TTF_ETC2_RGBA, TTF_BC1_RGB, TTF_BC3_RGBA, TTF_BC4_R, TTF_BC5_RG = 0, 1, 2, 3, 4, 5
+TTF_ETC2_EAC_R11, TTF_ETC2_EAC_RG11 = 20, 21   # ktx.h:1718-1722
 TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS, TF_HIGH_QUALITY = 4, 32   # ktx_transcode_flag_bits_e
 
 
 def target_block_bytes(target):
-    return 8 if target in (TTF_ETC1_RGB, TTF_BC1_RGB, TTF_BC4_R) else 16
+    return 8 if target in (TTF_ETC1_RGB, TTF_BC1_RGB, TTF_BC4_R, TTF_ETC2_EAC_R11) else 16
 
 
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",

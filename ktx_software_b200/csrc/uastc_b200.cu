@@ -226,8 +226,8 @@ __device__ __forceinline__ bool hinted_form_dispatch(uint32_t mode, const ub::Bi
 }
 
 // 0 = BC7, 1 = ASTC (dst = blocks, written through the shared-memory tile), 2 = texels (dst = image, im),
-// 3 = the hint-driven block targets (KIND = ktx_transcode_fmt_e 0..5: ETC1 / ETC2 / BC1 / BC3 / BC4 / BC5; 8 or 16 bytes per
-// block).  KIND is a template parameter so each target's kernel holds only its own packer (one kernel with a run-time
+// 3 = the hint-driven block targets (KIND = ktx_transcode_fmt_e 0..5: ETC1 / ETC2 / BC1 / BC3 / BC4 / BC5, 6 / 7 = ETC2 EAC
+// R11 / RG11; 8 or 16 bytes per block).  KIND is a template parameter so each target's kernel holds only its own packer (one kernel with a run-time
 // switch over six packers paid the register and spill cost of the largest, encode_bc1, in every target).
 template <int TARGET, int KIND = 0>
 __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   uint4* s_out = (uint4*)(xt_smem + 2 * (size_t)TILE * 16);   // TARGET 2 only: [4 texel rows][TILE] row pieces of 16 (or 8) bytes
   uint2* s_out8 = (uint2*)(xt_smem + 2 * (size_t)TILE * 16);  // TARGET 3, 8-byte targets: the output tile
   uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
-  constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4);
+  constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4 || KIND == 6);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
   uint16_t* s_order = (uint16_t*)(s_hist + 64);
   // BC1 / BC3: the cost of a block is set by which BC1 path its hint bits select (hint0: endpoints + weights as they are;
@@ -848,8 +848,8 @@ int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n
 }
 
 // The hint-driven block targets (ETC1_RGB 0, ETC2_RGBA 1, BC1_RGB 2, BC3_RGBA 3, BC4_R 4, BC5_RG 5): 8 or 16 bytes per block.
-bool is_hinted_target(uint32_t t) { return t <= B200_TTF_BC5_RG; }
-uint32_t out_block_bytes(uint32_t t) { return (t == B200_TTF_ETC1_RGB || t == B200_TTF_BC1_RGB || t == B200_TTF_BC4_R) ? 8u : 16u; }
+bool is_hinted_target(uint32_t t) { return t <= B200_TTF_BC5_RG || t == B200_TTF_ETC2_EAC_R11 || t == B200_TTF_ETC2_EAC_RG11; }
+uint32_t out_block_bytes(uint32_t t) { return (t == B200_TTF_ETC1_RGB || t == B200_TTF_BC1_RGB || t == B200_TTF_BC4_R || t == B200_TTF_ETC2_EAC_R11) ? 8u : 16u; }
 bool is_block_target(uint32_t t) { return t == B200_TTF_BC7_RGBA || t == B200_TTF_ASTC_4x4_RGBA || is_hinted_target(t); }
 
 int launch_hinted(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst, uint64_t n, cudaStream_t st,
@@ -861,13 +861,13 @@ int launch_hinted(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, co
   XtImage im{};
   im.kind = target;
   im.hq = (decode_flags & B200_DECODE_FLAG_HIGH_QUALITY) ? 1u : 0u;
-  im.chan0 = (target == B200_TTF_BC4_R && from_alpha) ? 3u : 0u;   // transcode_image, XC:10417-10438
+  im.chan0 = ((target == B200_TTF_BC4_R || target == B200_TTF_ETC2_EAC_R11) && from_alpha) ? 3u : 0u;   // transcode_image, XC:10417-10438, :10515
   im.chan1 = 3u;
   const uint64_t tiles = (n + xt_tile(3) - 1) / xt_tile(3);
   const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
-  switch (target) {
+  switch (target == B200_TTF_ETC2_EAC_R11 ? 6u : target == B200_TTF_ETC2_EAC_RG11 ? 7u : target) {
 #define XH_CASE(KIND) case KIND: k_transcode_tiled<3, KIND><<<grid, XT_THREADS, xt_smem_bytes(3), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im); break;
-    XH_CASE(0) XH_CASE(1) XH_CASE(2) XH_CASE(3) XH_CASE(4) XH_CASE(5)
+    XH_CASE(0) XH_CASE(1) XH_CASE(2) XH_CASE(3) XH_CASE(4) XH_CASE(5) XH_CASE(6) XH_CASE(7)
 #undef XH_CASE
   }
   g_launches++;
@@ -1100,6 +1100,8 @@ int b200_uastc_init(void) {
   CU(cudaFuncSetAttribute(k_transcode_tiled<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
   CU(cudaFuncSetAttribute(k_transcode_tiled<3, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
+  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
   g_ctx.ready = true;
   return B200_OK;
 }

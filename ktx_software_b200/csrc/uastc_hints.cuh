@@ -449,6 +449,7 @@ UB_FN void bc1_find_sels(const uint32_t* px, uint32_t lr, uint32_t lg, uint32_t 
   for (int i = 0; i < 4; i++) dots[i] = br[i] * ar + bg[i] * ag + bb[i] * ab;
   const int t0 = dots[0] + dots[1], t1 = dots[1] + dots[2], t2 = dots[2] + dots[3];
   ar *= 2; ag *= 2; ab *= 2;
+#pragma unroll 4
   for (uint32_t i = 0; i < 16; i++) {
     const int d = (int)ch(px[i], 0) * ar + (int)ch(px[i], 1) * ag + (int)ch(px[i], 2) * ab;
     sels[i] = (uint8_t)(3 - ((d <= t0) + (d < t1) + (d < t2)));
@@ -457,6 +458,7 @@ UB_FN void bc1_find_sels(const uint32_t* px, uint32_t lr, uint32_t lg, uint32_t 
 
 UB_FN bool bc1_least_squares(const uint32_t* px, const uint8_t* sels, float* xl, float* xh) {
   uint32_t q00[3] = {0, 0, 0}, tt[3] = {0, 0, 0}, wacc = 0;
+#pragma unroll 4
   for (uint32_t i = 0; i < 16; i++) {
     const uint32_t s = sels[i];
     wacc += (s == 0) ? 0x000009u : (s == 1) ? 0x010204u : (s == 2) ? 0x040201u : 0x090000u;
@@ -477,6 +479,7 @@ UB_FN bool bc1_least_squares(const uint32_t* px, const uint8_t* sels, float* xl,
   for (uint32_t c = 0; c < 3; c++)
     if (xl[c] < 0.0f || xh[c] > 255.0f) {
       uint32_t lo = 0xFFFFFFFFu, hi = 0;
+#pragma unroll 1
       for (uint32_t i = 0; i < 16; i++) { lo = minu(lo, ch(px[i], c)); hi = maxu(hi, ch(px[i], c)); }
       if (lo == hi) { xl[c] = (float)lo; xh[c] = (float)hi; }
     }
@@ -500,6 +503,8 @@ UB_FN Bc1Block bc1_solid(uint32_t fr, uint32_t fg, uint32_t fb) {
   return b;
 }
 
+// (The 16-texel loops are unrolled by 4, not fully: fully unrolled the function is 34 KB of SASS, more than the 32 KB
+// instruction cache, which the free-running warps of the BC1 / BC3 transcode kernels then thrash.)
 // encode_bc1 with flags 0 (have_sels = false) or cEncodeBC1UseSelectors (sels given, linear 0..3); ls_passes = 1, or 2 for
 // cEncodeBC1HighQuality (XC:17807)
 UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, uint32_t ls_passes = 1) {
@@ -511,10 +516,12 @@ UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, ui
     for (uint32_t j = 1; j < 16; j++) if ((px[j] & 0xFFFFFFu) != f0) { solid = false; break; }
     if (solid) return bc1_solid(ch(px[0], 0), ch(px[0], 1), ch(px[0], 2));
     int tot[3] = {0, 0, 0}, mx[3] = {0, 0, 0}, mn[3] = {255, 255, 255};
+#pragma unroll 4
     for (uint32_t i = 0; i < 16; i++)
       for (uint32_t c = 0; c < 3; c++) { const int v = (int)ch(px[i], c); tot[c] += v; if (v > mx[c]) mx[c] = v; if (v < mn[c]) mn[c] = v; }
     avg_r = (tot[0] + 8) >> 4; avg_g = (tot[1] + 8) >> 4; avg_b = (tot[2] + 8) >> 4;
     int icov[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll 4
     for (uint32_t i = 0; i < 16; i++) {
       const int r = (int)ch(px[i], 0) - avg_r, g = (int)ch(px[i], 1) - avg_g, b = (int)ch(px[i], 2) - avg_b;
       icov[0] += r * r; icov[1] += r * g; icov[2] += r * b; icov[3] += g * g; icov[4] += g * b; icov[5] += b * b;
@@ -535,6 +542,7 @@ UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, ui
     int sr = 306, sg = 601, sb = 117;
     if (k >= 2) { const float m = f_div(1024.0f, k); sr = (int)f_mul(xr, m); sg = (int)f_mul(xg, m); sb = (int)f_mul(xb, m); }
     int low_dot = 0x7FFFFFFF, high_dot = (int)0x80000000, low_c = 0, high_c = 0;
+#pragma unroll 4
     for (uint32_t i = 0; i < 16; i++) {
       const int dot = (int)ch(px[i], 0) * sr + (int)ch(px[i], 1) * sg + (int)ch(px[i], 2) * sb;
       if (dot < low_dot) { low_dot = dot; low_c = (int)i; }
@@ -549,6 +557,7 @@ UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, ui
     if (!bc1_least_squares(px, sels, xl, xh)) {
       if (avg_r < 0) {
         int tot[3] = {0, 0, 0};
+#pragma unroll 1
         for (uint32_t i = 0; i < 16; i++) for (uint32_t c = 0; c < 3; c++) tot[c] += (int)ch(px[i], c);
         avg_r = (tot[0] + 8) >> 4; avg_g = (tot[1] + 8) >> 4; avg_b = (tot[2] + 8) >> 4;
       }
@@ -573,6 +582,7 @@ UB_BIG Bc1Block encode_bc1(const uint32_t* px, bool have_sels, uint8_t* sels, ui
     uint32_t inv = 0;
     if (lc16 < hc16) { const uint32_t t = lc16; lc16 = hc16; hc16 = t; inv = 0x55555555u; }
     uint32_t packed = 0;
+#pragma unroll 4
     for (uint32_t i = 0; i < 16; i++) packed |= ((0x78u >> (2 * sels[i])) & 3u) << (i * 2);  // {0,2,3,1}
     b.lo16 = lc16; b.hi16 = hc16; b.sels = packed ^ inv;
   }

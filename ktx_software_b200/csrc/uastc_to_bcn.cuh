@@ -285,15 +285,87 @@ UB_FN uint64_t eac_a8_from_form(const HintedForm& h, const HintFields& hf, const
   return eac_a8_bytes((uint32_t)center, table, (uint32_t)mul, sels);
 }
 
-// Output bytes per block of a hinted target (0 = not one)
-UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind == 2 || kind == 4) ? 8u : (kind == 1 || kind == 3 || kind == 5) ? 16u : 0u; }
+// ---- ETC2 EAC R11 / RG11 (XC:18792-18850): pack_eac (:18515, four tables) or pack_eac_high_quality (:18672, all sixteen)
+// on one channel's 16 values; a solid block has multiplier 0 (pack_eac_solid_block :18503), unlike the A8 path's 1.
+UB_FN uint64_t eac_pack_values(const uint32_t* val, bool high_quality) {
+  const uint64_t SEL4 = 0x924924924924ull;
+  uint32_t mn = 255u, mx = 0u;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) { mn = minu(mn, val[i]); mx = maxu(mx, val[i]); }
+  if (mn == mx) return eac_a8_bytes(mn, 13, 0, SEL4);
+  const uint32_t arange = mx - mn;
+  if (arange <= 5u) {   // table 13 is lossless
+    const int base = clamp255((int)mx - 2);
+    uint64_t sels = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++) {
+      const uint32_t sel = (uint32_t)((int)val[i] - (base - 3));                    // 0..5
+      sels |= (uint64_t)((0x654012u >> (4 * sel)) & 7u) << (45 - 3 * ((i & 3u) * 4 + (i >> 2)));   // s_sels = {2,1,0,4,5,6}
+    }
+    return eac_a8_bytes((uint32_t)base, 13, 1, sels);
+  }
+  uint32_t best_err = 0xFFFFFFFFu, b_base = 0, b_mul = 0, b_table = 0;
+  uint64_t b_sels = 0;
+  const uint32_t n_tables = high_quality ? 16u : 4u;
+  for (uint32_t k = 0; k < n_tables; k++) {
+    const uint32_t table = high_quality ? k : ((0xDB82u >> (4 * k)) & 15u);   // {2, 8, 11, 13}
+    const int8_t* T = UBT(etc2_eac) + table * 8;
+    const float range = (float)((int)T[7] - (int)T[3]);
+    const float t = f_div((float)(0 - (int)T[3]), range);
+    const int base = clamp255((int)roundf(f_add((float)mn, f_mul(f_sub((float)mx, (float)mn), t))));
+    const int mul = clampi((int)roundf(f_div((float)arange, range)), 1, 15);
+    uint32_t err = 0;
+    uint64_t sels = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++) {
+      const int a = (int)val[i];
+      const bool clamped = high_quality || a < 7 || a > 255 - 7;   // pack_eac clamps the table values only near the ends (:18592-18636)
+      uint32_t l = 0xFFFFFFFFu;
+#pragma unroll
+      for (uint32_t sidx = 0; sidx < 8; sidx++) {
+        int v = mul * (int)T[sidx] + base;
+        if (clamped) v = clamp255(v);
+        int e = v - a;
+        if (e < 0) e = -e;
+        l = minu(l, ((uint32_t)e << 3) | sidx);
+      }
+      sels |= (uint64_t)(l & 7u) << (45 - 3 * ((i & 3u) * 4 + (i >> 2)));
+      err += (l >> 3) * (l >> 3);
+    }
+    if (err < best_err) { best_err = err; b_base = (uint32_t)base; b_mul = (uint32_t)mul; b_table = table; b_sels = sels; }
+  }
+  return eac_a8_bytes(b_base, b_table, b_mul, b_sels);
+}
 
-// The shared part.  kind = ktx_transcode_fmt_e (0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG);
-// chan0 / chan1: the channels BC4 / BC5 take (transcode_image, XC:10417-10438).  8-byte targets fill d.lo only.
+// one EAC block of transcode_uastc_to_etc2_eac_r11 / _rg11 for channel `chan`
+UB_FN uint64_t eac_r11_from_form(const HintedForm& h, const HintFields& hf, uint32_t chan, bool high_quality) {
+  if (h.mode == UASTC_MODE_SOLID) return eac_a8_bytes((h.solid >> (8 * chan)) & 255u, 13, 0, 0x924924924924ull);
+  if (chan == 3) {
+    uint32_t px[16];
+    texels_from_form(h.f, px);
+    return eac_a8_from_form(h, hf, px);
+  }
+  uint32_t v[16];
+  channel_from_form(h.f, chan, v);
+  return eac_pack_values(v, high_quality);
+}
+
+// Output bytes per block of a hinted target (0 = not one)
+UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind == 2 || kind == 4 || kind == 6) ? 8u : (kind == 1 || kind == 3 || kind == 5 || kind == 7) ? 16u : 0u; }
+
+// The shared part.  kind = ktx_transcode_fmt_e for 0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG, and
+// 6 = ETC2_EAC_R11, 7 = ETC2_EAC_RG11 (KTX_TTF 20 / 21); chan0 / chan1: the channels BC4 / BC5 / R11 / RG11 take
+// (transcode_image, XC:10417-10438, :10511-10527).  8-byte targets fill d.lo only.
 UB_FN void hinted_target_from_form(const HintedForm& h, uint32_t kind, bool high_quality, uint32_t chan0, uint32_t chan1, Bits128& d) {
   d.lo = 0; d.hi = 0;
   if (kind == 4) { d.lo = bc4_from_form(h.f, chan0); return; }
   if (kind == 5) { d.lo = bc4_from_form(h.f, chan0); d.hi = bc4_from_form(h.f, chan1); return; }
+  if (kind == 6 || kind == 7) {
+    const HintFields hf = parse_hints(h.mode, h.hints);
+    d.lo = eac_r11_from_form(h, hf, chan0, high_quality);
+    if (kind == 7) d.hi = eac_r11_from_form(h, hf, chan1, high_quality);
+    return;
+  }
   uint32_t px[16];
   texels_from_form(h.f, px);
   const HintFields hf = parse_hints(h.mode, h.hints);

@@ -11,7 +11,7 @@ oracle/_ref exist; the GPU box only reads the committed files).
                           payloads behind every mode prefix, invalid blocks) with the reference's BC7 / ASTC output.
   encode_golden.npz       source 4x4 blocks + the reference encoder's output at levels 0-3 (small set).
   hinted_golden.npz       (`make_golden.py hinted`) reference output of the hint-driven targets ETC1_RGB, ETC2_RGBA, BC1_RGB,
-                          BC3_RGBA, BC4_R, BC5_RG (+ high-quality BC1 / BC3, BC4 from alpha) for every second block of
+                          BC3_RGBA, BC4_R, BC5_RG, ETC2_EAC_R11 / RG11 (+ high-quality BC1 / BC3 / R11 / RG11, BC4 / R11 from alpha) for every second block of
                           transcode_golden.npz that the reference's ETC2 path accepts (`index` = positions in its `uastc`).
 """
 import json, os, struct, sys
@@ -92,12 +92,15 @@ def make_hinted():
     index = np.nonzero(R.etc2_transcodable(u))[0][::2].astype(np.uint32)
     b = u[index]
     out = {"index": index}
-    for name, tf in [("etc1", 0), ("etc2", 1), ("bc1", 2), ("bc3", 3), ("bc4", 4), ("bc5", 5)]:
+    for name, tf in [("etc1", 0), ("etc2", 1), ("bc1", 2), ("bc3", 3), ("bc4", 4), ("bc5", 5), ("r11", 20), ("rg11", 21)]:
         out[name], ok = R.ref_transcode_hinted(b, tf)
         assert ok
     out["bc1_hq"] = R.ref_transcode_hinted(b, 2, 32)[0]
     out["bc3_hq"] = R.ref_transcode_hinted(b, 3, 32)[0]
     out["bc4_alpha"] = R.ref_transcode_hinted(b, 4, 4, True)[0]
+    out["r11_hq"] = R.ref_transcode_hinted(b, 20, 32)[0]
+    out["rg11_hq"] = R.ref_transcode_hinted(b, 21, 32)[0]
+    out["r11_alpha"] = R.ref_transcode_hinted(b, 20, 4, True)[0]
     np.savez_compressed(os.path.join(HERE, "hinted_golden.npz"), **out)
     print("hinted corpus:", b.shape, "modes:", np.bincount(R.block_modes(b), minlength=19))
 

@@ -99,7 +99,7 @@ def ref_transcode_image(blocks, w, h, tf):
     return out, rc == 0
 
 
-HINTED_TARGET_BYTES = {0: 8, 1: 16, 2: 8, 3: 16, 4: 8, 5: 16}   # ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R, BC5_RG
+HINTED_TARGET_BYTES = {0: 8, 1: 16, 2: 8, 3: 16, 4: 8, 5: 16, 20: 8, 21: 16}   # ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R, BC5_RG, ETC2_EAC_R11, _RG11
 
 
 def ref_transcode_hinted(blocks, tf, decode_flags=0, has_alpha=True):
@@ -122,8 +122,9 @@ def port_transcode_hinted(blocks, tf, decode_flags=0, has_alpha=True):
     f.restype = ctypes.c_int64
     f.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, _u8p]
     out = np.zeros((blocks.shape[0], HINTED_TARGET_BYTES[tf]), np.uint8)
-    chan0 = 3 if (tf == 4 and has_alpha and (decode_flags & 4)) else 0
-    bad = f(_p(blocks), blocks.shape[0], tf, 1 if (decode_flags & 32) else 0, chan0, 3, _p(out))
+    chan0 = 3 if (tf in (4, 20) and has_alpha and (decode_flags & 4)) else 0
+    kind = {20: 6, 21: 7}.get(tf, tf)
+    bad = f(_p(blocks), blocks.shape[0], kind, 1 if (decode_flags & 32) else 0, chan0, 3, _p(out))
     return out, bad
 
 

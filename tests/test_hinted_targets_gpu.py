@@ -1,4 +1,4 @@
-"""GPU parity tests for the hint-driven transcode targets (KTX_TTF_ETC1_RGB / ETC2_RGBA / BC1_RGB / BC3_RGBA / BC4_R / BC5_RG)
+"""GPU parity tests for the hint-driven transcode targets (KTX_TTF_ETC1_RGB / ETC2_RGBA / BC1_RGB / BC3_RGBA / BC4_R / BC5_RG / ETC2_EAC_R11 / ETC2_EAC_RG11)
 through the C ABI (b200_uastc_transcode_ex, b200_uastc_transcode_dev_ex).  SURVEY 8(f).2; bar: bit-exact with the
 reference's transcode_image -> transcode_slice (XC/basisu_transcoder.cpp:10141-10180) -> transcode_uastc_to_etc1 /
 _etc2_rgba / _bc1 / _bc3 / _bc4 / _bc5, including the high-quality and alpha-to-opaque decode flags."""
@@ -10,7 +10,7 @@ import refutil as R
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 needs_ref = pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not shipped")
-NAMES = {0: "etc1", 1: "etc2", 2: "bc1", 3: "bc3", 4: "bc4", 5: "bc5"}
+NAMES = {0: "etc1", 1: "etc2", 2: "bc1", 3: "bc3", 4: "bc4", 5: "bc5", 20: "r11", 21: "rg11"}
 
 
 @pytest.fixture(scope="module")
@@ -38,7 +38,10 @@ def test_decode_flags_on_golden_corpus(K, gold):
     u, h, _ = gold
     assert (K.transcode(u, K.TTF_BC1_RGB, decode_flags=K.TF_HIGH_QUALITY).reshape(-1, 8) == h["bc1_hq"]).all()
     assert (K.transcode(u, K.TTF_BC3_RGBA, decode_flags=K.TF_HIGH_QUALITY).reshape(-1, 16) == h["bc3_hq"]).all()
+    assert (K.transcode(u, K.TTF_ETC2_EAC_R11, decode_flags=K.TF_HIGH_QUALITY).reshape(-1, 8) == h["r11_hq"]).all()
+    assert (K.transcode(u, K.TTF_ETC2_EAC_RG11, decode_flags=K.TF_HIGH_QUALITY).reshape(-1, 16) == h["rg11_hq"]).all()
     a2o = K.TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS
+    assert (K.transcode(u, K.TTF_ETC2_EAC_R11, decode_flags=a2o, has_alpha=True).reshape(-1, 8) == h["r11_alpha"]).all()
     assert (K.transcode(u, K.TTF_BC4_R, decode_flags=a2o, has_alpha=True).reshape(-1, 8) == h["bc4_alpha"]).all()
     # without alpha content the flag changes nothing (XC:10417)
     assert (K.transcode(u, K.TTF_BC4_R, decode_flags=a2o, has_alpha=False).reshape(-1, 8) == h["bc4"]).all()

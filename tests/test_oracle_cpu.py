@@ -250,7 +250,7 @@ def test_port_decode_image_targets_vs_reference(w, h):
 
 
 # ---- the hint-driven targets (ETC1_RGB, ETC2_RGBA, BC1_RGB, BC3_RGBA, BC4_R, BC5_RG): SURVEY 8(f).2
-HINTED = {0: "etc1", 1: "etc2", 2: "bc1", 3: "bc3", 4: "bc4", 5: "bc5"}
+HINTED = {0: "etc1", 1: "etc2", 2: "bc1", 3: "bc3", 4: "bc4", 5: "bc5", 20: "r11", 21: "rg11"}
 
 
 @pytest.mark.parametrize("tf", sorted(HINTED))
@@ -260,8 +260,10 @@ def test_port_hinted_targets_golden_corpus(tf):
     u = g["uastc"][h["index"]]
     got, bad = R.port_transcode_hinted(u, tf)
     assert bad == -1 and (got == h[HINTED[tf]]).all()
-    if tf in (2, 3):
+    if tf in (2, 3, 20, 21):
         assert (R.port_transcode_hinted(u, tf, 32)[0] == h[HINTED[tf] + "_hq"]).all()
+    if tf == 20:
+        assert (R.port_transcode_hinted(u, tf, 4, True)[0] == h["r11_alpha"]).all()
     if tf == 4:
         assert (R.port_transcode_hinted(u, tf, 4, True)[0] == h["bc4_alpha"]).all()
         assert (R.port_transcode_hinted(u, tf, 4, False)[0] == h["bc4"]).all()
