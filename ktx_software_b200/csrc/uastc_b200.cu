@@ -240,11 +240,12 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
   constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4 || KIND == 6);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
-  uint16_t* s_order = (uint16_t*)(s_hist + 64);
   // BC1 / BC3: the cost of a block is set by which BC1 path its hint bits select (hint0: endpoints + weights as they are;
   // hint1: one least-squares fit on the block's weights; none: the full encode_bc1), so the bins are (path, mode) pairs --
   // 3 x 19 of them, scanned as two bins per lane -- and a warp runs one path of one mode.
   constexpr bool WIDE = TARGET == 3 && (KIND == 2 || KIND == 3);
+  constexpr uint32_t NBINS = WIDE ? 64 : 32;
+  uint16_t* s_order = (uint16_t*)(s_hist + NBINS);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
   const uint64_t n_tiles = (n_blocks + TILE - 1) / TILE;
@@ -252,7 +253,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   if (tile >= n_tiles) return;
   auto tile_count = [&](uint64_t t) { return (uint32_t)min((uint64_t)TILE, n_blocks - t * TILE); };
 
-  if (tid < 64) s_hist[tid] = 0;
+  if (tid < NBINS) s_hist[tid] = 0;
   if (XT_SMEM_TABLES) ub::shared_tables_load(tid, XT_THREADS);
   if (tid == 0) {
     mbar_init(&s_bar[0], 1);
@@ -327,12 +328,12 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 #pragma unroll
     for (int k = 0; k < PER_THREAD; k++) {
       const uint32_t i = tid + k * XT_THREADS;
-      uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, my_mode[k] & 31u);
+      uint32_t start = __shfl_sync(0xFFFFFFFFu, bin_start, WIDE ? (my_mode[k] & 31u) : my_mode[k]);
       if (WIDE) { const uint32_t hi = __shfl_sync(0xFFFFFFFFu, bin_start_hi, my_mode[k] & 31u); if (my_mode[k] >= 32u) start = hi; }
       if (i < cnt) s_order[start + my_rank[k]] = (uint16_t)i;
     }
     __syncthreads();
-    if (tid < 64) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
+    if (tid < NBINS) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
 #pragma unroll 1
