@@ -78,6 +78,9 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
 #ifndef XT_SMEM_TABLES
 #define XT_SMEM_TABLES true   // endpoint-unquantisation and p-bit tables are read from a per-CTA shared-memory copy
 #endif
+#ifndef XT_DYNAMIC
+#define XT_DYNAMIC 1   // transcode phase: warps claim 32-block runs of the sorted tile dynamically (0: fixed share per warp)
+#endif
 #ifndef XT_CTAS_PER_SM
 #define XT_CTAS_PER_SM 1
 #endif
@@ -154,7 +157,7 @@ __host__ __device__ constexpr int xt_tile(int target) { return (target == 2 && X
 __host__ __device__ constexpr int xt_data_tiles(int target) { return (target == 2 && XT_DECODE_STAGED) ? 6 : 2; }
 // TARGET 3 adds a TILE x 8-byte output tile for the 8-byte targets (their results cannot overwrite the 16-byte input slots)
 __host__ __device__ constexpr size_t xt_data_bytes(int target) { return (size_t)xt_data_tiles(target) * xt_tile(target) * 16 + (target == 3 ? (size_t)xt_tile(target) * 8 : 0); }
-constexpr size_t xt_smem_bytes(int target) { return xt_data_bytes(target) + 2 * 8 + 64 * 4 + (size_t)xt_tile(target) * 2; }
+constexpr size_t xt_smem_bytes(int target) { return xt_data_bytes(target) + 2 * 8 + 72 * 4 + (size_t)xt_tile(target) * 2; }
 
 __device__ __forceinline__ void store_block_texels(uint8_t* __restrict__ dst, const XtImage& im, uint64_t block_index, const uint32_t* px) {
   const uint32_t by = (uint32_t)(block_index / im.bx), bxi = (uint32_t)(block_index - (uint64_t)by * im.bx);
@@ -245,7 +248,8 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   // 3 x 19 of them, scanned as two bins per lane -- and a warp runs one path of one mode.
   constexpr bool WIDE = TARGET == 3 && (KIND == 2 || KIND == 3);
   constexpr uint32_t NBINS = WIDE ? 64 : 32;
-  uint16_t* s_order = (uint16_t*)(s_hist + NBINS);
+  uint32_t* s_next = s_hist + NBINS;                    // next unclaimed position of the sorted tile (see the transcode loop)
+  uint16_t* s_order = (uint16_t*)(s_hist + NBINS + 2);
 
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
   const uint64_t n_tiles = (n_blocks + TILE - 1) / TILE;
@@ -278,6 +282,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
       }
     }
+    if (XT_DYNAMIC && tid == 32) *s_next = 0;        // (every warp left the previous tile's loop at the barrier that ended it)
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
 
@@ -336,9 +341,18 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     if (tid < NBINS) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
+    // Warps claim runs of 32 sorted positions from a shared counter instead of a fixed share: modes differ several-fold in
+    // cost, and with a fixed share every warp waits at the tile's last barrier for the one that drew the expensive bins.
 #pragma unroll 1
-    for (int k = 0; k < PER_THREAD; k++) {
-      const uint32_t j = tid + k * XT_THREADS;
+    for (int k = 0; XT_DYNAMIC || k < PER_THREAD; k++) {
+      uint32_t j = tid + k * XT_THREADS;
+      if (XT_DYNAMIC) {
+        uint32_t c = 0;
+        if (lane == 0) c = atomicAdd(s_next, 32u);
+        c = __shfl_sync(0xFFFFFFFFu, c, 0);
+        if (c >= cnt) break;
+        j = c + lane;
+      }
       if (j < cnt) {
         const uint32_t idx = s_order[j];
         const uint4 v = s_in[buf][idx];
