@@ -275,10 +275,10 @@ def run_c5(args):
     # The other block targets on a 2^24-block slice of the same input, device-resident, with the reference
     # transcoder timed beside each on a bounded sample.  bytes = 16 read + 8 or 16 written per block.
     targets = {}
-    if rank == 0:
+    if rank == 0 and world == 1:   # (single-GPU runs only: the other ranks of a multi-GPU run would idle behind rank 0 here)
         nt = min(n, 1 << 24)
         names = [("astc", K.TTF_ASTC_4x4_RGBA), ("bc1", K.TTF_BC1_RGB), ("bc3", K.TTF_BC3_RGBA), ("bc4", K.TTF_BC4_R), ("bc5", K.TTF_BC5_RG),
-                 ("etc1", K.TTF_ETC1_RGB), ("etc2", K.TTF_ETC2_RGBA)]
+                 ("etc1", K.TTF_ETC1_RGB), ("etc2", K.TTF_ETC2_RGBA), ("eac_r11", K.TTF_ETC2_EAC_R11), ("eac_rg11", K.TTF_ETC2_EAC_RG11)]
         for name, tf in names:
             ob = K.target_block_bytes(tf)
             for _ in range(2):

@@ -10,6 +10,8 @@ g = np.load(os.path.join(os.path.dirname(__file__), "..", "tests", "golden", "tr
 u = g["uastc"][:16384]
 n = 1 << 26
 rep = torch.from_numpy(np.tile(u, (n // u.shape[0], 1))).cuda()
+if "shuffled" in sys.argv[1:]:   # every tile sees the corpus' whole mode mix (as bench.py's C5 input does)
+    rep = rep[torch.randperm(n, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))].contiguous()
 dst = torch.empty_like(rep)
 st = torch.cuda.current_stream().cuda_stream
 for tf, name in [(6, "bc7"), (10, "astc")]:
@@ -22,4 +24,4 @@ for tf, name in [(6, "bc7"), (10, "astc")]:
         L.b200_uastc_transcode_dev(tf, rep.data_ptr(), dst.data_ptr(), n, st, None)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 10
-    print("%s %-5s %7.3f ms  %7.1f GB/s" % (os.path.basename(path), name, ms, n * 32 / ms / 1e6))
+    print(("shuffled " if "shuffled" in sys.argv[1:] else "") + "%s %-5s %7.3f ms  %7.1f GB/s" % (os.path.basename(path), name, ms, n * 32 / ms / 1e6))
