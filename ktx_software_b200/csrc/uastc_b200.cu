@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
       }
     }
-    if (XT_DYNAMIC && tid == 32) *s_next = 0;        // (every warp left the previous tile's loop at the barrier that ended it)
+    if (XT_DYNAMIC && tid == 32) *s_next = XT_THREADS;   // every warp's first run is its own: claims start behind those        // (every warp left the previous tile's loop at the barrier that ended it)
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
 
@@ -343,15 +343,17 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
     // Warps claim runs of 32 sorted positions from a shared counter instead of a fixed share: modes differ several-fold in
     // cost, and with a fixed share every warp waits at the tile's last barrier for the one that drew the expensive bins.
+    // The claim for the run after this one is issued before this run is processed, so the shared-memory atomic's latency
+    // hides behind the work instead of heading every run.
+    uint32_t claimed = tid & ~31u;
 #pragma unroll 1
     for (int k = 0; XT_DYNAMIC || k < PER_THREAD; k++) {
       uint32_t j = tid + k * XT_THREADS;
+      uint32_t nxt = 0;
       if (XT_DYNAMIC) {
-        uint32_t c = 0;
-        if (lane == 0) c = atomicAdd(s_next, 32u);
-        c = __shfl_sync(0xFFFFFFFFu, c, 0);
-        if (c >= cnt) break;
-        j = c + lane;
+        if (claimed >= cnt) break;
+        if (lane == 0) nxt = atomicAdd(s_next, 32u);
+        j = claimed + lane;
       }
       if (j < cnt) {
         const uint32_t idx = s_order[j];
@@ -395,6 +397,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         }
         if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)(tile * TILE + idx));
       }
+      if (XT_DYNAMIC) claimed = __shfl_sync(0xFFFFFFFFu, nxt, 0);
     }
     if (TARGET != 2) fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
     __syncthreads();
