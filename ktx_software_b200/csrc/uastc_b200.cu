@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src
 #define XT_SMEM_TABLES true   // endpoint-unquantisation and p-bit tables are read from a per-CTA shared-memory copy
 #endif
 #ifndef XT_DYNAMIC
-#define XT_DYNAMIC 1   // transcode phase: warps claim 32-block runs of the sorted tile dynamically (0: fixed share per warp)
+#define XT_DYNAMIC 1   // hint-driven targets: warps claim 32-block runs of the sorted tile dynamically (0: fixed share per warp)
 #endif
 #ifndef XT_CTAS_PER_SM
 #define XT_CTAS_PER_SM 1
@@ -248,6 +248,12 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
   // 3 x 19 of them, scanned as two bins per lane -- and a warp runs one path of one mode.
   constexpr bool WIDE = TARGET == 3 && (KIND == 2 || KIND == 3);
   constexpr uint32_t NBINS = WIDE ? 64 : 32;
+  // Dynamic claiming of the sorted tile (see the transcode loop) for the hint-driven targets only.  Same-box A/B on BC7
+  // (tools/ab_xcode.py, bench.py --workload c5; profiles/r3d_ab_claiming.txt): +5..12 % on image-ordered input (tiles whose
+  // bins differ in size: C2's blocks, the golden corpus) but -6 % on C5's i.i.d. block mix, where every round of a fixed
+  // share is homogeneous already; a variant that claims only the last of four rounds loses the same 6 % there, so the cost
+  // is the claim loop's code, not the schedule.  BC7 / ASTC / texels keep the fixed share until that is understood.
+  constexpr bool DYN = XT_DYNAMIC && TARGET == 3;
   uint32_t* s_next = s_hist + NBINS;                    // next unclaimed position of the sorted tile (see the transcode loop)
   uint16_t* s_order = (uint16_t*)(s_hist + NBINS + 2);
 
@@ -282,7 +288,7 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
       }
     }
-    if (XT_DYNAMIC && tid == 32) *s_next = XT_THREADS;   // every warp's first run is its own: claims start behind those        // (every warp left the previous tile's loop at the barrier that ended it)
+    if (DYN && tid == 32) *s_next = 0;   // (every warp left the previous tile's loop at the barrier that ended it)
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
 
@@ -343,17 +349,15 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)
     // Warps claim runs of 32 sorted positions from a shared counter instead of a fixed share: modes differ several-fold in
     // cost, and with a fixed share every warp waits at the tile's last barrier for the one that drew the expensive bins.
-    // The claim for the run after this one is issued before this run is processed, so the shared-memory atomic's latency
-    // hides behind the work instead of heading every run.
-    uint32_t claimed = tid & ~31u;
 #pragma unroll 1
-    for (int k = 0; XT_DYNAMIC || k < PER_THREAD; k++) {
+    for (int k = 0; DYN || k < PER_THREAD; k++) {
       uint32_t j = tid + k * XT_THREADS;
-      uint32_t nxt = 0;
-      if (XT_DYNAMIC) {
-        if (claimed >= cnt) break;
-        if (lane == 0) nxt = atomicAdd(s_next, 32u);
-        j = claimed + lane;
+      if (DYN) {
+        uint32_t c = 0;
+        if (lane == 0) c = atomicAdd(s_next, 32u);
+        c = __shfl_sync(0xFFFFFFFFu, c, 0);
+        if (c >= cnt) break;
+        j = c + lane;
       }
       if (j < cnt) {
         const uint32_t idx = s_order[j];
@@ -397,7 +401,6 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
         }
         if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)(tile * TILE + idx));
       }
-      if (XT_DYNAMIC) claimed = __shfl_sync(0xFFFFFFFFu, nxt, 0);
     }
     if (TARGET != 2) fence_proxy_async();  // make the generic-proxy writes of the tile visible to the bulk-copy engine
     __syncthreads();
