@@ -366,9 +366,16 @@ UB_FN void hinted_target_from_form(const HintedForm& h, uint32_t kind, bool high
     if (kind == 7) d.hi = eac_r11_from_form(h, hf, chan1, high_quality);
     return;
   }
+  const HintFields hf = parse_hints(h.mode, h.hints);
+  if (kind == 2 && !high_quality && hf.bc1_hint0) {
+    // hint0: the colour block comes from the endpoints and weights as they are -- no texels needed (BC1 1.80 -> 1.65 ms per
+    // 2^24 blocks of C5).  (The same shortcut for BC3, with the alpha channel alone interpolated for its BC4 half, measured
+    // slower: 2.09 -> 2.96 ms; BC3 keeps the full interpolation.)
+    d.lo = bc1_bytes(bc1_from_hint0(h));
+    return;
+  }
   uint32_t px[16];
   texels_from_form(h.f, px);
-  const HintFields hf = parse_hints(h.mode, h.hints);
   switch (kind) {
     case 0: d.lo = etc1_from_form(h, hf, px); break;
     case 1: d.lo = eac_a8_from_form(h, hf, px); d.hi = etc1_from_form(h, hf, px); break;
