@@ -5,7 +5,10 @@
  * Each entry point names the reference interface it replaces (paths relative to the KTX-Software checkout;
  * ENC/ = external/basis_universal/encoder/, XC/ = external/basis_universal/transcoder/).
  *
- * Threading: every call is re-entrant; calls from different host threads run on different CUDA streams.
+ * Threading: every call is re-entrant; each in-flight call owns its CUDA streams and staging buffers (a lane from a per-device pool).
+ * Alignment: device pointers to blocks (UASTC in, any block target out, 64-byte texel blocks) must be 16-byte aligned
+ * (B200_E_INVALID_VALUE otherwise: the kernels move them with 16-byte vector and bulk-copy accesses); image pointers may have any
+ * 4-byte alignment and any pitch -- rows that are not 16-byte aligned take a narrower load path.
  * Errors: 0 = success; negative = B200_E_* below; b200_uastc_last_error() returns a thread-local message.
  * There is NO CPU fallback: if no sm_100 device is usable the calls fail with B200_E_NO_DEVICE.
  */
@@ -52,7 +55,15 @@ extern "C" {
  * (lib/src/basis_transcode.cpp:427-436).  Idempotent and thread-safe.  Selects the current CUDA device
  * of the calling thread (or device 0), creates the stream pool. */
 int b200_uastc_init(void);
+/* Frees every idle stream set and staging buffer of every device; calls still in flight on other threads finish normally. */
 void b200_uastc_shutdown(void);
+/* Devices the HOST-buffer entry points (b200_uastc_encode*, b200_uastc_transcode*, b200_uastc_decode) spread a call over: bit d =
+ * CUDA device ordinal d (d < 16).  0 (the default) = the calling thread's current device.  Replaces the reference's
+ * ktxBasisParams::threadCount / job pool as the "how wide" knob (lib/src/basis_encode.cpp:1017-1029, ENC/basisu_comp.cpp:1503).
+ * Every named device must be sm_100 (B200_E_NO_DEVICE otherwise).  Process-wide, thread-safe. */
+int b200_uastc_set_devices(uint64_t device_mask);
+/* Number of CUDA devices this library can run on (sm_100 class). */
+int b200_uastc_device_count(void);
 const char* b200_uastc_last_error(void);
 /* Number of kernel launches this library has issued since init (bench.py's gpu_launches). */
 uint64_t b200_uastc_launch_count(void);
@@ -89,7 +100,7 @@ int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, ui
  * alpha instead of red when has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE are set (XC:10417, :10515); BC5_RG and
  * ETC2_EAC_RG11 take red and alpha (XC:10430, :10526).  Not accelerated
  * (B200_E_INVALID_VALUE, the glue keeps the stock path): ETC1_RGB from the alpha channel.  Device pointers must be
- * 16-byte aligned. */
+ * 16-byte aligned (B200_E_INVALID_VALUE otherwise). */
 int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans,
                             uint32_t n_spans, const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span);
 int b200_uastc_transcode_dev_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst,
@@ -139,7 +150,12 @@ typedef struct b200_uastc_params {
   float rdo_max_smooth_block_error_scale; /* 0 -> 10 */
   float rdo_max_smooth_block_std_dev;     /* 0 -> 18 */
   uint32_t rdo_total_jobs;   /* min(4, threadCount) as ENC/basisu_comp.cpp:1574-1576; 0/1 = one serial chain */
-  uint32_t reserved[4];
+  uint32_t device_mask;      /* bit d = use CUDA device d for this call; 0 = the set of b200_uastc_set_devices, else the calling
+                              * thread's current device.  The call's images are cut into block-row slabs and spread over the
+                              * devices the way the reference spreads 256-block jobs over its pool (ENC/basisu_comp.cpp:1503-1509);
+                              * with rdo_enable whole images are spread (a job range never crosses an image, :1574-1576).
+                              * Every device writes its slabs straight into out_blocks: the output bytes do not depend on the mask. */
+  uint32_t reserved[3];
 } b200_uastc_params;
 
 /* Replaces basis_compressor::process -> encode_slices_to_uastc_4x4_ldr (ENC/basisu_comp.cpp:1474-1591) and the

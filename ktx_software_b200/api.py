@@ -21,7 +21,8 @@ def target_block_bytes(target):
 EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_error", "b200_uastc_launch_count",
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
-                    "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex"]
+                    "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex",
+                    "b200_uastc_set_devices", "b200_uastc_device_count"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -57,7 +58,7 @@ class UastcParams(ctypes.Structure):
     _fields_ = [("struct_size", ctypes.c_uint32), ("pack_flags", ctypes.c_uint32), ("rdo_enable", ctypes.c_uint32),
                 ("rdo_lambda", ctypes.c_float), ("rdo_dict_size", ctypes.c_uint32),
                 ("rdo_max_smooth_block_error_scale", ctypes.c_float), ("rdo_max_smooth_block_std_dev", ctypes.c_float),
-                ("rdo_total_jobs", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 4)]
+                ("rdo_total_jobs", ctypes.c_uint32), ("device_mask", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 3)]
 
 
 _lib = None
@@ -72,6 +73,7 @@ def lib():
         l = ctypes.CDLL(LIB_PATH)
         l.b200_uastc_last_error.restype = ctypes.c_char_p
         l.b200_uastc_launch_count.restype = ctypes.c_uint64
+        l.b200_uastc_set_devices.argtypes = [ctypes.c_uint64]
         l.b200_uastc_transcode.argtypes = [ctypes.c_uint32, ctypes.POINTER(XcodeSpan), ctypes.c_uint32, ctypes.c_void_p,
                                            ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
         l.b200_uastc_transcode_dev.argtypes = [ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
@@ -108,6 +110,19 @@ def init():
 
 def launch_count():
     return int(lib().b200_uastc_launch_count())
+
+
+def set_devices(device_mask):
+    """Devices the host-buffer calls spread over (bit d = CUDA device d); 0 = the calling thread's current device."""
+    _check(lib().b200_uastc_set_devices(device_mask))
+
+
+def device_count():
+    return int(lib().b200_uastc_device_count())
+
+
+def shutdown():
+    lib().b200_uastc_shutdown()
 
 
 def transcode(src, target, spans=None, dst=None, decode_flags=None, has_alpha=True):
@@ -193,7 +208,7 @@ def encode_images_dev(images, pack_flags, stream=0, d_any_alpha=0):
     _check(lib().b200_uastc_encode_images_dev(arr, len(images), pack_flags, stream or None, d_any_alpha or None))
 
 
-def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale=0.0, smooth_std_dev=0.0, total_jobs=0):
+def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale=0.0, smooth_std_dev=0.0, total_jobs=0, device_mask=0):
     p = UastcParams()
     p.struct_size = ctypes.sizeof(UastcParams)
     p.pack_flags = pack_flags
@@ -203,6 +218,7 @@ def make_params(pack_flags, rdo=False, rdo_lambda=0.0, dict_size=0, smooth_scale
     p.rdo_max_smooth_block_error_scale = smooth_scale
     p.rdo_max_smooth_block_std_dev = smooth_std_dev
     p.rdo_total_jobs = total_jobs
+    p.device_mask = device_mask
     return p
 
 

@@ -1,14 +1,16 @@
 // uastc_b200.cu -- CUDA kernels (sm_100a) and the C ABI declared in include/ktx_b200_uastc.h.
 //
-// Transcode (reference hot loop #3, XC/basisu_transcoder.cpp:10128-10305): one thread per 16-byte block,
-// 128-bit coalesced loads/stores, grid sized in whole waves of the SM count, grid-stride over the span.
-// Host variant: the spans are cut into slabs that stream H2D -> kernel -> D2H through a ring of device
-// buffers on three streams so PCIe in, compute and PCIe out overlap.
+// Kernels: k_transcode_tiled (reference hot loop #3, XC/basisu_transcoder.cpp:10128-10305: persistent CTAs, TMA bulk tiles,
+// blocks binned by UASTC mode in shared memory), k_encode_image(s) / k_encode_blocks (hot loop #1, ENC/basisu_comp.cpp:1519-1562
+// -> encode_uastc), k_rdo_* (hot loop #2, ENC/basisu_uastc_enc.cpp:3825-4165), k_mip_down (2x2 box filter for the device-resident
+// mip chain).  The host side (device contexts, lane pool, multi-device planner, slab pipelines that stream
+// H2D -> kernel -> D2H through a ring of device buffers on three streams) is in uastc_host.inc.
 #include <cuda_runtime.h>
 #include <atomic>
 #include <mutex>
 #include <string>
 #include <vector>
+#include <thread>
 #include <algorithm>
 #include <stdio.h>
 
@@ -32,33 +34,8 @@ int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
 }
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(e_ == cudaErrorMemoryAllocation ? B200_E_OUT_OF_MEMORY : B200_E_CUDA, #call, e_); } while (0)
 
-struct DeviceCtx {
-  int device = -1;
-  int sm_count = 0;
-  bool ready = false;
-};
-std::mutex g_mu;
-DeviceCtx g_ctx;
-
 // ---------------------------------------------------------------------------------------------------------
 // kernels
-
-template <int TARGET>  // 0 = BC7, 1 = ASTC
-__global__ void __launch_bounds__(256) k_transcode(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
-                                                   unsigned long long* __restrict__ first_bad) {
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_blocks; i += stride) {
-    const uint4 v = __ldg(src + i);
-    ub::Bits128 s, d;
-    s.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
-    s.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
-    const bool ok = TARGET ? ub::transcode_block_to_astc(s, d) : ub::transcode_block_to_bc7(s, d);
-    uint4 o;
-    o.x = (uint32_t)d.lo; o.y = (uint32_t)(d.lo >> 32); o.z = (uint32_t)d.hi; o.w = (uint32_t)(d.hi >> 32);
-    dst[i] = o;
-    if (!ok && first_bad) atomicMin(first_bad, (unsigned long long)i);
-  }
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // Tiled transcode: the streaming kernel.  A CTA owns tiles of XT_TILE consecutive blocks (16 KB in, 16 KB out).
@@ -430,9 +407,6 @@ __global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __r
 #ifndef ENC_FINE_SYNC
 #define ENC_FINE_SYNC true  // barriers between the per-mode stages inside candidate generation, not only between the phases
 #endif
-#ifndef ENC_FINE_SYNC
-#define ENC_FINE_SYNC true  // barriers between the per-mode stages inside candidate generation, not only between the phases
-#endif
 #ifndef ENC_MIN_CTAS
 #define ENC_MIN_CTAS 1    // resident encode CTAs per SM (register cap = 65536 / (ENC_THREADS * ENC_MIN_CTAS))
 #endif
@@ -503,10 +477,11 @@ __device__ __forceinline__ void encode_phased(uint64_t n, uint32_t flags, uint4*
 template <int MAXC>
 __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_image(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
                                                       uint4* __restrict__ out, uint32_t bx, uint32_t by, uint32_t flags,
-                                                      unsigned int* __restrict__ any_alpha) {
+                                                      unsigned int* __restrict__ any_alpha, uint32_t vec_ok) {
+  // vec_ok: base and pitch are 16-byte aligned (host-checked), so whole blocks load as four 16-byte rows
   encode_phased<MAXC>((uint64_t)bx * by, flags, out, [&](uint64_t i, uint32_t* px) {
     const uint32_t x0 = (uint32_t)(i % bx) * 4, y0 = (uint32_t)(i / bx) * 4;
-    if (x0 + 4 <= w && y0 + 4 <= h && !(pitch & 15u)) {
+    if (vec_ok && x0 + 4 <= w && y0 + 4 <= h) {
 #pragma unroll
       for (uint32_t y = 0; y < 4; y++) {
         const uint4 v = __ldg((const uint4*)(img + (size_t)(y0 + y) * pitch + (size_t)x0 * 4));
@@ -536,9 +511,16 @@ struct EncImageDesc {
   uint64_t first_block;
 };
 
-template <int MAXC>
-__global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_images(const EncImageDesc* __restrict__ descs, uint32_t n_images, uint64_t total_blocks,
+// Up to ENC_PACK_MAX descriptors travel by value in the kernel's parameter block (a mip chain has <= 16 levels): the launch
+// then needs no device allocation and no copy.  Longer lists (cube map arrays) come from a device table.
+const uint32_t ENC_PACK_MAX = 32;
+struct EncDescPack { EncImageDesc d[ENC_PACK_MAX]; };
+
+template <int MAXC, bool PACKED>
+__global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_images(const __grid_constant__ EncDescPack pack, const EncImageDesc* __restrict__ d_descs,
+                                                                             uint32_t n_images, uint64_t total_blocks,
                                                                              uint32_t flags, unsigned int* __restrict__ any_alpha) {
+  const EncImageDesc* descs = PACKED ? pack.d : d_descs;
   ub::Candidate cands[MAXC];
   uint64_t overall[MAXC];
   float uerr[MAXC];
@@ -598,7 +580,7 @@ struct RdoChain {
   uint32_t first, last;      // job range [first, last) in the concatenated block array
   uint64_t hist_off;         // first entry of this chain's selector history
   uint32_t hist_mask;
-  uint32_t pad;
+  uint32_t slot_off;         // first table slot of this chain: prefix sum of min(length, RDO_CHUNK) over the chains before it
 };
 const int RDO_THREADS = 288;       // 256 trial threads + one warp that prepares the current block
 const uint32_t RDO_CHUNK = 8192;   // steps per launch
@@ -655,14 +637,16 @@ __device__ __forceinline__ uint4 from_bits(const ub::Bits128& b) {
   return make_uint4((uint32_t)b.lo, (uint32_t)(b.lo >> 32), (uint32_t)b.hi, (uint32_t)(b.hi >> 32));
 }
 
-// chunk-local table slot of block `bi` of chain `c`: c * RDO_CHUNK + (bi - first - step0)
+// chunk-local table slot of block `bi` of chain `c`: chains[c].slot_off + (bi - first - step0)
 __global__ void __launch_bounds__(256) k_rdo_prep(const uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
-                                                  uint32_t n_chains, uint32_t step0, ub::RdoBlockInfo* __restrict__ info,
+                                                  uint32_t n_chains, uint32_t n_slots, uint32_t step0, ub::RdoBlockInfo* __restrict__ info,
                                                   ub::RdoPre* __restrict__ pre, uint32_t* __restrict__ tables,
                                                   unsigned int* __restrict__ err_flag, ub::RdoParams prm) {
   const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
-  const uint32_t c = warp / RDO_CHUNK, k = warp % RDO_CHUNK;
-  if (c >= n_chains) return;
+  if (warp >= n_slots) return;
+  uint32_t c = 0, hi = n_chains - 1;   // last chain whose slot_off <= warp
+  while (c < hi) { const uint32_t mid = (c + hi + 1) >> 1; if (chains[mid].slot_off <= warp) c = mid; else hi = mid - 1; }
+  const uint32_t k = warp - chains[c].slot_off;
   const uint32_t bi = chains[c].first + step0 + k;
   if (bi >= chains[c].last) return;
   uint32_t p[16];
@@ -675,15 +659,16 @@ __global__ void __launch_bounds__(256) k_rdo_prep(const uint4* __restrict__ bloc
   ub::RdoBlockInfo f;
   ub::UnpackedUastc u;
   const bool ok = ub::rdo_block_info(blk, f, u);
-  if (lane == 0) { info[(size_t)c * RDO_CHUNK + k] = f; if (!ok) atomicOr(err_flag, 1u); }
+  const size_t slot = (size_t)chains[c].slot_off + k;
+  if (lane == 0) { info[slot] = f; if (!ok) atomicOr(err_flag, 1u); }
   if (!ok || f.mode == ub::UASTC_MODE_SOLID) return;
-  uint32_t* table = tables + ((size_t)c * RDO_CHUNK + k) * ub::RDO_TABLE_WORDS;
+  uint32_t* table = tables + slot * ub::RDO_TABLE_WORDS;
   if (lane < (1u << f.wb)) ub::rdo_fill_level(p, u, f, lane, table);
   __syncwarp();  // orders the lanes' table writes before lane 0's reads
   if (lane == 0) {
     ub::RdoCur cur;
     ub::rdo_prepare_fast(p, blk, f, table, prm, cur);
-    pre[(size_t)c * RDO_CHUNK + k] = ub::rdo_pre_of(cur);
+    pre[slot] = ub::rdo_pre_of(cur);
   }
 }
 
@@ -734,7 +719,7 @@ __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ b
   ub::RdoBlockInfo nx_info;
   ub::RdoPre nx_pre;
   auto fetch = [&](uint32_t bi) {
-    const size_t slot = (size_t)blockIdx.x * RDO_CHUNK + (bi - begin);
+    const size_t slot = (size_t)ch.slot_off + (bi - begin);
     if (tid < 128) nx = __ldg((const uint4*)(tables + slot * ub::RDO_TABLE_WORDS) + tid);
     else if (tid < 132) nx = __ldg(px + (size_t)bi * 4 + (tid - 128));
     else if (tid == 132) nx = blocks[bi];
@@ -837,743 +822,6 @@ __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, 
   }
 }
 
-const int MAXC_FAST = 21, MAXC_FULL = 170;
-
-// Encode launch shape: 1024-thread CTAs (one per SM, every warp of the SM in the same phase) when there is enough
-// work to give every SM two of them; smaller CTAs for small inputs so that all SMs still get blocks.
-unsigned encode_threads(uint64_t n) {
-  unsigned t = ENC_THREADS;
-  while (t > 128 && (n + t - 1) / t < 2ull * (uint64_t)g_ctx.sm_count) t >>= 1;
-  return t;
-}
-unsigned encode_grid(uint64_t n) {
-  const unsigned t = encode_threads(n);
-  const uint64_t want = (n + t - 1) / t;
-  return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)g_ctx.sm_count * 64));
-}
-
 __global__ void k_set_u64(unsigned long long* p, unsigned long long v) { *p = v; }
 
-int launch_transcode(uint32_t target, const void* d_src, void* d_dst, uint64_t n, cudaStream_t st, uint64_t* d_first_bad) {
-  if (!n) return B200_OK;
-  // persistent tiles: up to 6 CTAs (34 KB of shared memory each) per SM, each walking tiles with a grid stride
-  const uint64_t tiles = (n + XT_TILE - 1) / XT_TILE;
-  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
-  if (target == B200_TTF_BC7_RGBA)
-    k_transcode_tiled<0><<<grid, XT_THREADS, xt_smem_bytes(0), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, XtImage{});
-  else
-    k_transcode_tiled<1><<<grid, XT_THREADS, xt_smem_bytes(1), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, XtImage{});
-  g_launches++;
-  CU(cudaGetLastError());
-  return B200_OK;
-}
-
-// The hint-driven block targets (ETC1_RGB 0, ETC2_RGBA 1, BC1_RGB 2, BC3_RGBA 3, BC4_R 4, BC5_RG 5): 8 or 16 bytes per block.
-bool is_hinted_target(uint32_t t) { return t <= B200_TTF_BC5_RG || t == B200_TTF_ETC2_EAC_R11 || t == B200_TTF_ETC2_EAC_RG11; }
-uint32_t out_block_bytes(uint32_t t) { return (t == B200_TTF_ETC1_RGB || t == B200_TTF_BC1_RGB || t == B200_TTF_BC4_R || t == B200_TTF_ETC2_EAC_R11) ? 8u : 16u; }
-bool is_block_target(uint32_t t) { return t == B200_TTF_BC7_RGBA || t == B200_TTF_ASTC_4x4_RGBA || is_hinted_target(t); }
-
-int launch_hinted(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst, uint64_t n, cudaStream_t st,
-                  uint64_t* d_first_bad) {
-  if (!n) return B200_OK;
-  const bool from_alpha = has_alpha && (decode_flags & B200_DECODE_FLAG_ALPHA_TO_OPAQUE);
-  if (target == B200_TTF_ETC1_RGB && from_alpha) return fail(B200_E_INVALID_VALUE, "ETC1 from the alpha channel is not accelerated");
-  if (((uintptr_t)d_dst & 15u) || ((uintptr_t)d_src & 15u)) return fail(B200_E_INVALID_VALUE, "device pointers must be 16-byte aligned");
-  XtImage im{};
-  im.kind = target;
-  im.hq = (decode_flags & B200_DECODE_FLAG_HIGH_QUALITY) ? 1u : 0u;
-  im.chan0 = ((target == B200_TTF_BC4_R || target == B200_TTF_ETC2_EAC_R11) && from_alpha) ? 3u : 0u;   // transcode_image, XC:10417-10438, :10515
-  im.chan1 = 3u;
-  const uint64_t tiles = (n + xt_tile(3) - 1) / xt_tile(3);
-  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
-  switch (target == B200_TTF_ETC2_EAC_R11 ? 6u : target == B200_TTF_ETC2_EAC_RG11 ? 7u : target) {
-#define XH_CASE(KIND) case KIND: k_transcode_tiled<3, KIND><<<grid, XT_THREADS, xt_smem_bytes(3), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im); break;
-    XH_CASE(0) XH_CASE(1) XH_CASE(2) XH_CASE(3) XH_CASE(4) XH_CASE(5) XH_CASE(6) XH_CASE(7)
-#undef XH_CASE
-  }
-  g_launches++;
-  CU(cudaGetLastError());
-  return B200_OK;
-}
-
-bool is_texel_target(uint32_t t) { return t == B200_TTF_RGBA32 || t == B200_TTF_RGB565 || t == B200_TTF_BGR565 || t == B200_TTF_RGBA4444; }
-uint32_t texel_bytes(uint32_t t) { return t == B200_TTF_RGBA32 ? 4u : 2u; }
-
-// One image's blocks (raster order, ceil(w/4) x ceil(h/4)) -> w x h texels at d_dst, row pitch in texels.
-int launch_decode(uint32_t target, const void* d_src, void* d_dst, uint32_t w, uint32_t h, uint32_t pitch_px, cudaStream_t st, uint64_t* d_first_bad) {
-  if (!w || !h) return B200_OK;
-  XtImage im;
-  im.w = w; im.h = h; im.bx = (w + 3) / 4; im.pitch_px = pitch_px; im.kind = target;
-  const uint32_t row_align = target == B200_TTF_RGBA32 ? 4u : 4u;   // 4 texels = 16 B (RGBA32) or 8 B (16-bit targets)
-  im.vec_ok = (pitch_px % row_align == 0 && ((uintptr_t)d_dst % (target == B200_TTF_RGBA32 ? 16 : 8)) == 0) ? 1u : 0u;
-  const uint64_t n = (uint64_t)im.bx * ((h + 3) / 4);
-  const uint64_t tiles = (n + xt_tile(2) - 1) / xt_tile(2);
-  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, (uint64_t)g_ctx.sm_count * XT_CTAS_PER_SM);
-  k_transcode_tiled<2><<<grid, XT_THREADS, xt_smem_bytes(2), st>>>((const uint4*)d_src, (uint4*)d_dst, n, (unsigned long long*)d_first_bad, im);
-  g_launches++;
-  CU(cudaGetLastError());
-  return B200_OK;
-}
-
-// The RDO post-pass over n device-resident blocks that form `n_images` consecutive images (image i holds
-// img_blocks[i] blocks; job ranges never cross an image, ENC/basisu_comp.cpp:1574 calls uastc_rdo per slice).
-int rdo_run(uint4* d_blocks, const uint4* d_px, const std::vector<uint64_t>& img_blocks, const b200_uastc_params& prm, cudaStream_t st) {
-  ub::RdoParams p;
-  p.lambda = prm.rdo_lambda > 0.0f ? prm.rdo_lambda : 1.0f;
-  p.max_rms_ratio = 10.0f;   // UASTC_RDO_DEFAULT_MAX_ALLOWED_RMS_INCREASE_RATIO (libktx does not expose it)
-  p.skip_rms = 8.0f;         // UASTC_RDO_DEFAULT_SKIP_BLOCK_RMS_THRESH
-  p.smooth_scale = prm.rdo_max_smooth_block_error_scale > 0.0f ? prm.rdo_max_smooth_block_error_scale : 10.0f;
-  p.smooth_std_dev = prm.rdo_max_smooth_block_std_dev > 0.0f ? prm.rdo_max_smooth_block_std_dev : 18.0f;
-  const uint32_t dict = prm.rdo_dict_size ? prm.rdo_dict_size : 4096u;
-  p.window = std::max<uint32_t>(1u, dict / 16u);
-  p.literal_cost = 100; p.flags = prm.pack_flags; p.refine = 1;
-
-  std::vector<RdoChain> chains;
-  uint64_t base = 0, hist_total = 0, n_total = 0;
-  uint32_t longest = 0;
-  for (uint64_t nb : img_blocks) {
-    uint32_t per;
-    const uint32_t jobs = ub::rdo_job_ranges((uint32_t)nb, prm.rdo_total_jobs, &per);
-    for (uint32_t j = 0; j < jobs; j++) {
-      RdoChain c;
-      c.first = (uint32_t)(base + (uint64_t)j * per);
-      c.last = (uint32_t)(base + std::min<uint64_t>(nb, (uint64_t)(j + 1) * per));
-      uint32_t cap = 16;
-      while (cap < 2 * (c.last - c.first) + 16) cap <<= 1;
-      c.hist_off = hist_total; c.hist_mask = cap - 1; c.pad = 0;
-      hist_total += cap;
-      longest = std::max(longest, c.last - c.first);
-      chains.push_back(c);
-    }
-    base += nb;
-  }
-  n_total = base;
-  if (n_total >= 0xFFFFFFFFull) return fail(B200_E_INVALID_VALUE, "too many blocks for one RDO call");
-  if (chains.empty()) return B200_OK;
-  const uint32_t nc = (uint32_t)chains.size();
-
-  RdoChain* d_chains = nullptr; ub::RdoHistEntry* d_hist = nullptr; ub::RdoBlockInfo* d_info = nullptr;
-  uint32_t* d_tables = nullptr; uint8_t* d_mod = nullptr; unsigned int* d_err = nullptr; ub::RdoPre* d_pre = nullptr; uint8_t* d_hz = nullptr;
-  auto cleanup = [&]() { cudaFree(d_chains); cudaFree(d_hist); cudaFree(d_info); cudaFree(d_tables); cudaFree(d_mod); cudaFree(d_err); cudaFree(d_pre); cudaFree(d_hz); };
-  cudaError_t e = cudaSuccess;
-  if (e == cudaSuccess) e = cudaMalloc(&d_chains, nc * sizeof(RdoChain));
-  if (e == cudaSuccess) e = cudaMalloc(&d_hist, hist_total * sizeof(ub::RdoHistEntry));
-  if (e == cudaSuccess) e = cudaMalloc(&d_info, (size_t)nc * RDO_CHUNK * sizeof(ub::RdoBlockInfo));
-  if (e == cudaSuccess) e = cudaMalloc(&d_tables, (size_t)nc * RDO_CHUNK * ub::RDO_TABLE_WORDS * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&d_pre, (size_t)nc * RDO_CHUNK * sizeof(ub::RdoPre));
-  if (e == cudaSuccess) e = cudaMalloc(&d_hz, n_total);
-  if (e == cudaSuccess) e = cudaMalloc(&d_mod, n_total);
-  if (e == cudaSuccess) e = cudaMalloc(&d_err, 4);
-  if (e != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc RDO state", e); }
-  cudaMemcpyAsync(d_chains, chains.data(), nc * sizeof(RdoChain), cudaMemcpyHostToDevice, st);
-  cudaMemsetAsync(d_hist, 0, hist_total * sizeof(ub::RdoHistEntry), st);
-  cudaMemsetAsync(d_mod, 0, n_total, st);
-  cudaMemsetAsync(d_err, 0, 4, st);
-  k_rdo_hazard<<<dim3((unsigned)std::min<uint32_t>((longest + 255) / 256, 1024u), nc), 256, 0, st>>>(d_blocks, d_chains, nc, p.window, d_hz);
-  g_launches++;
-  for (uint32_t step0 = 0; step0 < longest; step0 += RDO_CHUNK) {
-    const uint64_t warps = (uint64_t)nc * RDO_CHUNK;
-    k_rdo_prep<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, st>>>(d_blocks, d_px, d_chains, nc, step0, d_info, d_pre, d_tables, d_err, p);
-    k_rdo_chain<<<nc, RDO_THREADS, 0, st>>>(d_blocks, d_px, d_chains, step0, d_info, d_pre, d_tables, d_hist, d_hz, d_mod, p);
-    g_launches += 2;
-  }
-  k_rdo_rehint<<<(unsigned)std::min<uint64_t>((n_total + 127) / 128, (uint64_t)g_ctx.sm_count * 64), 128, 0, st>>>(d_blocks, d_px, d_mod, n_total, prm.pack_flags);
-  g_launches++;
-  unsigned int h_err = 0;
-  e = cudaMemcpyAsync(&h_err, d_err, 4, cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  if (e == cudaSuccess) e = cudaGetLastError();
-  cleanup();
-  if (e != cudaSuccess) return fail(B200_E_CUDA, "RDO pipeline", e);
-  if (h_err) return fail(B200_E_BAD_BLOCK, "RDO: an input block does not unpack");
-  return B200_OK;
-}
-
-// Encode + RDO for a host call: every image's texel blocks and UASTC blocks stay resident (64 + 16 B per block) so the
-// post-pass can walk them; job ranges are per image, all ranges of all images walk concurrently.
-unsigned expand_grid(uint64_t texels) { return (unsigned)std::min<uint64_t>((texels + 255) / 256, (uint64_t)g_ctx.sm_count * 32); }
-
-// Source layout of a host encode call: components per texel and the packed component mapping (see k_expand_swizzle)
-struct SrcFmt { uint32_t comps = 4, sel = 0x04030201u; bool identity() const { return comps == 4 && sel == 0x04030201u; } };
-
-int encode_with_rdo(const b200_image* images, uint32_t n_images, const SrcFmt& fmt, const b200_uastc_params* params, uint8_t* const* out_blocks,
-                    uint32_t* out_any_alpha, cudaStream_t* ss) {
-  std::vector<uint64_t> nb(n_images);
-  uint64_t total = 0;
-  size_t max_in = 0, max_exp = 0;
-  for (uint32_t i = 0; i < n_images; i++) {
-    const size_t pitch = images[i].row_pitch_bytes ? images[i].row_pitch_bytes : (size_t)images[i].width * fmt.comps;
-    if (pitch < (size_t)images[i].width * fmt.comps) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
-    nb[i] = (uint64_t)((images[i].width + 3) / 4) * ((images[i].height + 3) / 4);
-    total += nb[i];
-    max_in = std::max(max_in, pitch * images[i].height);
-    max_exp = std::max(max_exp, (size_t)images[i].width * 4 * images[i].height);
-  }
-  uint8_t* d_img = nullptr; uint4* d_px = nullptr; uint4* d_blk = nullptr; unsigned int* d_alpha = nullptr; uint8_t* d_exp = nullptr;
-  auto cleanup = [&]() { cudaFree(d_img); cudaFree(d_px); cudaFree(d_blk); cudaFree(d_alpha); cudaFree(d_exp); };
-  cudaError_t e = cudaMalloc(&d_img, max_in);
-  if (e == cudaSuccess && !fmt.identity()) e = cudaMalloc(&d_exp, max_exp);
-  if (e == cudaSuccess) e = cudaMalloc(&d_px, total * 64);
-  if (e == cudaSuccess) e = cudaMalloc(&d_blk, total * 16);
-  if (e == cudaSuccess) e = cudaMalloc(&d_alpha, 4);
-  if (e != cudaSuccess) { cleanup(); return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc RDO buffers", e); }
-  cudaStream_t st = ss[1];
-  cudaMemsetAsync(d_alpha, 0, 4, st);
-  const bool full = (params->pack_flags & 7u) >= 4u;
-  uint64_t off = 0;
-  for (uint32_t i = 0; i < n_images && e == cudaSuccess; i++) {
-    const b200_image& im = images[i];
-    uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * fmt.comps;
-    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
-    e = cudaMemcpyAsync(d_img, im.rgba, (size_t)pitch * im.height, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) break;
-    const uint8_t* d_rgba = d_img;
-    if (!fmt.identity()) {
-      k_expand_swizzle<<<expand_grid((uint64_t)im.width * im.height), 256, 0, st>>>(d_img, im.width, im.height, pitch, fmt.comps, fmt.sel, (uint32_t*)d_exp);
-      g_launches++;
-      d_rgba = d_exp; pitch = im.width * 4;
-    }
-    k_gather_blocks<<<(unsigned)std::min<uint64_t>((nb[i] + 255) / 256, (uint64_t)g_ctx.sm_count * 16), 256, 0, st>>>(d_rgba, im.width, im.height, pitch, d_px + off * 4, bx, by, d_alpha);
-    if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
-    else k_encode_blocks<MAXC_FAST><<<encode_grid(nb[i]), encode_threads(nb[i]), 0, st>>>(d_px + off * 4, d_blk + off, nb[i], params->pack_flags);
-    g_launches += 2;
-    off += nb[i];
-  }
-  if (e == cudaSuccess) e = cudaGetLastError();
-  if (e != cudaSuccess) { cleanup(); return fail(B200_E_CUDA, "encode before RDO", e); }
-  int rc = rdo_run(d_blk, d_px, nb, *params, st);
-  if (rc) { cleanup(); return rc; }
-  off = 0;
-  for (uint32_t i = 0; i < n_images && e == cudaSuccess; i++) {
-    e = cudaMemcpyAsync(out_blocks[i], d_blk + off, nb[i] * 16, cudaMemcpyDeviceToHost, st);
-    off += nb[i];
-  }
-  unsigned int h_alpha = 0;
-  if (e == cudaSuccess) e = cudaMemcpyAsync(&h_alpha, d_alpha, 4, cudaMemcpyDeviceToHost, st);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cleanup();
-  if (e != cudaSuccess) return fail(B200_E_CUDA, "RDO download", e);
-  if (out_any_alpha) *out_any_alpha = h_alpha ? 1u : 0u;
-  return B200_OK;
-}
-
-// per-thread stream set, created lazily
-struct ThreadStreams {
-  cudaStream_t s[4] = {nullptr, nullptr, nullptr, nullptr};   // copy in, kernels, copy out, second kernel stream
-  int device = -1;
-  ~ThreadStreams() { /* streams die with the context */ }
-};
-thread_local ThreadStreams t_streams;
-
-// Per host thread: the staging buffers of the host-buffer entry points live across calls (a cudaMalloc / cudaFree pair per
-// call costs milliseconds and synchronises the device).  Slots 0-2: slab inputs, 3-5: slab outputs, 6: flags.
-struct Staging {
-  void* p[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // 7-9: expanded RGBA8 slabs
-  size_t n[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-  void* get(int i, size_t bytes) {
-    if (n[i] < bytes) {
-      if (p[i]) cudaFree(p[i]);
-      p[i] = nullptr; n[i] = 0;
-      if (cudaMalloc(&p[i], bytes) != cudaSuccess) return nullptr;
-      n[i] = bytes;
-    }
-    return p[i];
-  }
-  void release() { for (int i = 0; i < 10; i++) { if (p[i]) cudaFree(p[i]); p[i] = nullptr; n[i] = 0; } }
-  ~Staging() { /* at thread exit the context may be gone: the driver reclaims */ }
-};
-thread_local Staging t_stage;
-
-int get_streams(cudaStream_t** out) {
-  if (t_streams.device != g_ctx.device) {
-    CU(cudaSetDevice(g_ctx.device));
-    for (int i = 0; i < 4; i++) CU(cudaStreamCreateWithFlags(&t_streams.s[i], cudaStreamNonBlocking));
-    t_streams.device = g_ctx.device;
-  }
-  *out = t_streams.s;
-  return B200_OK;
-}
-
-}  // namespace
-
-extern "C" {
-
-int b200_uastc_init(void) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  if (g_ctx.ready) return B200_OK;
-  int n = 0;
-  cudaError_t e = cudaGetDeviceCount(&n);
-  if (e != cudaSuccess || n == 0) return fail(B200_E_NO_DEVICE, "no CUDA device (this library has no CPU fallback)", e);
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
-  cudaDeviceProp p;
-  CU(cudaGetDeviceProperties(&p, dev));
-  if (p.major < 10) return fail(B200_E_NO_DEVICE, "device is not sm_100 (B200) class; kernels are built for sm_100a only");
-  CU(cudaSetDevice(dev));
-  g_ctx.device = dev;
-  g_ctx.sm_count = p.multiProcessorCount;
-  CU(cudaFuncSetAttribute(k_transcode_tiled<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(0)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(1)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(2)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  CU(cudaFuncSetAttribute(k_transcode_tiled<3, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xt_smem_bytes(3)));
-  g_ctx.ready = true;
-  return B200_OK;
-}
-
-void b200_uastc_shutdown(void) {
-  t_stage.release();
-  std::lock_guard<std::mutex> lk(g_mu);
-  g_ctx.ready = false;
-}
-
-const char* b200_uastc_last_error(void) { return g_err.c_str(); }
-uint64_t b200_uastc_launch_count(void) { return g_launches.load(); }
-
-int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, uint64_t n_blocks, void* stream, uint64_t* d_first_bad) {
-  return b200_uastc_transcode_dev_ex(target, 0, 1, d_src, d_dst, n_blocks, stream, d_first_bad);
-}
-
-int b200_uastc_transcode_dev_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const void* d_src, void* d_dst, uint64_t n_blocks,
-                                void* stream, uint64_t* d_first_bad) {
-  if (!is_block_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
-  if (n_blocks && (!d_src || !d_dst)) return fail(B200_E_INVALID_VALUE, "null device pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  if (d_first_bad) { k_set_u64<<<1, 1, 0, st>>>((unsigned long long*)d_first_bad, ~0ull); g_launches++; }
-  rc = is_hinted_target(target) ? launch_hinted(target, decode_flags, has_alpha, d_src, d_dst, n_blocks, st, d_first_bad)
-                                : launch_transcode(target, d_src, d_dst, n_blocks, st, d_first_bad);
-  if (rc) return rc;
-  if (!stream) CU(cudaStreamSynchronize(st));
-  return B200_OK;
-}
-
-int b200_uastc_decode_image_dev(uint32_t target, const void* d_src, void* d_dst, uint32_t width, uint32_t height,
-                                uint32_t dst_row_pitch_texels, void* stream, uint64_t* d_first_bad) {
-  if (!is_texel_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported decode target");
-  if (width && height && (!d_src || !d_dst)) return fail(B200_E_INVALID_VALUE, "null device pointer");
-  if (dst_row_pitch_texels && dst_row_pitch_texels < width) return fail(B200_E_INVALID_VALUE, "row pitch smaller than the image");
-  if (((uintptr_t)d_dst % texel_bytes(target)) != 0) return fail(B200_E_INVALID_VALUE, "destination not aligned to the texel size");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  if (d_first_bad) { k_set_u64<<<1, 1, 0, st>>>((unsigned long long*)d_first_bad, ~0ull); g_launches++; }
-  rc = launch_decode(target, d_src, d_dst, width, height, dst_row_pitch_texels ? dst_row_pitch_texels : width, st, d_first_bad);
-  if (rc) return rc;
-  if (!stream) CU(cudaStreamSynchronize(st));
-  return B200_OK;
-}
-
-int b200_uastc_decode(uint32_t target, const b200_decode_image* images, uint32_t n_images, const uint8_t* src_base,
-                      uint8_t* dst_base, int64_t* bad_image) {
-  if (bad_image) *bad_image = -1;
-  if (!is_texel_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported decode target");
-  if (n_images && (!images || !src_base || !dst_base)) return fail(B200_E_INVALID_VALUE, "null pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t* ss;
-  rc = get_streams(&ss);
-  if (rc) return rc;
-  const uint32_t bpp = texel_bytes(target);
-
-  // Slabs = whole block rows of one image: contiguous in the UASTC source and (rows of w texels) in the destination.
-  struct Slab { uint32_t image, w, rows_px; uint64_t so, dofs, n_blocks; };
-  std::vector<Slab> slabs;
-  const uint64_t SLAB_BLOCKS = 1u << 19;   // 8 MiB in, up to 32 MiB out
-  uint64_t max_in = 0, max_out = 0;
-  for (uint32_t i = 0; i < n_images; i++) {
-    const uint32_t w = images[i].width, h = images[i].height;
-    if (!w || !h) continue;
-    const uint32_t bx = (w + 3) / 4, by = (h + 3) / 4;
-    const uint32_t rows_per = (uint32_t)std::max<uint64_t>(1, SLAB_BLOCKS / bx);
-    for (uint32_t r0 = 0; r0 < by; r0 += rows_per) {
-      const uint32_t nr = std::min(rows_per, by - r0);
-      const uint32_t px_rows = std::min(h - r0 * 4, nr * 4);
-      slabs.push_back({i, w, px_rows, images[i].src_offset + (uint64_t)r0 * bx * 16, images[i].dst_offset + (uint64_t)r0 * 4 * w * bpp, (uint64_t)nr * bx});
-      max_in = std::max(max_in, (uint64_t)nr * bx * 16);
-      max_out = std::max(max_out, (uint64_t)px_rows * w * bpp);
-    }
-  }
-  if (slabs.empty()) return B200_OK;
-  const int RING = 3;
-  const int nring = (int)std::min<size_t>(RING, slabs.size());
-  uint8_t* d_in[RING] = {0}; uint8_t* d_out[RING] = {0};
-  cudaEvent_t ev_in[RING], ev_k[RING], ev_out[RING];
-  for (int i = 0; i < nring; i++) {
-    d_in[i] = (uint8_t*)t_stage.get(i, max_in); d_out[i] = (uint8_t*)t_stage.get(3 + i, max_out);
-    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
-  }
-  unsigned long long* d_bad = (unsigned long long*)t_stage.get(6, (size_t)n_images * sizeof(unsigned long long));
-  if (!d_bad) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flags");
-  for (int i = 0; i < nring; i++) {
-    cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
-  }
-  cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
-  cudaMemsetAsync(d_bad, 0xFF, (size_t)n_images * sizeof(unsigned long long), s_k);
-  cudaError_t err = cudaSuccess;
-  for (size_t k = 0; k < slabs.size() && err == cudaSuccess; k++) {
-    const Slab& sl = slabs[k];
-    const int b = (int)(k % nring);
-    if (k >= (size_t)nring) {
-      cudaStreamWaitEvent(s_in, ev_k[b], 0);
-      cudaStreamWaitEvent(s_k, ev_out[b], 0);
-    }
-    err = cudaMemcpyAsync(d_in[b], src_base + sl.so, sl.n_blocks * 16, cudaMemcpyHostToDevice, s_in);
-    if (err != cudaSuccess) break;
-    cudaEventRecord(ev_in[b], s_in);
-    cudaStreamWaitEvent(s_k, ev_in[b], 0);
-    launch_decode(target, d_in[b], d_out[b], sl.w, sl.rows_px, sl.w, s_k, (uint64_t*)(d_bad + sl.image));
-    cudaEventRecord(ev_k[b], s_k);
-    cudaStreamWaitEvent(s_out, ev_k[b], 0);
-    err = cudaMemcpyAsync(dst_base + sl.dofs, d_out[b], (size_t)sl.rows_px * sl.w * bpp, cudaMemcpyDeviceToHost, s_out);
-    cudaEventRecord(ev_out[b], s_out);
-  }
-  std::vector<unsigned long long> h_bad(n_images, ~0ull);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_k);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
-  if (err == cudaSuccess) err = cudaMemcpy(h_bad.data(), d_bad, (size_t)n_images * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
-  for (int i = 0; i < nring; i++) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); cudaEventDestroy(ev_out[i]); }
-  if (err != cudaSuccess) return fail(B200_E_CUDA, "decode pipeline", err);
-  for (uint32_t i = 0; i < n_images; i++)
-    if (h_bad[i] != ~0ull) {
-      if (bad_image) *bad_image = i;
-      return fail(B200_E_BAD_BLOCK, "invalid UASTC block");
-    }
-  return B200_OK;
-}
-
-int b200_uastc_transcode(uint32_t target, const b200_xcode_span* spans, uint32_t n_spans, const uint8_t* src_base,
-                         uint8_t* dst_base, int64_t* bad_span) {
-  return b200_uastc_transcode_ex(target, 0, 1, spans, n_spans, src_base, dst_base, bad_span);
-}
-
-int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans, uint32_t n_spans,
-                            const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span) {
-  if (bad_span) *bad_span = -1;
-  if (!is_block_target(target)) return fail(B200_E_INVALID_VALUE, "unsupported transcode target");
-  const bool hinted = is_hinted_target(target);
-  if (hinted && target == B200_TTF_ETC1_RGB && has_alpha && (decode_flags & B200_DECODE_FLAG_ALPHA_TO_OPAQUE))
-    return fail(B200_E_INVALID_VALUE, "ETC1 from the alpha channel is not accelerated");
-  const uint64_t ob = out_block_bytes(target);
-  if (n_spans && (!spans || !src_base || !dst_base)) return fail(B200_E_INVALID_VALUE, "null pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t* ss;
-  rc = get_streams(&ss);
-  if (rc) return rc;
-
-  // Slab list: spans are cut into <= SLAB blocks; adjacent spans that are contiguous in both src and dst merge.
-  struct Run { uint64_t so, dofs, n; uint32_t first_span; };
-  std::vector<Run> runs;
-  for (uint32_t i = 0; i < n_spans; i++) {
-    if (!spans[i].n_blocks) continue;
-    // (the hint-driven targets keep one run -- one flag -- per span: a valid BC4 / BC5 block can be all zero, so the
-    // zero-block scan below that names the span inside a merged run does not apply to them)
-    if (!runs.empty() && !hinted) {
-      Run& r = runs.back();
-      if (r.so + r.n * 16 == spans[i].src_offset && r.dofs + r.n * ob == spans[i].dst_offset) { r.n += spans[i].n_blocks; continue; }
-    }
-    runs.push_back({spans[i].src_offset, spans[i].dst_offset, spans[i].n_blocks, i});
-  }
-  if (runs.empty()) return B200_OK;
-
-  const uint64_t SLAB = 1u << 20;  // 16 MiB in, 16 MiB out per slab
-  const int RING = 3;
-  uint8_t* d_in[RING] = {0}; uint8_t* d_out[RING] = {0};
-  unsigned long long* d_bad = nullptr;
-  cudaEvent_t ev_in[RING], ev_k[RING], ev_out[RING];
-  uint64_t maxn = 0;
-  for (auto& r : runs) maxn = std::max(maxn, std::min(r.n, SLAB));
-  auto cleanup = [&]() {};   // staging buffers stay cached (t_stage)
-  int nring = 0;
-  uint64_t total_slabs = 0;
-  for (auto& r : runs) total_slabs += (r.n + SLAB - 1) / SLAB;
-  nring = (int)std::min<uint64_t>(RING, total_slabs);
-  for (int i = 0; i < nring; i++) {
-    d_in[i] = (uint8_t*)t_stage.get(i, maxn * 16); d_out[i] = (uint8_t*)t_stage.get(3 + i, maxn * ob);
-    if (!d_in[i] || !d_out[i]) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
-    cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
-  }
-  // one "first bad block" word per run so the failing span can be named
-  d_bad = (unsigned long long*)t_stage.get(6, runs.size() * sizeof(unsigned long long));
-  if (!d_bad) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flags");
-  cudaMemsetAsync(d_bad, 0xFF, runs.size() * sizeof(unsigned long long), ss[1]);
-
-  cudaStream_t s_in = ss[0], s_k = ss[1], s_out = ss[2];
-  uint64_t slab_idx = 0;
-  cudaError_t err = cudaSuccess;
-  for (size_t ri = 0; ri < runs.size() && err == cudaSuccess; ri++) {
-    const Run& r = runs[ri];
-    for (uint64_t o = 0; o < r.n && err == cudaSuccess; o += SLAB, slab_idx++) {
-      const uint64_t n = std::min(SLAB, r.n - o);
-      const int b = (int)(slab_idx % nring);
-      if (slab_idx >= (uint64_t)nring) {
-        cudaStreamWaitEvent(s_in, ev_k[b], 0);    // input buffer free once its kernel ran
-        cudaStreamWaitEvent(s_k, ev_out[b], 0);   // output buffer free once copied back
-      }
-      err = cudaMemcpyAsync(d_in[b], src_base + r.so + o * 16, n * 16, cudaMemcpyHostToDevice, s_in);
-      if (err != cudaSuccess) break;
-      cudaEventRecord(ev_in[b], s_in);
-      cudaStreamWaitEvent(s_k, ev_in[b], 0);
-      // block indices inside the kernel are slab-relative; the flag only has to say "this run holds a bad block"
-      if (hinted) launch_hinted(target, decode_flags, has_alpha, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
-      else launch_transcode(target, d_in[b], d_out[b], n, s_k, (uint64_t*)(d_bad + ri));
-      cudaEventRecord(ev_k[b], s_k);
-      cudaStreamWaitEvent(s_out, ev_k[b], 0);
-      err = cudaMemcpyAsync(dst_base + r.dofs + o * ob, d_out[b], n * ob, cudaMemcpyDeviceToHost, s_out);
-      cudaEventRecord(ev_out[b], s_out);
-    }
-  }
-  std::vector<unsigned long long> h_bad(runs.size(), ~0ull);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_k);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
-  if (err == cudaSuccess) err = cudaMemcpy(h_bad.data(), d_bad, runs.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
-  for (int i = 0; i < nring; i++) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); cudaEventDestroy(ev_out[i]); }
-  cleanup();
-  if (err != cudaSuccess) return fail(B200_E_CUDA, "transcode pipeline", err);
-
-  for (size_t ri = 0; ri < runs.size(); ri++) {
-    if (h_bad[ri] != ~0ull) {
-      // A run may hold several merged spans and several slabs; the flag only says "this run has a bad block".
-      // Name the first span of the run that contains one by rescanning that run's spans on the device output:
-      // cheap path -- report the run's first span unless the run was merged, in which case walk its spans.
-      if (bad_span) {
-        int64_t which = runs[ri].first_span;
-        // refine: spans of this run are contiguous; a bad block's output is all-zero, which no valid BC7/ASTC
-        // block produced here can be (BC7 mode bit / ASTC block mode are never zero).
-        uint64_t off = runs[ri].dofs;
-        for (uint32_t si = runs[ri].first_span; si < n_spans && !hinted; si++) {
-          if (spans[si].dst_offset != off) break;
-          bool found = false;
-          const uint64_t* q = (const uint64_t*)(dst_base + off);
-          for (uint64_t k = 0; k < spans[si].n_blocks; k++) if (!q[2 * k] && !q[2 * k + 1]) { found = true; break; }
-          if (found) { which = si; break; }
-          off += spans[si].n_blocks * 16;
-        }
-        *bad_span = which;
-      }
-      return fail(B200_E_BAD_BLOCK, "invalid UASTC block in input");
-    }
-  }
-  return B200_OK;
-}
-
-int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64_t n_blocks, uint32_t pack_flags, void* stream) {
-  if (n_blocks && (!d_block_pixels || !d_out)) return fail(B200_E_INVALID_VALUE, "null device pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  if (!n_blocks) return B200_OK;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  const bool full = (pack_flags & 7u) >= 4u;
-  if (full) k_encode_blocks<MAXC_FULL><<<encode_grid(n_blocks), encode_threads(n_blocks), 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
-  else k_encode_blocks<MAXC_FAST><<<encode_grid(n_blocks), encode_threads(n_blocks), 0, st>>>((const uint4*)d_block_pixels, (uint4*)d_out, n_blocks, pack_flags);
-  g_launches++;
-  CU(cudaGetLastError());
-  if (!stream) CU(cudaStreamSynchronize(st));
-  return B200_OK;
-}
-
-int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
-                                uint32_t pack_flags, void* stream, uint32_t* d_any_alpha) {
-  if (!d_rgba || !d_out || !width || !height) return fail(B200_E_INVALID_VALUE, "bad image");
-  const uint32_t pitch = row_pitch_bytes ? row_pitch_bytes : width * 4;
-  if (pitch < width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  const uint32_t bx = (width + 3) / 4, by = (height + 3) / 4;
-  const uint64_t n = (uint64_t)bx * by;
-  if ((pack_flags & 7u) >= 4u)
-    k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
-  else
-    k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, st>>>((const uint8_t*)d_rgba, width, height, pitch, (uint4*)d_out, bx, by, pack_flags, d_any_alpha);
-  g_launches++;
-  CU(cudaGetLastError());
-  if (!stream) CU(cudaStreamSynchronize(st));
-  return B200_OK;
-}
-
-int b200_uastc_encode_images_dev(const b200_dev_image* images, uint32_t n_images, uint32_t pack_flags, void* stream, uint32_t* d_any_alpha) {
-  if (n_images && !images) return fail(B200_E_INVALID_VALUE, "null pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  if (!n_images) return B200_OK;
-  std::vector<EncImageDesc> descs(n_images);
-  uint64_t total = 0;
-  for (uint32_t i = 0; i < n_images; i++) {
-    const b200_dev_image& im = images[i];
-    if (!im.d_rgba || !im.d_out || !im.width || !im.height) return fail(B200_E_INVALID_VALUE, "bad image");
-    const uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * 4;
-    if (pitch < im.width * 4 || (pitch & 3u) || ((uintptr_t)im.d_rgba & 3u)) return fail(B200_E_INVALID_VALUE, "row pitch / base must be 4-byte aligned and hold a row");
-    descs[i] = {(const uint8_t*)im.d_rgba, (uint4*)im.d_out, im.width, im.height, pitch, (im.width + 3) / 4, total};
-    total += (uint64_t)((im.width + 3) / 4) * ((im.height + 3) / 4);
-  }
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  EncImageDesc* d_descs = nullptr;
-  CU(cudaMallocAsync((void**)&d_descs, n_images * sizeof(EncImageDesc), st));
-  cudaError_t e = cudaMemcpyAsync(d_descs, descs.data(), n_images * sizeof(EncImageDesc), cudaMemcpyHostToDevice, st);  // pageable source: staged before return
-  if (e == cudaSuccess) {
-    if ((pack_flags & 7u) >= 4u) k_encode_images<MAXC_FULL><<<encode_grid(total), encode_threads(total), 0, st>>>(d_descs, n_images, total, pack_flags, d_any_alpha);
-    else k_encode_images<MAXC_FAST><<<encode_grid(total), encode_threads(total), 0, st>>>(d_descs, n_images, total, pack_flags, d_any_alpha);
-    g_launches++;
-    e = cudaGetLastError();
-  }
-  cudaFreeAsync(d_descs, st);
-  if (e != cudaSuccess) return fail(B200_E_CUDA, "encode_images_dev", e);
-  if (!stream) CU(cudaStreamSynchronize(st));
-  return B200_OK;
-}
-
-int b200_uastc_rdo_blocks_dev(void* d_blocks, const void* d_block_pixels, uint64_t n_blocks, const b200_uastc_params* params, void* stream) {
-  if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
-  if (n_blocks && (!d_blocks || !d_block_pixels)) return fail(B200_E_INVALID_VALUE, "null device pointer");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  if (!n_blocks) return B200_OK;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (!st) { cudaStream_t* ss; rc = get_streams(&ss); if (rc) return rc; st = ss[0]; }
-  std::vector<uint64_t> nb(1, n_blocks);
-  return rdo_run((uint4*)d_blocks, (const uint4*)d_block_pixels, nb, *params, st);
-}
-
-int b200_uastc_encode(const b200_image* images, uint32_t n_images, const b200_uastc_params* params, uint8_t* const* out_blocks,
-                      uint32_t* out_any_alpha) {
-  return b200_uastc_encode_ex(images, n_images, nullptr, params, out_blocks, out_any_alpha);
-}
-
-int b200_uastc_encode_ex(const b200_image* images, uint32_t n_images, const b200_src_format* format, const b200_uastc_params* params,
-                         uint8_t* const* out_blocks, uint32_t* out_any_alpha) {
-  if (out_any_alpha) *out_any_alpha = 0;
-  SrcFmt fmt;
-  if (format) {
-    if (format->num_components < 1 || format->num_components > 4) return fail(B200_E_INVALID_VALUE, "num_components must be 1..4");
-    fmt.comps = format->num_components; fmt.sel = 0;
-    for (int c = 0; c < 4; c++) {
-      const uint32_t sc = format->swizzle[c];
-      if (sc < 1 || sc > 6) return fail(B200_E_INVALID_VALUE, "swizzle entries are swizzle_e values 1..6");
-      if (sc <= 4 && sc > fmt.comps) return fail(B200_E_INVALID_VALUE, "swizzle names a component the source does not have");
-      fmt.sel |= sc << (8 * c);
-    }
-  }
-  if (!params || params->struct_size != sizeof(b200_uastc_params)) return fail(B200_E_INVALID_VALUE, "params->struct_size");
-  if (n_images && (!images || !out_blocks)) return fail(B200_E_INVALID_VALUE, "null pointer");
-  for (uint32_t i = 0; i < n_images; i++)
-    if (!images[i].rgba || !images[i].width || !images[i].height || !out_blocks[i]) return fail(B200_E_INVALID_VALUE, "bad image");
-  int rc = b200_uastc_init();
-  if (rc) return rc;
-  cudaStream_t* ss;
-  rc = get_streams(&ss);
-  if (rc) return rc;
-  if (!n_images) return B200_OK;
-  if (params->rdo_enable) return encode_with_rdo(images, n_images, fmt, params, out_blocks, out_any_alpha, ss);
-
-  // Slab list: every image is cut into runs of whole block rows (contiguous in the RGBA source and in the UASTC
-  // output) of at most SLAB_BYTES of input, so upload, encode and download of neighbouring slabs overlap on three
-  // streams through a ring of staging buffers.
-  const size_t SLAB_BYTES = 32u << 20;
-  struct Slab { uint32_t img, y0, rows_px; size_t in_bytes, out_off, out_bytes; };
-  std::vector<Slab> slabs;
-  size_t max_in = 0, max_out = 0, max_exp = 0;
-  for (uint32_t i = 0; i < n_images; i++) {
-    const b200_image& im = images[i];
-    const size_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : (size_t)im.width * fmt.comps;
-    if (pitch < (size_t)im.width * fmt.comps) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
-    const uint32_t bx = (im.width + 3) / 4, by = (im.height + 3) / 4;
-    uint32_t rows_per = (uint32_t)std::max<size_t>(1, SLAB_BYTES / (std::max(pitch, (size_t)im.width * 4) * 4));
-    for (uint32_t r0 = 0; r0 < by; r0 += rows_per) {
-      const uint32_t r1 = std::min(by, r0 + rows_per);
-      const uint32_t y0 = r0 * 4, y1 = std::min(im.height, r1 * 4);
-      Slab sl{i, y0, y1 - y0, pitch * (y1 - y0), (size_t)r0 * bx * 16, (size_t)(r1 - r0) * bx * 16};
-      max_in = std::max(max_in, sl.in_bytes);
-      max_out = std::max(max_out, sl.out_bytes);
-      max_exp = std::max(max_exp, (size_t)im.width * 4 * (y1 - y0));
-      slabs.push_back(sl);
-    }
-  }
-  const int SLOTS = 3;
-  uint8_t* d_in[SLOTS] = {0}; uint8_t* d_out[SLOTS] = {0}; uint8_t* d_exp[SLOTS] = {0};
-  unsigned int* d_alpha = nullptr;
-  cudaEvent_t ev_in[SLOTS], ev_k[SLOTS], ev_out[SLOTS];
-  const int nslots = (int)std::min<size_t>(SLOTS, slabs.size());
-  auto cleanup = [&]() {};   // staging buffers stay cached (t_stage)
-  for (int i = 0; i < nslots; i++) {
-    d_in[i] = (uint8_t*)t_stage.get(i, max_in); d_out[i] = (uint8_t*)t_stage.get(3 + i, max_out);
-    if (!fmt.identity()) d_exp[i] = (uint8_t*)t_stage.get(7 + i, max_exp);
-    if (!d_in[i] || !d_out[i] || (!fmt.identity() && !d_exp[i])) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc staging");
-    cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_k[i], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming);
-  }
-  d_alpha = (unsigned int*)t_stage.get(6, sizeof(unsigned int));
-  if (!d_alpha) return fail(B200_E_OUT_OF_MEMORY, "cudaMalloc flag");
-  // Kernels of consecutive slabs go to two streams in turn: the tail of one slab's grid (fewer CTAs left than SMs)
-  // overlaps the head of the next instead of idling SMs.
-  cudaStream_t s_in = ss[0], s_kk[2] = {ss[1], ss[3]}, s_out = ss[2];
-  cudaEvent_t ev_zero;
-  cudaEventCreateWithFlags(&ev_zero, cudaEventDisableTiming);
-  cudaMemsetAsync(d_alpha, 0, sizeof(unsigned int), s_kk[0]);
-  cudaEventRecord(ev_zero, s_kk[0]);
-  cudaStreamWaitEvent(s_kk[1], ev_zero, 0);
-  const bool full = (params->pack_flags & 7u) >= 4u;
-  cudaError_t err = cudaSuccess;
-  for (size_t k = 0; k < slabs.size() && err == cudaSuccess; k++) {
-    const Slab& sl = slabs[k];
-    const b200_image& im = images[sl.img];
-    const int b = (int)(k % nslots);
-    cudaStream_t s_k = s_kk[k & 1];
-    uint32_t pitch = im.row_pitch_bytes ? im.row_pitch_bytes : im.width * fmt.comps;
-    const uint32_t bx = (im.width + 3) / 4, by = (sl.rows_px + 3) / 4;
-    if (k >= (size_t)nslots) { cudaStreamWaitEvent(s_in, ev_k[b], 0); cudaStreamWaitEvent(s_k, ev_out[b], 0); }
-    err = cudaMemcpyAsync(d_in[b], im.rgba + (size_t)sl.y0 * pitch, sl.in_bytes, cudaMemcpyHostToDevice, s_in);
-    if (err != cudaSuccess) break;
-    cudaEventRecord(ev_in[b], s_in);
-    cudaStreamWaitEvent(s_k, ev_in[b], 0);
-    const uint64_t n = (uint64_t)bx * by;
-    const uint8_t* d_rgba = d_in[b];
-    if (!fmt.identity()) {   // component expansion / swizzle on the device: the upload carries the texture's own 1-4 bytes per texel
-      k_expand_swizzle<<<expand_grid((uint64_t)im.width * sl.rows_px), 256, 0, s_k>>>(d_in[b], im.width, sl.rows_px, pitch, fmt.comps, fmt.sel, (uint32_t*)d_exp[b]);
-      g_launches++;
-      d_rgba = d_exp[b]; pitch = im.width * 4;
-    }
-    if (full) k_encode_image<MAXC_FULL><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_rgba, im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
-    else k_encode_image<MAXC_FAST><<<encode_grid(n), encode_threads(n), 0, s_k>>>(d_rgba, im.width, sl.rows_px, pitch, (uint4*)d_out[b], bx, by, params->pack_flags, d_alpha);
-    g_launches++;
-    cudaEventRecord(ev_k[b], s_k);
-    cudaStreamWaitEvent(s_out, ev_k[b], 0);
-    err = cudaMemcpyAsync(out_blocks[sl.img] + sl.out_off, d_out[b], sl.out_bytes, cudaMemcpyDeviceToHost, s_out);
-    cudaEventRecord(ev_out[b], s_out);
-  }
-  unsigned int h_alpha = 0;
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_in);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_kk[0]);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_kk[1]);
-  cudaEventDestroy(ev_zero);
-  if (err == cudaSuccess) err = cudaStreamSynchronize(s_out);
-  if (err == cudaSuccess) err = cudaGetLastError();
-  if (err == cudaSuccess) err = cudaMemcpy(&h_alpha, d_alpha, sizeof(h_alpha), cudaMemcpyDeviceToHost);
-  for (int i = 0; i < nslots; i++) { cudaEventDestroy(ev_in[i]); cudaEventDestroy(ev_k[i]); cudaEventDestroy(ev_out[i]); }
-  cleanup();
-  if (err != cudaSuccess) return fail(B200_E_CUDA, "encode pipeline", err);
-  if (out_any_alpha) *out_any_alpha = h_alpha ? 1u : 0u;
-  return B200_OK;
-}
-
-}  // extern "C"
+#include "uastc_host.inc"

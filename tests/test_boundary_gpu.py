@@ -1,0 +1,146 @@
+"""GPU tests of the C-ABI boundary itself: re-entrancy from several host threads (the reference pins this for
+ktxTexture2_TranscodeBasis with tests/threadtests/threadtests.cc:90-128), the multi-device planner (one job spread over the
+devices of a mask must produce the bytes of the one-device run), pointer-alignment rejections, shutdown / re-init, and the
+RDO scratch sizing with hundreds of small images."""
+import ctypes, os, threading
+import numpy as np
+import pytest
+import refutil as R
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def K():
+    import ktx_software_b200 as K
+    K.init()
+    return K
+
+
+def test_concurrent_calls_from_8_threads(K):
+    """8 host threads x (transcode BC7 + ASTC, encode level 1) at once; every result must equal the serial one."""
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    u = np.ascontiguousarray(np.tile(g["uastc"], (8, 1)))          # ~170k blocks: several tiles per call
+    imgs = [R.img_mix(96 + 8 * t, 64 + 4 * t, 30 + t) for t in range(8)]
+    want_b = K.transcode(u, K.TTF_BC7_RGBA).copy()
+    want_a = K.transcode(u, K.TTF_ASTC_4x4_RGBA).copy()
+    want_e = [K.encode_images([im], 1)[0][0].copy() for im in imgs]
+    errs = []
+
+    def work(t):
+        try:
+            for _ in range(3):
+                assert (K.transcode(u, K.TTF_BC7_RGBA) == want_b).all()
+                assert (K.encode_images([imgs[t]], 1)[0][0] == want_e[t]).all()
+                assert (K.transcode(u, K.TTF_ASTC_4x4_RGBA) == want_a).all()
+        except Exception as e:   # noqa: BLE001
+            errs.append((t, repr(e)))
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(8)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    assert not errs, errs
+
+
+def _mask(K, want):
+    n = K.device_count()
+    return (1 << min(n, want)) - 1, min(n, want)
+
+
+def test_one_job_over_the_device_mask_matches_one_device(K):
+    """One mip chain (level 0 must be slab-split) and one batch of faces through b200_uastc_encode with a device mask: the
+    gathered bytes equal the single-device bytes.  Runs over 2 devices when the box has them (gpurun --gpus 2), else 1."""
+    mask, nd = _mask(K, 8)
+    base = R.img_mix(1024, 1024, 9)
+    chain = [base]
+    while chain[-1].shape[0] > 1:
+        a = chain[-1].astype(np.uint16)
+        chain.append(((a[0::2, 0::2] + a[1::2, 0::2] + a[0::2, 1::2] + a[1::2, 1::2] + 2) >> 2).astype(np.uint8))
+    one, alpha1 = K.encode_images(chain, 2)
+    many, alpha2 = K.encode_images(chain, 2, device_mask=mask)
+    assert alpha1 == alpha2
+    for a, b in zip(one, many):
+        assert (a == b).all()
+    faces = [R.img_mix(256, 256, 100 + i) for i in range(12)]
+    one, _ = K.encode_images(faces, 1)
+    many, _ = K.encode_images(faces, 1, device_mask=mask)
+    assert all((a == b).all() for a, b in zip(one, many))
+    # RDO spreads whole images
+    one, _ = K.encode_images(faces[:5], 1 | 512, rdo=True, rdo_lambda=2.0, total_jobs=4)
+    many, _ = K.encode_images(faces[:5], 1 | 512, rdo=True, rdo_lambda=2.0, total_jobs=4, device_mask=mask)
+    assert all((a == b).all() for a, b in zip(one, many))
+    # transcode over the process-wide device set
+    u = np.concatenate(one + [np.tile(one[0], (40, 1))])
+    want = K.transcode(u, K.TTF_BC7_RGBA).copy()
+    K.set_devices(mask)
+    try:
+        got = K.transcode(u, K.TTF_BC7_RGBA)
+        got1 = K.transcode(u, K.TTF_BC1_RGB, decode_flags=0)
+    finally:
+        K.set_devices(0)
+    assert (got == want).all()
+    assert (got1 == K.transcode(u, K.TTF_BC1_RGB, decode_flags=0)).all()
+    print("devices used:", nd)
+
+
+def test_bad_device_mask_is_rejected(K):
+    n = K.device_count()
+    assert n >= 1
+    with pytest.raises(K.B200Error) as e:
+        K.encode_images([R.img_mix(8, 8, 1)], 0, device_mask=1 << 15 if n < 16 else 0xFFFF0000)
+    assert e.value.code in (-1, -2)
+    with pytest.raises(K.B200Error):
+        K.set_devices(1 << 15 if n < 16 else 1 << 20)
+
+
+def test_misaligned_device_pointers(K):
+    """Block pointers must be 16-byte aligned (rejected, not faulted); a cropped, unaligned image pointer is legal and takes
+    the narrow load path (a misaligned uint4 load is a sticky context error)."""
+    import torch
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    raw = torch.zeros(16 * 1024 + 64, dtype=torch.uint8, device="cuda")
+    dst = torch.zeros(16 * 1024 + 64, dtype=torch.uint8, device="cuda")
+    raw[8:8 + 16 * 1024] = torch.from_numpy(g["uastc"][:1024].reshape(-1)).cuda()
+    for tf in (K.TTF_BC7_RGBA, K.TTF_BC4_R):
+        with pytest.raises(K.B200Error) as e:
+            K.transcode_dev(tf, raw.data_ptr() + 8, dst.data_ptr(), 1024) if tf == K.TTF_BC7_RGBA else \
+                K.transcode_dev_ex(tf, 0, True, raw.data_ptr() + 8, dst.data_ptr(), 1024)
+        assert e.value.code == -2
+        with pytest.raises(K.B200Error):
+            K.transcode_dev_ex(tf, 0, True, raw.data_ptr(), dst.data_ptr() + 4, 1024)
+    # a crop of a larger image: base 4-byte aligned only, pitch of the parent
+    big = R.img_mix(100, 64, 4)
+    d_big = torch.from_numpy(big).cuda()
+    x0, y0, w, h = 3, 5, 64, 40
+    out = torch.zeros(((w // 4) * (h // 4), 16), dtype=torch.uint8, device="cuda")
+    K.encode_image_dev(d_big.data_ptr() + (y0 * 100 + x0) * 4, w, h, out.data_ptr(), 1, row_pitch_bytes=400)
+    want, _ = K.encode_images([np.ascontiguousarray(big[y0:y0 + h, x0:x0 + w])], 1)
+    assert (out.cpu().numpy() == want[0]).all()
+    with pytest.raises(K.B200Error):
+        K.encode_image_dev(d_big.data_ptr(), 64, 40, out.data_ptr() + 8, 1, row_pitch_bytes=400)
+    torch.cuda.synchronize()   # no sticky error left behind
+    assert (K.transcode(g["uastc"][:64], K.TTF_BC7_RGBA).reshape(-1, 16) == g["bc7"][:64]).all()
+
+
+def test_shutdown_and_reinit(K):
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    K.transcode(g["uastc"][:4096], K.TTF_BC7_RGBA)
+    K.shutdown()
+    K.shutdown()
+    K.init()
+    assert (K.transcode(g["uastc"][:4096], K.TTF_ASTC_4x4_RGBA).reshape(-1, 16) == g["astc"][:4096]).all()
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not shipped")
+def test_rdo_with_hundreds_of_small_images(K):
+    """RDO scratch was RDO_CHUNK table slots per chain whatever its length (256 small images x 4 jobs ~ 16 GB)."""
+    imgs = [R.img_mix(32 + 4 * (i % 5), 24 + 4 * (i % 3), 400 + i) for i in range(256)]
+    flags = 1 | 512
+    outs, _ = K.encode_images(imgs, flags, rdo=True, rdo_lambda=2.0, total_jobs=4)
+    for i in (0, 1, 7, 100, 255):
+        px = R.ref_extract_blocks(imgs[i])
+        want = R.ref_rdo(R.ref_encode_blocks(px, flags), px, flags, 4, 4, lam=2.0)
+        assert (outs[i] == want).all(), i
