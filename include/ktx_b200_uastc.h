@@ -65,6 +65,8 @@ int b200_uastc_set_devices(uint64_t device_mask);
 /* Number of CUDA devices this library can run on (sm_100 class). */
 int b200_uastc_device_count(void);
 const char* b200_uastc_last_error(void);
+/* Identifies the sources this binary was built from (SHA-1 prefix; bench.py quotes ncu counters only for a matching build). */
+const char* b200_uastc_build_id(void);
 /* Number of kernel launches this library has issued since init (bench.py's gpu_launches). */
 uint64_t b200_uastc_launch_count(void);
 
@@ -179,6 +181,16 @@ typedef struct b200_src_format {
 } b200_src_format;
 int b200_uastc_encode_ex(const b200_image* images, uint32_t n_images, const b200_src_format* format,
                          const b200_uastc_params* params, uint8_t* const* out_blocks, uint32_t* out_any_alpha);
+
+/* Device-resident pipeline: only the BASE level crosses PCIe.  Levels 1 .. n_levels-1 (level l is
+ * max(1, w >> l) x max(1, h >> l)) are filtered from the level above on the device with the 2x2 box filter, per channel
+ * (a + b + c + d + 2) >> 2 with source coordinates clamped to the level, then every level is encoded.  This is the integer box
+ * filter of the measurement harness; `ktx create --generate-mipmap` runs a float resampler on the host before libktx is
+ * called (tools/ktx/command_create.cpp:1994-1996), which this does not replace.  base: tightly packed RGBA8.  out_blocks[l]
+ * receives level l's blocks; out_level_rgba (may be NULL, entries may be NULL) receives the generated RGBA8 levels l >= 1.
+ * No RDO (B200_E_INVALID_VALUE with rdo_enable).  Runs on the first device of the mask. */
+int b200_uastc_encode_mipchain(const b200_image* base, uint32_t n_levels, const b200_uastc_params* params,
+                               uint8_t* const* out_blocks, uint8_t* const* out_level_rgba, uint32_t* out_any_alpha);
 
 /* Device-resident variant: d_block_pixels = n_blocks x 64 bytes (4x4 RGBA8 texels, raster within the block, as
  * basis_compressor::extract_source_blocks lays them out, ENC/basisu_comp.cpp:2705-2766); d_out = n_blocks x 16 B. */

@@ -22,7 +22,7 @@ EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_e
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
                     "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex",
-                    "b200_uastc_set_devices", "b200_uastc_device_count"]
+                    "b200_uastc_set_devices", "b200_uastc_device_count", "b200_uastc_build_id", "b200_uastc_encode_mipchain"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -74,6 +74,9 @@ def lib():
         l.b200_uastc_last_error.restype = ctypes.c_char_p
         l.b200_uastc_launch_count.restype = ctypes.c_uint64
         l.b200_uastc_set_devices.argtypes = [ctypes.c_uint64]
+        l.b200_uastc_build_id.restype = ctypes.c_char_p
+        l.b200_uastc_encode_mipchain.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(UastcParams), ctypes.POINTER(ctypes.c_void_p),
+                                                 ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
         l.b200_uastc_transcode.argtypes = [ctypes.c_uint32, ctypes.POINTER(XcodeSpan), ctypes.c_uint32, ctypes.c_void_p,
                                            ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64)]
         l.b200_uastc_transcode_dev.argtypes = [ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
@@ -110,6 +113,10 @@ def init():
 
 def launch_count():
     return int(lib().b200_uastc_launch_count())
+
+
+def build_id():
+    return lib().b200_uastc_build_id().decode()
 
 
 def set_devices(device_mask):
@@ -246,6 +253,30 @@ def encode_images(images, pack_flags, **rdo):
     any_alpha = ctypes.c_uint32(0)
     _check(lib().b200_uastc_encode(arr, len(imgs), ctypes.byref(p), optr, ctypes.byref(any_alpha)))
     return outs, bool(any_alpha.value)
+
+
+def encode_mipchain(base, n_levels, pack_flags, want_levels=False):
+    """Base level in, all levels out (b200_uastc_encode_mipchain): base uint8 [h,w,4].  Returns (blocks per level, generated
+    RGBA8 levels 1.. or None, any_alpha)."""
+    base = np.ascontiguousarray(base, dtype=np.uint8)
+    h, w = base.shape[:2]
+    img = Image(base.ctypes.data, w, h, 0)
+    outs, lv = [], []
+    optr = (ctypes.c_void_p * n_levels)()
+    lptr = (ctypes.c_void_p * n_levels)()
+    for l in range(n_levels):
+        lw, lh = max(1, w >> l), max(1, h >> l)
+        o = np.zeros((((lw + 3) // 4) * ((lh + 3) // 4), 16), np.uint8)
+        outs.append(o)
+        optr[l] = o.ctypes.data
+        if want_levels and l:
+            m = np.zeros((lh, lw, 4), np.uint8)
+            lv.append(m)
+            lptr[l] = m.ctypes.data
+    p = make_params(pack_flags)
+    any_alpha = ctypes.c_uint32(0)
+    _check(lib().b200_uastc_encode_mipchain(ctypes.byref(img), n_levels, ctypes.byref(p), optr, lptr if want_levels else None, ctypes.byref(any_alpha)))
+    return outs, (lv if want_levels else None), bool(any_alpha.value)
 
 
 SWIZZLE_CODES = {"r": 1, "g": 2, "b": 3, "a": 4, "0": 5, "1": 6}   # swizzle_e (lib/src/basis_encode.cpp:77-84)

@@ -17,6 +17,17 @@ def _sources():
     return out
 
 
+def build_id():
+    """First 12 hex digits of the SHA-1 over every source the library is compiled from: names the build in bench lines and in
+    profiles/ncu_counters.json, so a counter measured on one build is never quoted for another."""
+    import hashlib
+    h = hashlib.sha1()
+    for f in sorted(_sources()):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:12]
+
+
 def stale():
     if not os.path.exists(LIB):
         return True
@@ -27,7 +38,7 @@ def stale():
 def build_ext(force=False, verbose=False):
     if not force and not stale():
         return LIB
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "uastc_b200.cu")]
+    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ['-DB200_BUILD_ID="%s"' % build_id()] + ["-o", LIB, os.path.join(CSRC, "uastc_b200.cu")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or r.returncode:
         sys.stderr.write(r.stdout + r.stderr)

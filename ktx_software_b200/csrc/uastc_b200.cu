@@ -824,4 +824,21 @@ __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, 
 
 __global__ void k_set_u64(unsigned long long* p, unsigned long long v) { *p = v; }
 
+// One mip level from the one above it: 2x2 box filter, per channel (a + b + c + d + 2) >> 2, source coordinates clamped to the
+// level (so a 1-texel-wide or -high level averages the pair it has: (a + c + 1) >> 1).  SURVEY 8(d)'s harness definition; the
+// CLI's float resampler (tools/ktx/command_create.cpp:1994-1996) is outside this path.  One thread per destination texel.
+__global__ void __launch_bounds__(256) k_mip_down(const uint32_t* __restrict__ src, uint32_t sw, uint32_t sh, uint32_t* __restrict__ dst, uint32_t dw, uint32_t dh) {
+  const uint64_t n = (uint64_t)dw * dh;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t y = (uint32_t)(i / dw), x = (uint32_t)(i - (uint64_t)y * dw);
+    const uint32_t x0 = min(2 * x, sw - 1), x1 = min(2 * x + 1, sw - 1), y0 = min(2 * y, sh - 1), y1 = min(2 * y + 1, sh - 1);
+    const uint32_t a = __ldg(src + (size_t)y0 * sw + x0), b = __ldg(src + (size_t)y0 * sw + x1);
+    const uint32_t c = __ldg(src + (size_t)y1 * sw + x0), d = __ldg(src + (size_t)y1 * sw + x1);
+    // two channels at a time in 16-bit lanes: sums <= 4 * 255 + 2 fit
+    const uint32_t rb = ((a & 0x00FF00FFu) + (b & 0x00FF00FFu) + (c & 0x00FF00FFu) + (d & 0x00FF00FFu) + 0x00020002u) >> 2;
+    const uint32_t ga = (((a >> 8) & 0x00FF00FFu) + ((b >> 8) & 0x00FF00FFu) + ((c >> 8) & 0x00FF00FFu) + ((d >> 8) & 0x00FF00FFu) + 0x00020002u) >> 2;
+    dst[i] = (rb & 0x00FF00FFu) | ((ga & 0x00FF00FFu) << 8);
+  }
+}
+
 #include "uastc_host.inc"

@@ -144,3 +144,26 @@ def test_rdo_with_hundreds_of_small_images(K):
         px = R.ref_extract_blocks(imgs[i])
         want = R.ref_rdo(R.ref_encode_blocks(px, flags), px, flags, 4, 4, lam=2.0)
         assert (outs[i] == want).all(), i
+
+
+def test_mipchain_from_base_level(K):
+    """b200_uastc_encode_mipchain: generated levels equal the harness's integer box filter byte for byte, and every level's
+    blocks equal b200_uastc_encode of that level (non-square, odd tail sizes included)."""
+    for w, h in ((256, 256), (200, 72), (37, 5)):
+        base = R.img_mix(w, h, 21)
+        n = max(w, h).bit_length()
+        outs, levels, alpha = K.encode_mipchain(base, n, 2, want_levels=True)
+        prev = base
+        for l in range(1, n):
+            a = prev.astype(np.uint16)
+            sh, sw = a.shape[:2]
+            lw, lh = max(1, w >> l), max(1, h >> l)
+            xs0 = np.minimum(2 * np.arange(lw), sw - 1); xs1 = np.minimum(2 * np.arange(lw) + 1, sw - 1)
+            ys0 = np.minimum(2 * np.arange(lh), sh - 1); ys1 = np.minimum(2 * np.arange(lh) + 1, sh - 1)
+            m = ((a[ys0][:, xs0] + a[ys0][:, xs1] + a[ys1][:, xs0] + a[ys1][:, xs1] + 2) >> 2).astype(np.uint8)
+            assert (levels[l - 1] == m).all(), (w, h, l)
+            prev = m
+        want, alpha2 = K.encode_images([base] + levels, 2)
+        assert alpha == alpha2
+        for l in range(n):
+            assert (outs[l] == want[l]).all(), (w, h, l)
