@@ -21,6 +21,7 @@
 #include "uastc_rdo.cuh"
 #include "uastc_to_rgba.cuh"
 #include "uastc_to_bcn.cuh"
+#include "uastc_jobs.cuh"
 
 namespace {
 
@@ -566,6 +567,288 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(con
       px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
     }
   });
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Job-based encode, levels 0-3 (uastc_jobs.cuh).  A CTA of EJ_T threads owns tiles of EJ_T blocks and walks each tile
+// through five stages, a CTA barrier between them:
+//   load      thread = block: texels -> shared memory, block class, compacted class lists
+//   estimate  warp-jobs over (estimate slot, 32 blocks of the slot's class group): partition patterns -> shared memory
+//   cells     warp-jobs over (cell slot, 32 blocks): one colour-cell fit per lane -> 24 B per cell in the CTA's scratch
+//   score     warp-jobs over (candidate slot, 32 blocks): assemble from the cells, score -> 8 B per candidate in the scratch
+//   finish    thread = block: the reference's selection rules over the stored scores, hints, pack, store
+// In the three middle stages a warp claims its next warp-job from a shared counter, so every warp of the CTA is busy until
+// the stage's jobs run out (the block-at-a-time kernel waited at every stage barrier for the warp that held the
+// most expensive blocks), the 32 lanes of a warp-job run the SAME mode on 32 different blocks (a block-at-a-time warp that
+// holds opaque and alpha blocks runs both mode lists one after the other, each under a partial mask), and a thread holds one
+// cell or one candidate at a time instead of the block's whole candidate list.  The scratch (cells + scores, 1080 B per block
+// of the tile) is written and read by the same CTA within one tile and reused for the next: it lives in L2.
+#ifndef EJ_THREADS
+#define EJ_THREADS 512
+#endif
+#ifndef EJ_MIN_CTAS
+#define EJ_MIN_CTAS 1
+#endif
+constexpr int EJ_T = EJ_THREADS;
+constexpr size_t EJ_SCRATCH_PER_CTA = (size_t)EJ_T * (ub::J_MAX_CELL_SLOTS * 24 + ub::J_MAX_CAND_SLOTS * 8);
+struct EjShared {
+  uint32_t px[EJ_T * 17];        // texel j of tile block b at [b * 17 + j]: conflict-free whether a warp reads one block or 32
+  uint8_t parts[EJ_T * ub::J_PARTS];
+  uint16_t list[EJ_T];           // tile blocks by class: [opaque][LA opaque][LA alpha][alpha] -> every group is one range
+  uint8_t cls[EJ_T];
+  uint32_t cnt[4];
+  uint32_t next[3];              // next unclaimed warp-job of the estimate / cell / score stage
+  unsigned long long tile;       // the tile this CTA works on
+};
+constexpr size_t EJ_SCRATCH_HEADER = 256;
+
+// Stage bookkeeping of one warp: how many warp-jobs every slot has (lane l holds slots l and l + 32), as inclusive prefix sums.
+struct EjStage {
+  uint32_t c_lo, c_hi, incl_lo, incl_hi, total;
+  __device__ __forceinline__ void build(uint32_t lane, uint32_t my_lo, uint32_t my_hi) {
+    c_lo = my_lo; c_hi = my_hi;
+    uint32_t v = my_lo;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v, o); if ((int)lane >= o) v += t; }
+    incl_lo = v;
+    const uint32_t tot_lo = __shfl_sync(0xFFFFFFFFu, v, 31);
+    v = my_hi;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, v, o); if ((int)lane >= o) v += t; }
+    incl_hi = tot_lo + v;
+    total = __shfl_sync(0xFFFFFFFFu, incl_hi, 31);
+  }
+  // warp-job w -> its slot and the index of its first block inside the slot's group
+  __device__ __forceinline__ void decode(uint32_t w, uint32_t& slot, uint32_t& r0) const {
+    const uint32_t m_lo = __ballot_sync(0xFFFFFFFFu, w < incl_lo);
+    uint32_t excl;
+    if (m_lo) { slot = __ffs(m_lo) - 1; excl = __shfl_sync(0xFFFFFFFFu, incl_lo - c_lo, slot); }
+    else { const uint32_t m_hi = __ballot_sync(0xFFFFFFFFu, w < incl_hi); const uint32_t l = __ffs(m_hi) - 1; slot = 32 + l; excl = __shfl_sync(0xFFFFFFFFu, incl_hi - c_hi, l); }
+    r0 = (w - excl) * 32;
+  }
+};
+
+template <bool PACKED>
+__global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const __grid_constant__ EncDescPack pack, const EncImageDesc* __restrict__ d_descs,
+                                                                         uint32_t n_images, uint64_t total_blocks, uint32_t flags,
+                                                                         unsigned int* __restrict__ any_alpha, uint2* scratch_all) {
+  extern __shared__ __align__(16) unsigned char ej_smem[];
+  EjShared& sh = *(EjShared*)ej_smem;
+  const EncImageDesc* descs = PACKED ? pack.d : d_descs;
+  const uint32_t tid = threadIdx.x, lane = tid & 31u;
+  unsigned long long* tile_counter = (unsigned long long*)scratch_all;          // zeroed by the host before the launch
+  uint2* cells = scratch_all + EJ_SCRATCH_HEADER / 8 + (size_t)blockIdx.x * (EJ_SCRATCH_PER_CTA / 8);   // [cell slot][3][EJ_T]
+  uint2* scores = cells + (size_t)ub::J_MAX_CELL_SLOTS * 3 * EJ_T;                // [candidate slot][EJ_T]
+  ub::EncCfg cfg = ub::enc_cfg_from_flags(flags);
+  // enabled slots (uniform over the launch)
+  const uint32_t en_cands = ub::j_enabled_cands(cfg.mode_mask);
+  uint64_t en_cells = 0;
+  for (uint32_t gc = 0; gc < ub::J_NUM_CELL; gc++) if ((en_cands >> (ub::UBT(j_cell)[gc] & 31u)) & 1u) en_cells |= 1ull << gc;
+  uint32_t en_est = 0;
+  for (uint32_t e = 0; e < ub::J_NUM_EST; e++) if ((cfg.mode_mask >> (ub::UBT(j_est)[e] & 31u)) & 1u) en_est |= 1u << e;
+
+  const uint64_t n_tiles = (total_blocks + EJ_T - 1) / EJ_T;
+  for (;;) {
+    // tiles are claimed from a global counter: tile costs differ several-fold (solid / opaque / alpha content), a fixed share
+    // per CTA leaves SMs idle behind the CTA that drew the expensive tiles
+    if (tid == 0) sh.tile = atomicAdd(tile_counter, 1ull);
+    if (tid < 4) sh.cnt[tid] = 0;
+    if (tid < 3) sh.next[tid] = 0;
+    __syncthreads();
+    const uint64_t tile = sh.tile;
+    if (tile >= n_tiles) break;   // uniform per CTA
+    const uint64_t base = tile * EJ_T;
+    // ---- load: thread = block
+    const uint64_t i = base + tid;
+    const bool live = i < total_blocks;
+    uint4* dst = nullptr;
+    uint32_t cls = 0;
+    if (live) {
+      uint32_t lo = 0, hi = n_images - 1;  // last image whose first_block <= i
+      while (lo < hi) { const uint32_t mid = (lo + hi + 1) >> 1; if (descs[mid].first_block <= i) lo = mid; else hi = mid - 1; }
+      const EncImageDesc d = descs[lo];
+      uint32_t px[16];
+      uint32_t amin = 255;
+      if (d.w == 0) {   // pre-gathered 64-byte texel blocks (b200_uastc_encode_blocks_dev)
+        const uint64_t k = i - d.first_block;
+        dst = d.out + k;
+#pragma unroll
+        for (uint32_t y = 0; y < 4; y++) {
+          const uint4 v = __ldg((const uint4*)d.img + k * 4 + y);
+          px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
+        }
+      } else {
+        const uint64_t k = block_of_thread(i - d.first_block, d.bx, (d.h + 3) / 4);
+        dst = d.out + k;
+        const uint32_t x0 = (uint32_t)(k % d.bx) * 4, y0 = (uint32_t)(k / d.bx) * 4;
+        if (x0 + 4 <= d.w && y0 + 4 <= d.h && !(d.pitch & 15u) && !((uintptr_t)d.img & 15u)) {
+#pragma unroll
+          for (uint32_t y = 0; y < 4; y++) {
+            const uint4 v = __ldg((const uint4*)(d.img + (size_t)(y0 + y) * d.pitch + (size_t)x0 * 4));
+            px[4 * y] = v.x; px[4 * y + 1] = v.y; px[4 * y + 2] = v.z; px[4 * y + 3] = v.w;
+          }
+        } else {
+          for (uint32_t y = 0; y < 4; y++)
+            for (uint32_t x = 0; x < 4; x++) {
+              const uint32_t sx = min(x0 + x, d.w - 1), sy = min(y0 + y, d.h - 1);
+              px[4 * y + x] = __ldg((const uint32_t*)(d.img + (size_t)sy * d.pitch + (size_t)sx * 4));
+            }
+        }
+      }
+#pragma unroll
+      for (uint32_t j = 0; j < 16; j++) { sh.px[tid * 17 + j] = px[j]; amin = min(amin, px[j] >> 24); }
+      if (amin < 255 && any_alpha) atomicOr(any_alpha, 1u);
+      cls = ub::j_classify(px, cfg);
+    }
+    sh.cls[tid] = (uint8_t)cls;
+    // class lists: rank inside the class from a warp-aggregated shared atomic
+    const uint32_t ci = !(cls & ub::J_CLS_LIVE) ? 4u : ((cls & ub::J_CLS_LA) ? ((cls & ub::J_CLS_ALPHA) ? 2u : 1u) : ((cls & ub::J_CLS_ALPHA) ? 3u : 0u));
+    uint32_t my_rank = 0;
+    {
+      const uint32_t peers = __match_any_sync(0xFFFFFFFFu, ci);
+      const uint32_t leader = __ffs(peers) - 1;
+      uint32_t b0 = 0;
+      if (lane == leader && ci < 4u) b0 = atomicAdd(&sh.cnt[ci], __popc(peers));
+      b0 = __shfl_sync(0xFFFFFFFFu, b0, leader);
+      my_rank = b0 + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    const uint32_t c0 = sh.cnt[0], c1 = sh.cnt[1], c2 = sh.cnt[2], c3 = sh.cnt[3];
+    if (ci < 4u) sh.list[(ci == 0 ? 0u : ci == 1 ? c0 : ci == 2 ? c0 + c1 : c0 + c1 + c2) + my_rank] = (uint16_t)tid;
+    // group -> range of the list: LA = [c0, c0 + c1 + c2), opaque = [0, c0 + c1), alpha = [c0 + c1, all)
+    const uint32_t g_start[3] = {c0, 0u, c0 + c1}, g_count[3] = {c1 + c2, c0 + c1, c2 + c3};
+    auto warps_of = [&](uint32_t g) { return (g_count[g] + 31u) >> 5; };
+    __syncthreads();
+
+    // ---- estimate jobs
+    {
+      EjStage stg;
+      stg.build(lane, (lane < ub::J_NUM_EST && ((en_est >> lane) & 1u)) ? warps_of(ub::UBT(j_est)[lane] >> 22) : 0u, 0u);
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[0], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= stg.total) break;
+        uint32_t e, r0;
+        stg.decode(w, e, r0);
+        const uint32_t g = ub::UBT(j_est)[e] >> 22, r = r0 + lane;
+        if (r < g_count[g]) {
+          const uint32_t b = sh.list[g_start[g] + r];
+          uint32_t px[16];
+#pragma unroll
+          for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+          ub::j_run_estimate(e, px, sh.parts + b * ub::J_PARTS);
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- cell jobs
+    {
+      EjStage stg;
+      const uint32_t s_hi = lane + 32u;
+      stg.build(lane, ((en_cells >> lane) & 1ull) ? warps_of(ub::jc_group(ub::UBT(j_cand)[ub::UBT(j_cell)[lane] & 31u])) : 0u,
+                (s_hi < ub::J_NUM_CELL && ((en_cells >> s_hi) & 1ull)) ? warps_of(ub::jc_group(ub::UBT(j_cand)[ub::UBT(j_cell)[s_hi] & 31u])) : 0u);
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[1], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= stg.total) break;
+        uint32_t gc, r0;
+        stg.decode(w, gc, r0);
+        const uint32_t g = ub::jc_group(ub::UBT(j_cand)[ub::UBT(j_cell)[gc] & 31u]), r = r0 + lane;
+        if (r < g_count[g]) {
+          const uint32_t b = sh.list[g_start[g] + r];
+          uint32_t px[16];
+#pragma unroll
+          for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+          alignas(4) uint8_t parts[ub::J_PARTS];
+#pragma unroll
+          for (uint32_t j = 0; j < ub::J_PARTS / 4; j++) ((uint32_t*)parts)[j] = ((const uint32_t*)(sh.parts + b * ub::J_PARTS))[j];
+          ub::CellOut o;
+          ub::j_run_cell(gc, px, parts, cfg, o);
+          uint2* q = cells + (size_t)ub::j_cell_local(gc) * 3 * EJ_T + b;
+          q[0] = make_uint2(o.astc_lo, o.astc_hi);
+          q[EJ_T] = ((const uint2*)o.sel)[0];
+          q[2 * EJ_T] = ((const uint2*)o.sel)[1];
+        }
+      }
+    }
+    __syncthreads();   // (global scratch written above is read below by other threads of this CTA: the barrier orders it)
+
+    // ---- candidate jobs: assemble + score
+    {
+      EjStage stg;
+      stg.build(lane, ((en_cands >> lane) & 1u) ? warps_of(ub::jc_group(ub::UBT(j_cand)[lane])) : 0u, 0u);
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[2], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= stg.total) break;
+        uint32_t gs, r0;
+        stg.decode(w, gs, r0);
+        const uint32_t d = ub::UBT(j_cand)[gs], g = ub::jc_group(d), r = r0 + lane;
+        if (r < g_count[g]) {
+          const uint32_t b = sh.list[g_start[g] + r];
+          uint32_t px[16];
+#pragma unroll
+          for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+          alignas(4) uint8_t parts[ub::J_PARTS];
+#pragma unroll
+          for (uint32_t j = 0; j < ub::J_PARTS / 4; j++) ((uint32_t*)parts)[j] = ((const uint32_t*)(sh.parts + b * ub::J_PARTS))[j];
+          ub::CellOut co[3];
+          const uint32_t nc = ub::jc_cells(d);
+          for (uint32_t s = 0; s < nc; s++) {
+            const uint2* q = cells + (size_t)ub::j_cell_local(ub::jc_cell0(d) + s) * 3 * EJ_T + b;
+            const uint2 a = q[0], s0 = q[EJ_T], s1 = q[2 * EJ_T];
+            co[s].astc_lo = a.x; co[s].astc_hi = a.y;
+            ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
+          }
+          ub::Candidate c;
+          ub::j_assemble(gs, parts, co, c);
+          uint32_t overall;
+          float uerr;
+          ub::j_score(px, c, sh.cls[b], flags, overall, uerr);
+          scores[(size_t)ub::j_cand_local(gs) * EJ_T + b] = make_uint2(overall, __float_as_uint(uerr));
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---- finish: thread = block
+    {
+      const bool solid = cls == ub::J_CLS_SOLID;
+      ub::Candidate win;
+      uint32_t px[16];
+#pragma unroll
+      for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[tid * 17 + j];
+      if (live && !solid) {
+        const uint32_t mine = ub::j_block_cands(cls, en_cands);
+        uint32_t overall[ub::J_MAX_CAND_SLOTS], n = 0;
+        float uerr[ub::J_MAX_CAND_SLOTS];
+        uint8_t modes[ub::J_MAX_CAND_SLOTS], slots[ub::J_MAX_CAND_SLOTS];
+        for (uint32_t m = mine; m; m &= m - 1) {
+          const uint32_t gs = __ffs(m) - 1;
+          const uint2 v = scores[(size_t)ub::j_cand_local(gs) * EJ_T + tid];
+          overall[n] = v.x; uerr[n] = __uint_as_float(v.y);
+          modes[n] = (uint8_t)ub::jc_mode(ub::UBT(j_cand)[gs]); slots[n] = (uint8_t)gs; n++;
+        }
+        const uint32_t gs = slots[ub::j_select(n, overall, uerr, modes, flags)];
+        const uint32_t d = ub::UBT(j_cand)[gs], nc = ub::jc_cells(d);
+        ub::CellOut co[3];
+        for (uint32_t s = 0; s < nc; s++) {
+          const uint2* q = cells + (size_t)ub::j_cell_local(ub::jc_cell0(d) + s) * 3 * EJ_T + tid;
+          const uint2 a = q[0], s0 = q[EJ_T], s1 = q[2 * EJ_T];
+          co[s].astc_lo = a.x; co[s].astc_hi = a.y;
+          ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
+        }
+        ub::j_assemble(gs, sh.parts + tid * ub::J_PARTS, co, win);
+      }
+      const ub::Bits128 r = ub::j_finish(px, flags, &win, live, solid, ENC_FINE_SYNC);
+      if (live) *dst = make_uint4((uint32_t)r.lo, (uint32_t)(r.lo >> 32), (uint32_t)r.hi, (uint32_t)(r.hi >> 32));
+    }
+    __syncthreads();
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -158,68 +158,108 @@ UB_FN uint32_t sum_unq_rgb(uint32_t range, const uint8_t* ep, uint32_t which) {
   return astc_unquant(range, ep[0 + which]) + astc_unquant(range, ep[2 + which]) + astc_unquant(range, ep[4 + which]);
 }
 
-// "N subsets, one plane": modes 0,1,2,3,4,5,7,9,10,12,14,15,16,18.
-//   px     the 16 texels the cells see (already (l,0,0,a) for LA modes)
-//   kind   partition family (0 = single subset)
-UB_BIG void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const uint32_t* px, const EncCfg& cfg, Candidate& c,
-                             const uint8_t* force_sel = nullptr) {
-  const uint32_t d = UBT(uastc_mode_desc)[mode];
-  const uint32_t subsets = md_subsets(d), comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
-  const uint32_t pat = kind ? pattern_of(kind, pattern) : 0u;
-  c.mode = mode; c.pattern = pattern; c.ccs = 0;
+// One colour cell's result as the candidate assembly needs it (24 bytes: what travels between the cell jobs and the
+// candidate jobs of the job-based encode kernel).
+struct CellOut {
+  uint32_t astc_lo, astc_hi;   // endpoints as BISE codes, r | g<<8 | b<<16 | a<<24
+  alignas(8) uint8_t sel[16];  // weights of the cell's texels, in texel order
+};
+
+UB_FN void candidate_init(uint32_t mode, uint32_t pattern, uint32_t ccs, Candidate& c) {
+  c.mode = mode; c.pattern = pattern; c.ccs = ccs;
   for (uint32_t i = 0; i < 18; i++) c.ep[i] = 0;
   for (uint32_t i = 0; i < 32; i++) c.w[i] = 0;
+}
+
+// "N subsets, one plane": modes 0,1,2,3,4,5,7,9,10,12,14,15,16,18.  Subset s of the candidate = one cell job:
+//   px     the 16 texels the cells see (already (l,0,0,a) for LA modes)
+//   kind   partition family (0 = single subset)
+UB_BIG void single_plane_cell(uint32_t mode, int kind, uint32_t pattern, uint32_t s, const uint32_t* px, const EncCfg& cfg, CellOut& o,
+                             const uint8_t* force_sel = nullptr) {
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
+  const uint32_t pat = kind ? pattern_of(kind, pattern) : 0u;
   CccParams p;
   p.nw = nw; p.range = range; p.has_alpha = (comps != 3); p.force_sel = force_sel;
   p.uber_level = cfg.uber_level; p.ls_passes = cfg.ls_passes;
+  uint32_t sub[16], n = 0;
+  for (uint32_t i = 0; i < 16; i++) if (((pat >> (2 * i)) & 3u) == s) { sub[n] = px[i]; n++; }
+  p.n = n;
+  CccResults r;
+  color_cell_compression(p, sub, r);
+  o.astc_lo = r.astc_lo; o.astc_hi = r.astc_hi;
+#pragma unroll
+  for (uint32_t i = 0; i < 4; i++) ((uint32_t*)o.sel)[i] = ((const uint32_t*)r.sel)[i];
+}
+
+// ... and its place in the candidate: endpoint codes of subset s (with the ASTC blue-contraction ordering: s1 < s0 swaps the
+// endpoints and inverts the weights) and the weights of the subset's texels.
+UB_FN void single_plane_place(uint32_t mode, int kind, uint32_t pattern, uint32_t s, const CellOut& r, Candidate& c, bool forced) {
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
+  const uint32_t pat = kind ? pattern_of(kind, pattern) : 0u;
+  uint8_t* ep = c.ep + s * comps * 2;
+  if (comps == 2) {
+    ep[0] = (uint8_t)ch(r.astc_lo, 0); ep[1] = (uint8_t)ch(r.astc_hi, 0);
+    ep[2] = (uint8_t)ch(r.astc_lo, 3); ep[3] = (uint8_t)ch(r.astc_hi, 3);
+  } else {
+    for (uint32_t k = 0; k < comps; k++) { ep[2 * k] = (uint8_t)ch(r.astc_lo, k); ep[2 * k + 1] = (uint8_t)ch(r.astc_hi, k); }
+  }
+  bool invert = false;
+  if (comps >= 3 && !forced) {
+    if (sum_unq_rgb(range, ep, 1) < sum_unq_rgb(range, ep, 0)) {
+      for (uint32_t k = 0; k < comps; k++) { const uint8_t t = ep[2 * k]; ep[2 * k] = ep[2 * k + 1]; ep[2 * k + 1] = t; }
+      invert = true;
+    }
+  }
+  uint32_t j = 0;
+  for (uint32_t i = 0; i < 16; i++)
+    if (((pat >> (2 * i)) & 3u) == s) { c.w[i] = (uint8_t)(invert ? (nw - 1 - r.sel[j]) : r.sel[j]); j++; }
+}
+
+UB_BIG void mode_single_plane(uint32_t mode, int kind, uint32_t pattern, const uint32_t* px, const EncCfg& cfg, Candidate& c,
+                             const uint8_t* force_sel = nullptr) {
+  const uint32_t subsets = md_subsets(UBT(uastc_mode_desc)[mode]);
+  candidate_init(mode, pattern, 0, c);
   for (uint32_t s = 0; s < subsets; s++) {
-    uint32_t sub[16], idx[16], n = 0;
-    for (uint32_t i = 0; i < 16; i++) if (((pat >> (2 * i)) & 3u) == s) { sub[n] = px[i]; idx[n] = i; n++; }
-    p.n = n;
-    CccResults r;
-    color_cell_compression(p, sub, r);
-    uint8_t* ep = c.ep + s * comps * 2;
-    if (comps == 2) {
-      ep[0] = (uint8_t)ch(r.astc_lo, 0); ep[1] = (uint8_t)ch(r.astc_hi, 0);
-      ep[2] = (uint8_t)ch(r.astc_lo, 3); ep[3] = (uint8_t)ch(r.astc_hi, 3);
-    } else {
-      for (uint32_t k = 0; k < comps; k++) { ep[2 * k] = (uint8_t)ch(r.astc_lo, k); ep[2 * k + 1] = (uint8_t)ch(r.astc_hi, k); }
-    }
-    bool invert = false;
-    if (comps >= 3 && !force_sel) {
-      if (sum_unq_rgb(range, ep, 1) < sum_unq_rgb(range, ep, 0)) {
-        for (uint32_t k = 0; k < comps; k++) { const uint8_t t = ep[2 * k]; ep[2 * k] = ep[2 * k + 1]; ep[2 * k + 1] = t; }
-        invert = true;
-      }
-    }
-    for (uint32_t j = 0; j < n; j++) c.w[idx[j]] = (uint8_t)(invert ? (nw - 1 - r.sel[j]) : r.sel[j]);
+    CellOut o;
+    single_plane_cell(mode, kind, pattern, s, px, cfg, o, force_sel);
+    single_plane_place(mode, kind, pattern, s, o, c, force_sel != nullptr);
   }
 }
 
-// "one subset, two planes": modes 6 (rot 0..2), 11 and 13 (rot 0..3), 17 (L plane + A plane).
-UB_BIG void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, const EncCfg& cfg, Candidate& c) {
+// "one subset, two planes": modes 6 (rot 0..2), 11 and 13 (rot 0..3), 17 (L plane + A plane).  Plane 0 = the colour
+// plane with the rotated channel replaced, plane 1 = the rotated channel alone: two cell jobs of 16 texels.
+UB_BIG void dual_plane_cell(uint32_t mode, uint32_t rot, uint32_t plane, const uint32_t* px, const EncCfg& cfg, CellOut& o) {
   const uint32_t d = UBT(uastc_mode_desc)[mode];
-  const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
-  uint32_t p0[16], p1[16];
+  const uint32_t range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
+  uint32_t q[16];
   for (uint32_t i = 0; i < 16; i++) {
     const uint32_t v = px[i];
     if (mode == 17) {
-      p1[i] = ch(v, 3) * 0x010101u | 0xFF000000u;
-      p0[i] = ch(v, 0) * 0x010101u | 0xFF000000u;
+      q[i] = ch(v, plane ? 3 : 0) * 0x010101u | 0xFF000000u;
+    } else if (plane) {
+      q[i] = ch(v, rot) * 0x010101u | 0xFF000000u;
     } else {
-      p1[i] = ch(v, rot) * 0x010101u | 0xFF000000u;
       uint32_t t = v;
       if (mode == 6) t = (t & ~(255u << (8 * rot))) | (255u << (8 * rot));
       else { if (rot < 3) t = (t & ~(255u << (8 * rot))) | (ch(v, 3) << (8 * rot)); t |= 0xFF000000u; }
-      p0[i] = t;
+      q[i] = t;
     }
   }
   CccParams p;
   p.n = 16; p.nw = nw; p.range = range; p.has_alpha = false; p.force_sel = nullptr;
   p.uber_level = cfg.uber_level; p.ls_passes = cfg.ls_passes;
-  CccResults r0, r1;
-  color_cell_compression(p, p0, r0);
-  color_cell_compression(p, p1, r1);
+  CccResults r;
+  color_cell_compression(p, q, r);
+  o.astc_lo = r.astc_lo; o.astc_hi = r.astc_hi;
+#pragma unroll
+  for (uint32_t i = 0; i < 4; i++) ((uint32_t*)o.sel)[i] = ((const uint32_t*)r.sel)[i];
+}
+
+UB_FN void dual_plane_assemble(uint32_t mode, uint32_t rot, const CellOut& r0, const CellOut& r1, Candidate& c) {
+  const uint32_t d = UBT(uastc_mode_desc)[mode];
+  const uint32_t comps = md_comps(d), range = md_endpoint_range(d), nw = 1u << md_weight_bits(d);
   c.mode = mode; c.pattern = 0; c.ccs = (mode == 17) ? 3u : rot;
   for (uint32_t i = 0; i < 18; i++) c.ep[i] = 0;
   bool invert = false;
@@ -228,7 +268,7 @@ UB_BIG void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, con
     c.ep[2] = (uint8_t)ch(r1.astc_lo, 0); c.ep[3] = (uint8_t)ch(r1.astc_hi, 0);
   } else {
     for (uint32_t k = 0; k < 3; k++) {
-      const CccResults& rr = (rot == k) ? r1 : r0;
+      const CellOut& rr = (rot == k) ? r1 : r0;
       c.ep[2 * k] = (uint8_t)ch(rr.astc_lo, k); c.ep[2 * k + 1] = (uint8_t)ch(rr.astc_hi, k);
     }
     if (comps == 4) {
@@ -244,6 +284,13 @@ UB_BIG void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, con
     c.w[2 * i] = (uint8_t)(invert ? (nw - 1 - r0.sel[i]) : r0.sel[i]);
     c.w[2 * i + 1] = (uint8_t)(invert ? (nw - 1 - r1.sel[i]) : r1.sel[i]);
   }
+}
+
+UB_BIG void mode_dual_plane(uint32_t mode, uint32_t rot, const uint32_t* px, const EncCfg& cfg, Candidate& c) {
+  CellOut r0, r1;
+  dual_plane_cell(mode, rot, 0, px, cfg, r0);
+  dual_plane_cell(mode, rot, 1, px, cfg, r1);
+  dual_plane_assemble(mode, rot, r0, r1, c);
 }
 
 }  // namespace ub

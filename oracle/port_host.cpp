@@ -7,6 +7,7 @@
 #include "../ktx_software_b200/csrc/uastc_encode.cuh"
 #include "../ktx_software_b200/csrc/uastc_to_rgba.cuh"
 #include "../ktx_software_b200/csrc/uastc_to_bcn.cuh"
+#include "../ktx_software_b200/csrc/uastc_jobs.cuh"
 
 #define PORT_API extern "C" __attribute__((visibility("default")))
 
@@ -81,6 +82,16 @@ PORT_API void port_encode_blocks(const uint8_t* px, uint64_t n, uint32_t flags, 
     uint32_t p[16];
     memcpy(p, px + i * 64, 64);
     const ub::Bits128 b = ub::encode_uastc_block(p, flags, cands, overall, uerr);
+    memcpy(out + i * 16, &b, 16);
+  }
+}
+
+// The same encode cut into jobs (csrc/uastc_jobs.cuh: what k_encode_jobs computes), one block after the other.  Levels 0-3.
+PORT_API void port_encode_blocks_jobs(const uint8_t* px, uint64_t n, uint32_t flags, uint8_t* out) {
+  for (uint64_t i = 0; i < n; i++) {
+    uint32_t p[16];
+    memcpy(p, px + i * 64, 64);
+    const ub::Bits128 b = ub::encode_uastc_block_jobs(p, flags);
     memcpy(out + i * 16, &b, 16);
   }
 }

@@ -297,3 +297,21 @@ def test_port_hinted_targets_vs_reference_images(maker, seed):
                     want, ok = R.ref_transcode_hinted(blocks, tf, fl, has_alpha)
                     got, bad = R.port_transcode_hinted(blocks, tf, fl, has_alpha)
                     assert ok and bad == -1 and (got == want).all(), (level, tf, fl, has_alpha)
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("flags", [0, 1, 2, 3, 2 | 8, 2 | 16, 2 | 512, 1 | 64, 3 | 128, 2 | 256])
+def test_job_decomposition_matches_reference(flags):
+    """csrc/uastc_jobs.cuh (estimate / cell / candidate / block jobs: what k_encode_jobs computes), walked one block after the
+    other by the host build, against the unmodified reference encoder."""
+    import ctypes
+    f = R.port().port_encode_blocks_jobs
+    f.argtypes = [R._u8p, ctypes.c_uint64, ctypes.c_uint32, R._u8p]
+    f.restype = None
+    n_img = 96 if (flags & 7) == 3 else 128
+    px = np.concatenate([R.ref_extract_blocks(R.img_mix(n_img, n_img, 1)), R.adversarial_blocks(3, 24), R.ref_extract_blocks(R.img_noise(32, 32, 2))])
+    out = np.zeros((len(px), 16), np.uint8)
+    f(R._p(px), len(px), flags, R._p(out))
+    want = R.ref_encode_blocks(px, flags)
+    bad = np.nonzero((out != want).any(1))[0]
+    assert len(bad) == 0, (flags, bad[:8])
