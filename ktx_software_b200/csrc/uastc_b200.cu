@@ -584,7 +584,7 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(con
 // cell or one candidate at a time instead of the block's whole candidate list.  The scratch (cells + scores, 1080 B per block
 // of the tile) is written and read by the same CTA within one tile and reused for the next: it lives in L2.
 #ifndef EJ_THREADS
-#define EJ_THREADS 512
+#define EJ_THREADS 768
 #endif
 #ifndef EJ_MIN_CTAS
 #define EJ_MIN_CTAS 1
