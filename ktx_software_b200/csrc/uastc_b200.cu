@@ -211,7 +211,7 @@ __device__ __forceinline__ bool hinted_form_dispatch(uint32_t mode, const ub::Bi
 // R11 / RG11; 8 or 16 bytes per block).  KIND is a template parameter so each target's kernel holds only its own packer (one kernel with a run-time
 // switch over six packers paid the register and spill cost of the largest, encode_bc1, in every target).
 template <int TARGET, int KIND = 0>
-__global__ void __launch_bounds__(XT_THREADS) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
+__global__ void __launch_bounds__(XT_THREADS, XT_CTAS_PER_SM) k_transcode_tiled(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t n_blocks,
                                                                 unsigned long long* __restrict__ first_bad, const XtImage im) {
   constexpr int TILE = xt_tile(TARGET), PER_THREAD = TILE / XT_THREADS;
   extern __shared__ __align__(128) unsigned char xt_smem[];

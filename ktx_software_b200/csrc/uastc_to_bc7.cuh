@@ -38,18 +38,20 @@ UB_FN void pbit_entry(uint32_t which, uint32_t u, float& e0, float& e1, uint32_t
 template <bool TS = false>
 UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
   const uint32_t tab = wide ? 0u : 1u;
-  uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
+  uint32_t ca[4], cb[4];   // per channel: code for p = 0 | code for p = 1 << 8
   float e_lo0 = 0, e_lo1 = 0, e_hi0 = 0, e_hi1 = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++) {
     float a0, a1, b0, b1;
-    uint32_t ca, cb;
-    pbit_entry<TS>(tab, px_c(u_lo, c), a0, a1, ca);
-    pbit_entry<TS>(tab, px_c(u_hi, c), b0, b1, cb);
-    q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
-    q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
+    pbit_entry<TS>(tab, px_c(u_lo, c), a0, a1, ca[c]);
+    pbit_entry<TS>(tab, px_c(u_hi, c), b0, b1, cb[c]);
     if (c < total_comps) { e_lo0 = f_add(e_lo0, a0); e_lo1 = f_add(e_lo1, a1); e_hi0 = f_add(e_hi0, b0); e_hi1 = f_add(e_hi1, b1); }
   }
+  // gather the four channels' codes with byte permutes: x = {c0.p0, c1.p0, c0.p1, c1.p1}, y likewise for channels 2, 3
+  const uint32_t xa = ub_prmt(ca[0], ca[1], 0x5140u), ya = ub_prmt(ca[2], ca[3], 0x5140u);
+  const uint32_t xb = ub_prmt(cb[0], cb[1], 0x5140u), yb = ub_prmt(cb[2], cb[3], 0x5140u);
+  const uint32_t q_lo0 = ub_prmt(xa, ya, 0x5410u), q_lo1 = ub_prmt(xa, ya, 0x7632u);
+  const uint32_t q_hi0 = ub_prmt(xb, yb, 0x5410u), q_hi1 = ub_prmt(xb, yb, 0x7632u);
   // the reference takes p = 0 first (its error is always below the 1e+9 start value) and p = 1 only if strictly better
   const bool lo1 = e_lo1 < e_lo0, hi1 = e_hi1 < e_hi0;
   out_lo = lo1 ? q_lo1 : q_lo0;
@@ -61,18 +63,19 @@ UB_FN void unique_pbits(uint32_t total_comps, bool wide, uint32_t u_lo, uint32_t
 template <bool TS = false>
 UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t& out_hi, uint32_t& pb) {
   u_lo |= 0xFF000000u; u_hi |= 0xFF000000u;
-  uint32_t q_lo0 = 0, q_lo1 = 0, q_hi0 = 0, q_hi1 = 0;
+  uint32_t ca[4], cb[4];
   float err0 = 0, err1 = 0;
 #pragma unroll
   for (uint32_t c = 0; c < 4; c++) {
     float a0, a1, b0, b1;
-    uint32_t ca, cb;
-    pbit_entry<TS>(2u, px_c(u_lo, c), a0, a1, ca);
-    pbit_entry<TS>(2u, px_c(u_hi, c), b0, b1, cb);
-    q_lo0 |= (ca & 255u) << (8 * c); q_lo1 |= (ca >> 8) << (8 * c);
-    q_hi0 |= (cb & 255u) << (8 * c); q_hi1 |= (cb >> 8) << (8 * c);
+    pbit_entry<TS>(2u, px_c(u_lo, c), a0, a1, ca[c]);
+    pbit_entry<TS>(2u, px_c(u_hi, c), b0, b1, cb[c]);
     if (c < 3) { err0 = f_add(err0, f_add(a0, b0)); err1 = f_add(err1, f_add(a1, b1)); }
   }
+  const uint32_t xa = ub_prmt(ca[0], ca[1], 0x5140u), ya = ub_prmt(ca[2], ca[3], 0x5140u);
+  const uint32_t xb = ub_prmt(cb[0], cb[1], 0x5140u), yb = ub_prmt(cb[2], cb[3], 0x5140u);
+  const uint32_t q_lo0 = ub_prmt(xa, ya, 0x5410u), q_lo1 = ub_prmt(xa, ya, 0x7632u);
+  const uint32_t q_hi0 = ub_prmt(xb, yb, 0x5410u), q_hi1 = ub_prmt(xb, yb, 0x7632u);
   const bool p1 = err1 < err0;
   pb = p1 ? 3u : 0u;
   out_lo = p1 ? q_lo1 : q_lo0;
@@ -80,10 +83,42 @@ UB_FN void shared_pbits(uint32_t u_lo, uint32_t u_hi, uint32_t& out_lo, uint32_t
 }
 
 // Re-pack the UASTC weights (entries of wb bits) of one plane into `ob`-bit BC7 selectors through a tiny value map.
-// plane_stride = 1 (single plane) or 2; plane = 0/1.  map4 holds up to 32 4-bit outputs? no: see callers.
+// plane_stride = 1 (single plane) or 2; plane = 0/1.
+//   kind: 0 identity, 1 = 5->4 bits, 2 = 2->4 bits, 3 = 3->4 bits, 4 = 1->2 bits (0 / 3)
+// All 16 fields move at once (SIMD inside a 64-bit register) for every case but the 5-bit one: the per-texel loop was 11 % of the
+// BC7 transcode kernel's instructions.
+UB_FN uint64_t spread2to4(uint64_t x) {   // sixteen 2-bit fields -> the low 2 bits of sixteen nibbles
+  x = (x | (x << 16)) & 0x0000FFFF0000FFFFull;
+  x = (x | (x << 8)) & 0x00FF00FF00FF00FFull;
+  x = (x | (x << 4)) & 0x0F0F0F0F0F0F0F0Full;
+  x = (x | (x << 2)) & 0x3333333333333333ull;
+  return x;
+}
+UB_FN uint64_t spread3to4(uint64_t x) {   // sixteen 3-bit fields (48 bits) -> the low 3 bits of sixteen nibbles
+  x = (x & 0x0000000000FFFFFFull) | ((x & 0x0000FFFFFF000000ull) << 8);
+  x = (x & 0x00000FFF00000FFFull) | ((x & 0x00FFF00000FFF000ull) << 4);
+  x = (x & 0x003F003F003F003Full) | ((x & 0x0FC00FC00FC00FC0ull) << 2);
+  x = (x & 0x0707070707070707ull) | ((x & 0x3838383838383838ull) << 1);
+  return x;
+}
+UB_FN uint64_t even2(uint64_t x) {        // the even 2-bit fields of 32 -> sixteen packed 2-bit fields
+  x &= 0x3333333333333333ull;
+  x = (x | (x >> 2)) & 0x0F0F0F0F0F0F0F0Full;
+  x = (x | (x >> 4)) & 0x00FF00FF00FF00FFull;
+  x = (x | (x >> 8)) & 0x0000FFFF0000FFFFull;
+  x = (x | (x >> 16)) & 0x00000000FFFFFFFFull;
+  return x;
+}
 UB_FN uint64_t remap_selectors(const UnpackedUastc& u, uint32_t desc, uint32_t plane_stride, uint32_t plane, uint32_t ob, int kind) {
-  // kind: 0 identity, 1 = 5->4 bits, 2 = 2->4 bits, 3 = 3->4 bits, 4 = 1->2 bits (0 / 3)
   const uint32_t wb = md_weight_bits(desc);
+  if (plane_stride == 1 && kind == 0 && wb == ob) return u.w.lo;                       // same width: the packed weights are the selectors
+  if (plane_stride == 1 && kind == 2 && wb == 2 && ob == 4) return spread2to4(u.w.lo) * 5ull;        // 0,5,10,15 per nibble, no carries
+  if (plane_stride == 1 && kind == 3 && wb == 3 && ob == 4) {                          // 0,2,4,6,9,11,13,15 == 2w + (w >> 2)
+    const uint64_t x = spread3to4(u.w.lo);
+    return (x << 1) + ((x >> 2) & 0x1111111111111111ull);
+  }
+  if (plane_stride == 2 && kind == 0 && wb == 2 && ob == 2) return even2(u.w.lo >> (2 * plane));
+  if (plane_stride == 2 && kind == 4 && wb == 1 && ob == 2) return ((u.w.lo >> plane) & 0x55555555ull) * 3ull;   // weight w at bit 2i -> w ? 3 : 0
   uint64_t r = 0;
 #pragma unroll
   for (uint32_t i = 0; i < 16; i++) {
@@ -357,8 +392,11 @@ UB_FN uint32_t bc7_alpha_prec(uint32_t m) { return (0x57860000u >> (4 * m)) & 15
 UB_FN uint32_t bc7_index_bits(uint32_t m) { return (0x24222233u >> (4 * m)) & 15u; }   // 3,3,2,2,2,2,4,2
 
 // encode_bc7_block (XC:14292-14459) for the BC7 modes UASTC maps to (1,2,3,5,6,7; index_selector is always 0).
-UB_FN Bits128 bc7_pack(Bc7Build& o) {
-  const uint32_t m = o.mode;
+// BM >= 0: the BC7 mode is a compile-time constant (the mode-specialised transcoders): every field position folds, and the block
+// is assembled in 32-bit words (BitWriter32).  BM < 0: the mode is o.mode.
+template <int BM, typename WRITER>
+UB_FN Bits128 bc7_pack_t(Bc7Build& o) {
+  const uint32_t m = (BM >= 0) ? (uint32_t)BM : o.mode;
   const uint32_t subsets = bc7_subsets(m);
   const uint32_t ib = bc7_index_bits(m);
   uint32_t pat = 0;
@@ -397,7 +435,7 @@ UB_FN Bits128 bc7_pack(Bc7Build& o) {
     }
   }
 
-  BitWriter bw;
+  WRITER bw;
   bw.init();
   bw.put(1u << m, m + 1);
   if (m == 5) bw.put(o.rotation, 2);
@@ -437,13 +475,20 @@ UB_FN Bits128 bc7_pack(Bc7Build& o) {
     }
     s = u64_delete_bit(s, ib - 1);
     total -= 1;
-    bw.put(s, total);
+    bw.put64(s, total);
   }
   if (sep_alpha) {
     const uint64_t s = u64_delete_bit(o.asel, 1);
-    bw.put(s, 31);
+    bw.put64(s, 31);
   }
-  return bw.b;
+  return bw.bits();
+}
+UB_FN Bits128 bc7_pack(Bc7Build& o) { return bc7_pack_t<-1, BitWriter>(o); }
+
+// BC7 mode a UASTC mode transcodes to (XC:15669-16161); -1 = solid colour blocks: mode 5 or 6, decided per block
+UB_CONSTEXPR int bc7_mode_of_uastc(int m) {
+  constexpr int t[19] = {6, 3, 1, 2, 3, 6, 5, 2, -1, 7, 6, 5, 6, 5, 6, 6, 7, 5, 6};
+  return (m < 0 || m > 18) ? -1 : t[m];
 }
 
 // Full path for one block.  Returns false on an invalid UASTC block (output then zeroed).
@@ -453,7 +498,10 @@ UB_FN bool transcode_block_to_bc7_t(const Bits128& src, Bits128& dst) {
   if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
   Bc7Build o;
   uastc_to_bc7_build_t<KM, TS>(u, o);
-  dst = bc7_pack(o);
+  constexpr int BM = bc7_mode_of_uastc(KM);
+  if (KM < 0) dst = bc7_pack(o);
+  else if (BM >= 0) dst = bc7_pack_t<BM, BitWriter32>(o);
+  else dst = (o.mode == 5) ? bc7_pack_t<5, BitWriter32>(o) : bc7_pack_t<6, BitWriter32>(o);
   return true;
 }
 UB_FN bool transcode_block_to_bc7(const Bits128& src, Bits128& dst) { return transcode_block_to_bc7_t<-1>(src, dst); }

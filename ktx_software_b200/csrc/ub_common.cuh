@@ -121,7 +121,41 @@ struct BitWriter {
   uint32_t pos;
   UB_MFN void init() { b.lo = 0; b.hi = 0; pos = 0; }
   UB_MFN void put(uint64_t val, uint32_t n) { bits_or(b, pos, val); pos += n; }
+  UB_MFN void put64(uint64_t val, uint32_t n) { put(val, n); }
+  UB_MFN Bits128 bits() const { return b; }
 };
+
+// One compressed block assembled in four 32-bit words.  For code whose field positions are compile-time constants after
+// unrolling (the mode-specialised packers): every put then is one shift + one OR on a 32-bit register (two when the field
+// straddles a word), where the 64-bit BitWriter spends a shift pair and an OR pair per field.
+struct BitWriter32 {
+  uint32_t w0, w1, w2, w3, pos;
+  UB_MFN void init() { w0 = 0; w1 = 0; w2 = 0; w3 = 0; pos = 0; }
+  UB_MFN void or_word(uint32_t k, uint32_t v) { if (k == 0) w0 |= v; else if (k == 1) w1 |= v; else if (k == 2) w2 |= v; else if (k == 3) w3 |= v; }
+  UB_MFN void put(uint32_t val, uint32_t n) {   // n <= 32, val < 2^n; bits past 127 are dropped
+    const uint32_t k = pos >> 5, sh = pos & 31u;
+    or_word(k, val << sh);
+    if (sh && sh + n > 32u) or_word(k + 1, val >> (32u - sh));
+    pos += n;
+  }
+  UB_MFN void put64(uint64_t val, uint32_t n) {  // n <= 64
+    put((uint32_t)val, n < 32u ? n : 32u);
+    if (n > 32u) put((uint32_t)(val >> 32), n - 32u);
+  }
+  UB_MFN Bits128 bits() const { Bits128 b; b.lo = (uint64_t)w0 | ((uint64_t)w1 << 32); b.hi = (uint64_t)w2 | ((uint64_t)w3 << 32); return b; }
+};
+
+// __byte_perm: result byte i = byte (sel >> 4i) & 7 of the eight bytes {a0..a3, b0..b3}
+UB_FN uint32_t ub_prmt(uint32_t a, uint32_t b, uint32_t sel) {
+#ifdef __CUDA_ARCH__
+  return __byte_perm(a, b, sel);
+#else
+  const uint64_t v = (uint64_t)a | ((uint64_t)b << 32);
+  uint32_t r = 0;
+  for (int i = 0; i < 4; i++) r |= (uint32_t)((v >> (8 * ((sel >> (4 * i)) & 7u))) & 255u) << (8 * i);
+  return r;
+#endif
+}
 
 // insert a zero bit at position p (bits >= p move up by one)
 UB_FN Bits128 bits_insert0(const Bits128& b, uint32_t p) {
@@ -188,12 +222,15 @@ UB_CONSTEXPR uint32_t bise_c(uint32_t range, uint32_t k) {  // k: 0 = bits, 1 = 
 // (the default, and the only choice on the host): the global tables.
 #ifdef __CUDACC__
 struct SharedTables {
-  uint16_t unq[21 * 256];   // ubt_astc_unquant
+  uint8_t unq[21 * 256];    // low byte of ubt_astc_unquant: the unquantised value
   uint4 pb[3][256];         // ubt_pb8_q, ubt_pb6_q, ubt_pb7s_q
 };
 __shared__ SharedTables ub_shared_tables;   // only kernels that reference it get the 23 KB allocation
 __device__ __forceinline__ void shared_tables_load(uint32_t tid, uint32_t nthreads) {   // followed by a CTA barrier at the caller
-  for (uint32_t i = tid; i < 21 * 256 / 2; i += nthreads) ((uint32_t*)ub_shared_tables.unq)[i] = ((const uint32_t*)UBT(astc_unquant))[i];
+  for (uint32_t i = tid; i < 21 * 256 / 4; i += nthreads) {
+    const uint2 v = ((const uint2*)UBT(astc_unquant))[i];   // four 16-bit entries -> their four low bytes
+    ((uint32_t*)ub_shared_tables.unq)[i] = (v.x & 0xFFu) | ((v.x >> 8) & 0xFF00u) | ((v.y & 0xFFu) << 16) | ((v.y & 0xFF0000u) << 8);
+  }
   for (uint32_t i = tid; i < 256; i += nthreads) {
     ub_shared_tables.pb[0][i] = ((const uint4*)UBT(pb8_q))[i];
     ub_shared_tables.pb[1][i] = ((const uint4*)UBT(pb6_q))[i];
@@ -202,10 +239,18 @@ __device__ __forceinline__ void shared_tables_load(uint32_t tid, uint32_t nthrea
 }
 #endif
 
+// TS = true is used by the mode-specialised transcoders only, where `range` is a compile-time constant: the ranges without
+// trits or quints unquantise by bit replication (range 20: 8 bits, identity; 8: 4 bits; 11: 5 bits) and need no look-up
+// (checked against the table by tests/test_oracle_cpu.py::test_bit_only_unquant_identities).
 template <bool TS = false>
 UB_FN uint32_t astc_unquant_s(uint32_t range, uint32_t code) {
 #if defined(__CUDA_ARCH__)
-  if (TS) return ub_shared_tables.unq[range * 256 + code] & 0xFF;
+  if (TS) {
+    if (range == 20) return code;
+    if (range == 8) return code * 17u;
+    if (range == 11) return (code << 3) | (code >> 2);
+    return ub_shared_tables.unq[range * 256 + code];
+  }
 #endif
   return UBT(astc_unquant)[range * 256 + code] & 0xFF;
 }

@@ -24,6 +24,31 @@ PORT_API int64_t port_transcode(const uint8_t* blocks, uint64_t n, uint32_t fmt,
   return bad;
 }
 
+// The same through the mode-specialised code the CUDA kernels run (mode as a template parameter: constant field positions,
+// 32-bit block assembly, SIMD selector remaps), dispatched on the block's mode the way k_transcode_tiled's bins are.
+template <int TARGET>
+static bool known_mode_dispatch(uint32_t mode, const ub::Bits128& s, ub::Bits128& d) {
+  switch (mode) {
+#define XC_CASE(M) case M: return ub::transcode_known_mode<TARGET, M, false>(s, d);
+    XC_CASE(0) XC_CASE(1) XC_CASE(2) XC_CASE(3) XC_CASE(4) XC_CASE(5) XC_CASE(6) XC_CASE(7) XC_CASE(8) XC_CASE(9)
+    XC_CASE(10) XC_CASE(11) XC_CASE(12) XC_CASE(13) XC_CASE(14) XC_CASE(15) XC_CASE(16) XC_CASE(17) XC_CASE(18)
+#undef XC_CASE
+    default: d.lo = 0; d.hi = 0; return false;
+  }
+}
+PORT_API int64_t port_transcode_known(const uint8_t* blocks, uint64_t n, uint32_t fmt, uint8_t* out) {
+  int64_t bad = -1;
+  for (uint64_t i = 0; i < n; i++) {
+    ub::Bits128 s, d;
+    memcpy(&s, blocks + i * 16, 16);
+    const uint32_t mode = ub::UBT(uastc_huff_modes)[(uint32_t)s.lo & 127u];
+    const bool ok = fmt ? known_mode_dispatch<1>(mode, s, d) : known_mode_dispatch<0>(mode, s, d);
+    memcpy(out + i * 16, &d, 16);
+    if (!ok && bad < 0) bad = (int64_t)i;
+  }
+  return bad;
+}
+
 // UASTC -> 16 RGBA8 texels per block (64 B), the KTX_TTF_RGBA32 decode.  Returns -1 or the first invalid block.
 PORT_API int64_t port_decode_rgba(const uint8_t* blocks, uint64_t n, uint8_t* out_px) {
   int64_t bad = -1;

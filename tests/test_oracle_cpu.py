@@ -315,3 +315,34 @@ def test_job_decomposition_matches_reference(flags):
     want = R.ref_encode_blocks(px, flags)
     bad = np.nonzero((out != want).any(1))[0]
     assert len(bad) == 0, (flags, bad[:8])
+
+
+def test_mode_specialised_transcoders_match_golden():
+    """The code path the CUDA kernels run (mode as a template parameter) compiled for the host, against the reference outputs
+    of the golden corpus: every mode, random payloads, invalid blocks."""
+    import ctypes
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    f = R.port().port_transcode_known
+    f.restype = ctypes.c_int64
+    f.argtypes = [R._u8p, ctypes.c_uint64, ctypes.c_uint32, R._u8p]
+    u = np.ascontiguousarray(g["uastc"])
+    for fmt, key in ((0, "bc7"), (1, "astc")):
+        out = np.zeros_like(u)
+        f(R._p(u), len(u), fmt, R._p(out))
+        bad = np.nonzero((out != g[key]).any(1))[0]
+        assert len(bad) == 0, (key, bad[:8], R.block_modes(u[bad[:8]]))
+    inv = np.ascontiguousarray(g["invalid"]) if "invalid" in g.files else None
+    if inv is not None:
+        out = np.zeros_like(inv)
+        assert f(R._p(inv), len(inv), 0, R._p(out)) == 0 and not out[0].any()
+
+
+def test_bit_only_unquant_identities():
+    """csrc/ub_common.cuh astc_unquant_s<true>: ranges 20 / 8 / 11 (8, 4, 5 plain bits) unquantise by bit replication."""
+    import re
+    s = open(os.path.join(os.path.dirname(GOLD), "..", "ktx_software_b200", "csrc", "uastc_tables.inc")).read()
+    m = re.search(r"UB_TABLE\w*\(uint16_t, astc_unquant, (\d+)\) = \{([^}]*)\}", s)
+    t = np.array([int(x, 0) for x in m.group(2).replace("\n", " ").split(",") if x.strip()]).reshape(21, 256) & 255
+    assert (t[20] == np.arange(256)).all()
+    assert (t[8, :16] == np.arange(16) * 17).all()
+    assert (t[11, :32] == ((np.arange(32) << 3) | (np.arange(32) >> 2))).all()
