@@ -258,14 +258,19 @@ __global__ void __launch_bounds__(XT_THREADS, XT_CTAS_PER_SM) k_transcode_tiled(
   for (; tile < n_tiles; tile += gridDim.x) {
     const uint32_t cnt = tile_count(tile);
     const uint64_t next = tile + gridDim.x;
-    if (tid == 0 && (TARGET == 3 || next < n_tiles)) {  // prefetch the next tile into the other buffer once its bulk store has drained it
-      bulk_wait_read0();   // (TARGET 3: also frees the single 8-byte output tile before this iteration refills it)
-      if (next < n_tiles) {
-        const uint32_t bytes = tile_count(next) * 16u;
-        mbar_expect_tx(&s_bar[buf ^ 1], bytes);
-        bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
+    // Prefetch of the next tile into the other buffer: it must wait until the previous tile's bulk store has drained that
+    // buffer.  Issued by thread 0 AFTER the binning (below), not here: at the top of the iteration the store is microseconds
+    // old and thread 0 would stall in the wait while the other 1023 threads run into the next barrier behind it.
+    auto prefetch_next = [&]() {
+      if (tid == 0 && (TARGET == 3 || next < n_tiles)) {
+        bulk_wait_read0();   // (TARGET 3: also frees the single 8-byte output tile before this iteration refills it)
+        if (next < n_tiles) {
+          const uint32_t bytes = tile_count(next) * 16u;
+          mbar_expect_tx(&s_bar[buf ^ 1], bytes);
+          bulk_g2s(s_in[buf ^ 1], src + next * TILE, bytes, &s_bar[buf ^ 1]);
+        }
       }
-    }
+    };
     if (DYN && tid == 32) *s_next = 0;   // (every warp left the previous tile's loop at the barrier that ended it)
     mbar_wait(&s_bar[buf], buf ? phase1 : phase0);   // every thread waits for the tile itself: no CTA barrier needed here
     if (buf) phase1 ^= 1; else phase0 ^= 1;
@@ -321,7 +326,9 @@ __global__ void __launch_bounds__(XT_THREADS, XT_CTAS_PER_SM) k_transcode_tiled(
       if (WIDE) { const uint32_t hi = __shfl_sync(0xFFFFFFFFu, bin_start_hi, my_mode[k] & 31u); if (my_mode[k] >= 32u) start = hi; }
       if (i < cnt) s_order[start + my_rank[k]] = (uint16_t)i;
     }
+    if (TARGET == 3) prefetch_next();   // before the barrier: the 8-byte output tile must be free before anyone refills it
     __syncthreads();
+    if (TARGET != 3) prefetch_next();
     if (tid < NBINS) s_hist[tid] = 0;   // for the next tile; ordered before its atomics by the barrier that ends this one
 
     // ---- transcode in bin order: a warp sees one mode (two at a bin boundary)

@@ -76,7 +76,7 @@ UB_FN Bits128 astc_pack_solid(uint32_t rgba) {  // void-extent block, UNORM16 = 
 template <int KM, bool TS = false>
 UB_FN bool transcode_block_to_astc_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
-  if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
+  if (!unpack_uastc_t<KM, TS>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
   const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
   if (mode == UASTC_MODE_SOLID) { dst = astc_pack_solid(u.solid); return true; }
 

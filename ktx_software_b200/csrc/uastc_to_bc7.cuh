@@ -495,7 +495,7 @@ UB_CONSTEXPR int bc7_mode_of_uastc(int m) {
 template <int KM, bool TS = false>
 UB_FN bool transcode_block_to_bc7_t(const Bits128& src, Bits128& dst) {
   UnpackedUastc u;
-  if (!unpack_uastc_t<KM>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
+  if (!unpack_uastc_t<KM, TS>(src, u, false)) { dst.lo = 0; dst.hi = 0; return false; }
   Bc7Build o;
   uastc_to_bc7_build_t<KM, TS>(u, o);
   constexpr int BM = bc7_mode_of_uastc(KM);

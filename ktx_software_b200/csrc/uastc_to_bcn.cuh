@@ -30,7 +30,7 @@ UB_FN bool hinted_form_t(const Bits128& src, HintedForm& h) {
   texel_form_clear(h.f);
   h.mode = UASTC_MODE_SOLID; h.hints = 0; h.bc1_sels = 0; h.solid = 0;
   UnpackedUastc u;
-  if (!unpack_uastc_t<KM>(src, u, true)) return false;
+  if (!unpack_uastc_t<KM, TS>(src, u, true)) return false;
   texel_form_from_unpacked<KM, TS>(u, h.f);
   const uint32_t mode = (KM >= 0) ? (uint32_t)KM : u.mode;
   h.mode = mode; h.hints = u.hints; h.solid = u.solid;

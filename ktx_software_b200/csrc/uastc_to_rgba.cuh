@@ -98,7 +98,7 @@ template <int KM, bool TS = false>
 UB_FN bool texel_form_t(const Bits128& src, TexelForm& f) {
   texel_form_clear(f);
   UnpackedUastc u;
-  if (!unpack_uastc_t<KM>(src, u, false)) return false;
+  if (!unpack_uastc_t<KM, TS>(src, u, false)) return false;
   texel_form_from_unpacked<KM, TS>(u, f);
   return true;
 }

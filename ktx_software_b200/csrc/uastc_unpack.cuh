@@ -32,7 +32,8 @@ UB_FN uint32_t spread_mask2(uint32_t m16) {  // 16-bit subset mask -> 2 bits per
 
 // Returns false for an invalid block (reserved mode code, pattern index out of range): XC:14944, :15036-15049.
 // KM >= 0: the caller already knows the mode (blocks binned by mode); every field offset then folds to a constant.
-template <int KM>
+// TS: the per-CTA shared-memory tables are loaded (streaming transcode kernels): trit / quint bundles then decode by one look-up.
+template <int KM, bool TS = false>
 UB_FN bool unpack_uastc_t(const Bits128& blk, UnpackedUastc& u, bool want_hints) {
   const uint32_t mode = (KM >= 0) ? (uint32_t)KM : (uint32_t)UBT(uastc_huff_modes)[(uint32_t)blk.lo & 127u];
   if (KM < 0 && mode >= UASTC_TOTAL_MODES) return false;
@@ -122,11 +123,22 @@ UB_FN bool unpack_uastc_t(const Bits128& blk, UnpackedUastc& u, bool want_hints)
         v = bits_get(blk, ofs, ep_bits);
         ofs += ep_bits;
         if (bundle) {
-          if (!left) { accum = (tq >> (8 * next)) & 255u; next++; left = bundle; }
-          const uint32_t q = accum / mul;
-          v |= (accum - q * mul) << ep_bits;
-          accum = q;
-          left--;
+#ifdef __CUDA_ARCH__
+          if (TS) {   // accum = the bundle's digits, peeled by shifts
+            if (!left) { const uint32_t b = (tq >> (8 * next)) & 255u; accum = has_trits ? ub_shared_tables.trits[b] : ub_shared_tables.quints[b & 127u]; next++; left = bundle; }
+            const uint32_t dbits = has_trits ? 2u : 3u;
+            v |= (accum & ((1u << dbits) - 1u)) << ep_bits;
+            accum >>= dbits;
+            left--;
+          } else
+#endif
+          {
+            if (!left) { accum = (tq >> (8 * next)) & 255u; next++; left = bundle; }
+            const uint32_t q = accum / mul;
+            v |= (accum - q * mul) << ep_bits;
+            accum = q;
+            left--;
+          }
         }
       }
       u.ep[i] = (uint8_t)v;

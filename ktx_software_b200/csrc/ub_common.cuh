@@ -224,6 +224,8 @@ UB_CONSTEXPR uint32_t bise_c(uint32_t range, uint32_t k) {  // k: 0 = bits, 1 = 
 struct SharedTables {
   uint8_t unq[21 * 256];    // low byte of ubt_astc_unquant: the unquantised value
   uint4 pb[3][256];         // ubt_pb8_q, ubt_pb6_q, ubt_pb7s_q
+  uint16_t trits[256];      // BISE bundle -> its five base-3 digits, 2 bits each (digit k at bits 2k)
+  uint16_t quints[128];     // BISE bundle -> its three base-5 digits, 3 bits each
 };
 __shared__ SharedTables ub_shared_tables;   // only kernels that reference it get the 23 KB allocation
 __device__ __forceinline__ void shared_tables_load(uint32_t tid, uint32_t nthreads) {   // followed by a CTA barrier at the caller
@@ -232,6 +234,12 @@ __device__ __forceinline__ void shared_tables_load(uint32_t tid, uint32_t nthrea
     ((uint32_t*)ub_shared_tables.unq)[i] = (v.x & 0xFFu) | ((v.x >> 8) & 0xFF00u) | ((v.y & 0xFFu) << 16) | ((v.y & 0xFF0000u) << 8);
   }
   for (uint32_t i = tid; i < 256; i += nthreads) {
+    uint32_t v = i, t = 0, q = 0;
+    for (uint32_t k = 0; k < 5; k++) { t |= (v % 3u) << (2 * k); v /= 3u; }   // the reference peels digits with % and / (XC:15142-15168)
+    v = i;
+    for (uint32_t k = 0; k < 3; k++) { q |= (v % 5u) << (3 * k); v /= 5u; }
+    ub_shared_tables.trits[i] = (uint16_t)t;
+    if (i < 128) ub_shared_tables.quints[i] = (uint16_t)q;
     ub_shared_tables.pb[0][i] = ((const uint4*)UBT(pb8_q))[i];
     ub_shared_tables.pb[1][i] = ((const uint4*)UBT(pb6_q))[i];
     ub_shared_tables.pb[2][i] = ((const uint4*)UBT(pb7s_q))[i];
