@@ -43,7 +43,9 @@ def main():
         astc = ktx2_levels(f"{CTS}/golden/transcode/transcode_uastc/output_{sub}_2D_UASTC_to_astc.ktx2")
         assert src["scheme"] == 0
         cts["transcode"][sub] = dict(width=src["width"], height=src["height"], uastc=src["levels"][0].hex(),
-                                     bc7=bc7["levels"][0].hex(), astc=astc["levels"][0].hex())
+                                     bc7=bc7["levels"][0].hex(), astc=astc["levels"][0].hex(),
+                                     # the whole 304-byte input file, for ktxTexture2_CreateFromMemory in the compiled-boundary test
+                                     ktx2_file=open(f"{CTS}/input/ktx2/valid_{sub}_2D_UASTC.ktx2", "rb").read().hex())
     tj = json.load(open(f"{CTS}/tests/create/encode_uastc.json"))
     cts["encode_command"] = tj["command"]
     for sub, comps in [("R8_UNORM", 1), ("R8G8_UNORM", 2), ("R8G8B8_UNORM", 3), ("R8G8B8A8_UNORM", 4)]:
@@ -55,6 +57,8 @@ def main():
         cts["encode"][sub] = dict(width=g["width"], height=g["height"], comps=comps, uastc=g["levels"][0].hex(),
                                   raw=(raw.hex() if raw else None))
     json.dump(cts, open(os.path.join(HERE, "cts_uastc.json"), "w"), indent=1)
+    if "--cts-only" in sys.argv:
+        return
 
     # known-answer vector
     i = np.arange(16)
