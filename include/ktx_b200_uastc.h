@@ -204,6 +204,19 @@ int b200_uastc_encode_blocks_dev(const void* d_block_pixels, void* d_out, uint64
 int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
                                 uint32_t pack_flags, void* stream, uint32_t* d_any_alpha);
 
+/* Allocation-free variant of b200_uastc_encode_image_dev.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same arguments, same output bytes.  The encode kernel's scratch (cell results and candidate scores of the tiles in
+ * flight, ~117 MiB) is a static array inside the library's device image: every GPU that loads the library holds it until the
+ * process exits.  The call makes no cudaMalloc / cudaFree / cudaMallocAsync and creates no stream (stream = NULL runs on the
+ * legacy default stream and synchronises it).  Limits: pack levels 0-3 only, and at most B200_NOALLOC_MAX_BLOCKS 4x4 blocks per
+ * call (an 8192 x 8192 image); beyond either, B200_E_INVALID_VALUE.  EVERY call on a device shares the one array: calls whose
+ * kernels overlap on the GPU (different streams, different host threads) race on it -- order them on one stream or with events.
+ * (The scratch keeps the previous call's contents; the kernel clears what must start at zero.) */
+#define B200_NOALLOC_MAX_BLOCKS 4194304u
+int b200_uastc_encode_image_dev_noalloc(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
+                                        uint32_t pack_flags, void* stream, uint32_t* d_any_alpha);
+
 /* Several device-resident images in ONE launch (a mip chain, cube faces, array layers): small images then share the
  * launch with big ones instead of each under-filling the GPU.  Same semantics as b200_uastc_encode_image_dev per image. */
 typedef struct b200_dev_image {

@@ -22,7 +22,8 @@ EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_e
                     "b200_uastc_transcode", "b200_uastc_transcode_dev", "b200_uastc_encode", "b200_uastc_encode_blocks_dev",
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
                     "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex",
-                    "b200_uastc_set_devices", "b200_uastc_device_count", "b200_uastc_build_id", "b200_uastc_encode_mipchain"]
+                    "b200_uastc_set_devices", "b200_uastc_device_count", "b200_uastc_build_id", "b200_uastc_encode_mipchain",
+                    "b200_uastc_encode_image_dev_noalloc"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -92,6 +93,8 @@ def lib():
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
         l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        l.b200_uastc_encode_image_dev_noalloc.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
+                                                          ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_rdo_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.POINTER(UastcParams), ctypes.c_void_p]
         l.b200_uastc_encode_images_dev.argtypes = [ctypes.POINTER(DevImage), ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
         l.b200_uastc_decode.argtypes = [ctypes.c_uint32, ctypes.POINTER(DecodeImage), ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
@@ -207,6 +210,11 @@ def encode_blocks_dev(d_block_pixels, d_out, n_blocks, pack_flags, stream=0):
 def encode_image_dev(d_rgba, width, height, d_out, pack_flags, stream=0, row_pitch_bytes=0, d_any_alpha=0):
     """Device-pointer encode of one RGBA8 image resident in HBM; the 4x4 gather is fused into the kernel."""
     _check(lib().b200_uastc_encode_image_dev(d_rgba, width, height, row_pitch_bytes, d_out, pack_flags, stream or None, d_any_alpha or None))
+
+
+def encode_image_dev_noalloc(d_rgba, width, height, d_out, pack_flags, stream=0, row_pitch_bytes=0, d_any_alpha=0):
+    """b200_uastc_encode_image_dev_noalloc: the same encode with the kernel's scratch in a static device array (no allocation)."""
+    _check(lib().b200_uastc_encode_image_dev_noalloc(d_rgba, width, height, row_pitch_bytes, d_out, pack_flags, stream or None, d_any_alpha or None))
 
 
 def encode_images_dev(images, pack_flags, stream=0, d_any_alpha=0):

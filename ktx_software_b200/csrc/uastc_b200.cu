@@ -1132,3 +1132,62 @@ __global__ void __launch_bounds__(256) k_mip_down(const uint32_t* __restrict__ s
 }
 
 #include "uastc_host.inc"
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free encode (no counterpart in the reference).
+// b200_uastc_encode_image_dev launches k_encode_jobs with a stream-ordered scratch allocation per launch; callers that
+// cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same kernel over a
+// scratch that lives in the library's own device image: a file-scope array, one copy on every GPU that loads the library,
+// held until the process exits.  Size: the tile counter + 1080 B x EJ_T blocks for each of at most B200_NOALLOC_MAX_CTAS
+// resident tiles (one per SM of a B200).
+constexpr unsigned B200_NOALLOC_MAX_CTAS = 148;
+constexpr size_t B200_NOALLOC_SCRATCH_BYTES = EJ_SCRATCH_HEADER + (size_t)B200_NOALLOC_MAX_CTAS * EJ_SCRATCH_PER_CTA;   // ~117 MiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[MAX_DEVICES] = {};   // device address of g_noalloc_scratch on each device (the symbol itself is a host-side stand-in)
+
+// Device address of the scratch on the CURRENT device `dev`, looked up once per device with that device current.
+int noalloc_scratch(int dev, void** out) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) return fail(B200_E_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch)", e);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return B200_OK;
+}
+}  // namespace
+
+extern "C" int b200_uastc_encode_image_dev_noalloc(const void* d_rgba, uint32_t width, uint32_t height, uint32_t row_pitch_bytes, void* d_out,
+                                                   uint32_t pack_flags, void* stream, uint32_t* d_any_alpha) {
+  if (!d_rgba || !d_out || !width || !height) return fail(B200_E_INVALID_VALUE, "bad image");
+  const uint32_t pitch = row_pitch_bytes ? row_pitch_bytes : width * 4;
+  if (pitch < width * 4) return fail(B200_E_INVALID_VALUE, "row pitch smaller than a row");
+  if ((pitch & 3u) || ((uintptr_t)d_rgba & 3u)) return fail(B200_E_INVALID_VALUE, "row pitch / base must be 4-byte aligned");
+  if ((uintptr_t)d_out & 15u) return fail(B200_E_INVALID_VALUE, "d_out must be 16-byte aligned");
+  if ((pack_flags & 7u) >= 4u) return fail(B200_E_INVALID_VALUE, "b200_uastc_encode_image_dev_noalloc encodes levels 0-3 only (level 4 does not run the scratch-based kernel)");
+  const uint32_t bx = (width + 3) / 4, by = (height + 3) / 4;
+  const uint64_t n = (uint64_t)bx * by;
+  if (n > B200_NOALLOC_MAX_BLOCKS) return fail(B200_E_INVALID_VALUE, "b200_uastc_encode_image_dev_noalloc: image exceeds B200_NOALLOC_MAX_BLOCKS (4194304 blocks = 8192 x 8192 texels)");
+  const DeviceCtx* dc;
+  int rc = ensure_device(cur_device(), &dc);
+  if (rc) return rc;
+  void* scratch = nullptr;
+  rc = noalloc_scratch(dc->device, &scratch);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;   // NULL = the legacy default stream (no stream is created here)
+  const uint64_t tiles = (n + EJ_T - 1) / EJ_T;
+  const unsigned grid = (unsigned)std::min<uint64_t>(tiles, std::min<uint64_t>((uint64_t)dc->sm_count * EJ_MIN_CTAS, B200_NOALLOC_MAX_CTAS));
+  CU(cudaMemsetAsync(scratch, 0, EJ_SCRATCH_HEADER, st));   // the tile counter must start at zero; the rest is written before it is read
+  EncDescPack pack;
+  pack.d[0] = {(const uint8_t*)d_rgba, (uint4*)d_out, width, height, pitch, bx, 0};
+  k_encode_jobs<true><<<grid, EJ_T, sizeof(EjShared), st>>>(pack, nullptr, 1, n, pack_flags, d_any_alpha, (uint2*)scratch);
+  g_launches++;
+  CU(cudaGetLastError());
+  if (!stream) CU(cudaStreamSynchronize(st));
+  return B200_OK;
+}
