@@ -490,7 +490,7 @@ def bench_c2(cx, args):
                   "full_size_sweep": "profiles/r4_parity_sweep.json (all 5592407 blocks of this config, 0 mismatches)"}
         cpu = {"value": r["mpix_s"], "unit": "Mpix/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
                "encode_only_mpix_s": r["encode_mpix_s"], "transcode_gbs": r["transcode_gbs"]}
-    enc_key = "k_encode_images<21>"
+    enc_key = "k_encode_jobs@c2"
     line = {"metric": "uastc_encode_Mpix_per_s", "value": value, "unit": "Mpix/s", "n_gpus": cx.world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
@@ -506,7 +506,7 @@ def bench_c2(cx, args):
                     "ms_per_call": {"encode": 1e3 * parts[0], "transcode_bc7": 1e3 * parts[1], "transcode_astc": 1e3 * parts[2]},
                     "base_level_only_upload": mip},
             "gpu_launches": launches,
-            "roofline": cx.issue_roofline(enc_key, "k_encode_images<21> (all 14 mips in one launch: %d blocks)" % total_blocks, total_blocks, per["enc"], 80.0 * total_blocks),
+            "roofline": cx.issue_roofline(enc_key, "k_encode_jobs (all 14 mips in one launch: %d blocks)" % total_blocks, total_blocks, per["enc"], 80.0 * total_blocks),
             "kernel_ms_per_rank": {"encode": rank_enc_ms},
             "transcode": {"bc7_gbs": 32.0 * total_blocks / (per["bc7"] * 1e-3) / 1e9, "astc_gbs": 32.0 * total_blocks / (per["astc"] * 1e-3) / 1e9,
                           "bc7_ms": per["bc7"], "astc_ms": per["astc"], "blocks": total_blocks,
@@ -547,7 +547,7 @@ def bench_single_image(cx, args, name, img, flags, key, ref_px=None, ref_desc=No
            "e2e": {"value": w * h / e2e_s / 1e6, "unit": "Mpix/s", "h2d_bytes_per_step": img.nbytes, "d2h_bytes_per_step": 16 * n, "api": "b200_uastc_encode, pinned host buffers",
                    "matches_device_path": bool((h_out.numpy() == d_out.cpu().numpy()).all())},
            "gpu_launches": launches, "clocks": clocks,
-           "roofline": cx.issue_roofline(key, "k_encode_image<%d>" % (170 if (flags & 7) >= 4 else 21), n, kernel_ms, 80.0 * n)}
+           "roofline": cx.issue_roofline(key, "k_encode_image<170>" if (flags & 7) >= 4 else "k_encode_jobs", n, kernel_ms, 80.0 * n)}
     if R.have_ref():
         cores = os.cpu_count() or 1
         sel = None
@@ -566,7 +566,7 @@ def bench_single_image(cx, args, name, img, flags, key, ref_px=None, ref_desc=No
 
 
 def bench_c1(cx, args):
-    return bench_single_image(cx, args, C1_NAME, cx.R.img_mix(2048, 2048, 1), 2, "k_encode_image<21>@c1")
+    return bench_single_image(cx, args, C1_NAME, cx.R.img_mix(2048, 2048, 1), 2, "k_encode_jobs@c1")
 
 
 def bench_c3(cx, args):
@@ -575,7 +575,7 @@ def bench_c3(cx, args):
     img = R.img_mix(4096, 4096, 3)
     rows = np.arange(0, 1024, 8)
     sel = (rows[:, None] * 1024 + np.arange(1024)[None, :]).reshape(-1)
-    l3 = bench_single_image(cx, args, C3_NAME + " -- level 3, no RDO", img, 3, "k_encode_image<21>@c3_l3",
+    l3 = bench_single_image(cx, args, C3_NAME + " -- level 3, no RDO", img, 3, "k_encode_jobs@c3_l3",
                             ref_px=(blocks_of_rows(img, rows), sel), ref_desc="block rows r = 0 mod 8 (131072 blocks)")
     l3["parity_vs_reference"]["full_size_sweep"] = "profiles/r4_parity_sweep.json (all 1048576 blocks, 0 mismatches)"
     # level 4 + RDO through the host API (the RDO post-pass has no device-pointer image entry): flags 4 | 512 as libktx sets them

@@ -1140,7 +1140,7 @@ __global__ void __launch_bounds__(256) k_mip_down(const uint32_t* __restrict__ s
 // scratch that lives in the library's own device image: a file-scope array, one copy on every GPU that loads the library,
 // held until the process exits.  Size: the tile counter + 1080 B x EJ_T blocks for each of at most B200_NOALLOC_MAX_CTAS
 // resident tiles (one per SM of a B200).
-constexpr unsigned B200_NOALLOC_MAX_CTAS = 148;
+constexpr unsigned B200_NOALLOC_MAX_CTAS = 148 * EJ_MIN_CTAS;   // every resident CTA of a B200
 constexpr size_t B200_NOALLOC_SCRATCH_BYTES = EJ_SCRATCH_HEADER + (size_t)B200_NOALLOC_MAX_CTAS * EJ_SCRATCH_PER_CTA;   // ~117 MiB
 static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
 

@@ -22,8 +22,8 @@ for ch in chunks[1:]:
     ix = {h: i for i, h in enumerate(hdr)}
     base = int(rows[1][0], 16)
     # kernel mangled name: find FUNC symbols "$<kernel>$<func>" whose kernel matches template args in `name`
-    m = re.search(r"(k_\w+)<((?:\(int\)\d+(?:, )?)+)>", name)
-    kfilter = (m.group(1) + "I" + "".join("Li%sE" % v for v in re.findall(r"\(int\)(\d+)", m.group(2)))) if m else want
+    m = re.search(r"(k_\w+)<((?:\((?:int|bool)\)\d+(?:, )?)+)>", name)
+    kfilter = (m.group(1) + "I" + "".join("L%s%sE" % ("b" if t == "bool" else "i", v) for t, v in re.findall(r"\((int|bool)\)(\d+)", m.group(2)))) if m else want
     funcs = []
     for line in syms.splitlines():
         p = line.split()

@@ -19,8 +19,8 @@ for ch in re.split(r'(?m)^"Kernel Name",', out)[1:]:
     rows = list(csv.reader(io.StringIO(ch.split("\n", 1)[1])))
     hdr = rows[0]; ix = {h: i for i, h in enumerate(hdr)}
     base = int(rows[1][0], 16)
-    m = re.search(r"(k_\w+)<((?:\(int\)\d+(?:, )?)+)>", name)
-    kfilter = (m.group(1) + "I" + "".join("Li%sE" % v for v in re.findall(r"\(int\)(\d+)", m.group(2)))) if m else want
+    m = re.search(r"(k_\w+)<((?:\((?:int|bool)\)\d+(?:, )?)+)>", name)
+    kfilter = (m.group(1) + "I" + "".join("L%s%sE" % ("b" if t == "bool" else "i", v) for t, v in re.findall(r"\((int|bool)\)(\d+)", m.group(2)))) if m else want
     ksym = fsym = None
     for line in syms.splitlines():
         p = line.split()
