@@ -872,7 +872,7 @@ struct RdoChain {
   uint32_t hist_mask;
   uint32_t slot_off;         // first table slot of this chain: prefix sum of min(length, RDO_CHUNK) over the chains before it
 };
-const int RDO_THREADS = 288;       // 256 trial threads + one warp that prepares the current block
+const int RDO_THREADS = 320;       // 256 trial threads + the keep-cost warp (main group, 288) + the re-fit worker warp
 const uint32_t RDO_CHUNK = 8192;   // steps per launch
 
 __global__ void __launch_bounds__(256) k_gather_blocks(const uint8_t* __restrict__ img, uint32_t w, uint32_t h, uint32_t pitch,
@@ -980,53 +980,98 @@ __global__ void __launch_bounds__(256) k_rdo_hazard(const uint4* __restrict__ bl
   }
 }
 
-__global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
+// Threads 0..255 score the window's candidates, thread 256 prices "keep as is" (together: the 288 MAIN threads, which meet at
+// a named barrier), and the last warp is the RE-FIT WORKER: the mode-0 endpoint re-fit of a rewritten block (a full forced-selector
+// colour-cell fit, ~15 us on one thread) used to run on thread 0 inside the step whenever a later block might read the
+// endpoint bits (6.4 of 10.2 us per step on img_mix).  It needs only the block's own texels and bits, and only a block of mode
+// 15 / 17 / 18 ever reads another block's endpoint bits, so thread 0 now queues it, the worker re-fits up to 32 queued blocks at
+// a time (one lane each) behind the walk, and a step whose own block is one of those reader modes first waits for the queue to
+// drain -- the bits every step sees are the reference's.
+const int RDO_MAIN_THREADS = 288, RDO_QUEUE = 64;
+__device__ __forceinline__ void rdo_main_barrier() { asm volatile("bar.sync 1, 288;" ::: "memory"); }
+
+__global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* blocks, const uint4* __restrict__ px, const RdoChain* __restrict__ chains,
                                                            uint32_t step0, const ub::RdoBlockInfo* __restrict__ info,
                                                            const ub::RdoPre* __restrict__ pre, const uint32_t* __restrict__ tables,
                                                            ub::RdoHistEntry* __restrict__ hist_all, const uint8_t* __restrict__ hazard,
                                                            uint8_t* __restrict__ modified, ub::RdoParams p) {
   // per-step inputs are double-buffered: while step bi is scored, the loads of step bi+1 are in flight
   __shared__ __align__(16) uint32_t s_table[2][ub::RDO_TABLE_WORDS];
-  __shared__ __align__(16) uint32_t s_px[2][16];
   __shared__ __align__(16) uint4 s_blk[2];
   __shared__ __align__(16) ub::RdoPre s_pre[2];
   __shared__ ub::RdoBlockInfo s_info[2];
   __shared__ __align__(16) uint4 s_ring[256];
   __shared__ float s_keep_t;
   __shared__ unsigned long long s_best;
+  // re-fit queue: thread 0 pushes (head), the worker warp completes (tail); entry e lives in slot e % RDO_QUEUE
+  __shared__ __align__(16) uint4 s_q_blk[RDO_QUEUE];
+  __shared__ uint32_t s_q_bi[RDO_QUEUE];
+  __shared__ volatile uint32_t s_q_head, s_q_tail, s_q_done;
 
   const RdoChain ch = chains[blockIdx.x];
   const uint32_t tid = threadIdx.x;
   ub::RdoHistEntry* hist = hist_all + ch.hist_off;
   const uint32_t begin = ch.first + step0;
-  if (begin >= ch.last) return;
+  if (begin >= ch.last) return;   // (uniform over the CTA)
   const uint32_t end = min(ch.last, begin + RDO_CHUNK);
+  if (tid == 0) { s_q_head = 0; s_q_tail = 0; s_q_done = 0; s_best = ~0ull; }
   // refill the ring with the (final) blocks just before this chunk
   if (tid < 256) { const uint32_t back = tid + 1; if (begin >= ch.first + back) s_ring[(begin - back) & 255u] = blocks[begin - back]; }
+  __syncthreads();
 
-  // what each thread fetches for a step: 128 threads the table, 4 the texels, one each the block, info and pre-computed stats
+  if (tid >= RDO_MAIN_THREADS) {
+    // ---- the re-fit worker: lane l takes queue entry tail + l
+    const uint32_t lane = tid - RDO_MAIN_THREADS;
+    uint32_t tail = 0;
+    for (;;) {
+      const uint32_t head = s_q_head;
+      if (head == tail) {
+        if (s_q_done) break;
+        __nanosleep(200);
+        continue;
+      }
+      __threadfence_block();   // the entries below head were written before head moved
+      const uint32_t n = min(head - tail, 32u);
+      if (lane < n) {
+        const uint32_t slot = (tail + lane) % RDO_QUEUE, bi = s_q_bi[slot];
+        uint32_t q[16];
+#pragma unroll
+        for (uint32_t y = 0; y < 4; y++) {
+          const uint4 v = __ldg(px + (size_t)bi * 4 + y);
+          q[4 * y] = v.x; q[4 * y + 1] = v.y; q[4 * y + 2] = v.z; q[4 * y + 3] = v.w;
+        }
+        const uint4 r = from_bits(ub::rdo_refine_mode0(q, to_bits(s_q_blk[slot])));
+        blocks[bi] = r;
+        s_ring[bi & 255u] = r;   // (thread 0 does not reuse the ring slot of a block whose re-fit is pending)
+      }
+      __syncwarp();
+      __threadfence_block();
+      tail += n;
+      if (lane == 0) s_q_tail = tail;
+    }
+    return;
+  }
+
+  // what each main thread fetches for a step: 128 threads the table, one each the block, info and pre-computed stats
   uint4 nx = make_uint4(0, 0, 0, 0);
   ub::RdoBlockInfo nx_info;
   ub::RdoPre nx_pre;
   auto fetch = [&](uint32_t bi) {
     const size_t slot = (size_t)ch.slot_off + (bi - begin);
     if (tid < 128) nx = __ldg((const uint4*)(tables + slot * ub::RDO_TABLE_WORDS) + tid);
-    else if (tid < 132) nx = __ldg(px + (size_t)bi * 4 + (tid - 128));
     else if (tid == 132) nx = blocks[bi];
     else if (tid == 133) nx_info = info[slot];
     else if (tid == 134) nx_pre = pre[slot];
   };
   auto stash = [&](uint32_t b) {
     if (tid < 128) ((uint4*)s_table[b])[tid] = nx;
-    else if (tid < 132) ((uint4*)s_px[b])[tid - 128] = nx;
     else if (tid == 132) s_blk[b] = nx;
     else if (tid == 133) s_info[b] = nx_info;
     else if (tid == 134) s_pre[b] = nx_pre;
   };
   fetch(begin);
   stash(0);
-  if (tid == 0) s_best = ~0ull;
-  __syncthreads();
+  rdo_main_barrier();
 
   uint32_t b = 0;
   for (uint32_t bi = begin; bi < end; bi++, b ^= 1) {
@@ -1042,9 +1087,16 @@ __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ b
       c.ms_err = q.ms_err; c.rms_err = q.rms_err; c.smooth = q.smooth; c.solid = false; c.skip = q.skip != 0;
     }
     if (active && !c.skip) {
+      // this block reads endpoint bits of earlier mode-0 blocks: every queued re-fit must have landed (head is stable here:
+      // thread 0 pushes only between the two barriers of a step)
+      if (f.valid && ub::rdo_mode_reads_mode0_endpoints(f.mode)) {
+        const uint32_t head = s_q_head;
+        while (s_q_tail != head) __nanosleep(100);
+        __threadfence_block();
+      }
       const uint32_t lo_index = (bi - ch.first > p.window) ? bi - p.window : ch.first;
       const uint32_t n_win = bi - lo_index;
-      // thread k takes candidates k, k+256, ... (k = 0 is the nearest earlier block); the spare warp prices "keep as is"
+      // thread k takes candidates k, k+256, ... (k = 0 is the nearest earlier block); thread 256 prices "keep as is"
       if (tid == 256) s_keep_t = ub::rdo_keep_cost(c, ub::rdo_hist_find(hist, ch.hist_mask, first, c.sel_lo), bi, p);
       if (tid < 256) {
         unsigned long long my_key = ~0ull;
@@ -1063,10 +1115,11 @@ __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ b
         }
         if (my_key != ~0ull) atomicMin(&s_best, my_key);
       }
-      __syncthreads();
+      rdo_main_barrier();
     }
     if (tid == 0) {
       ub::Bits128 best = blk;
+      bool queued = false;
       if (active) {
         uint64_t key_lo = c.sel_lo;
         if (!c.skip) {
@@ -1078,22 +1131,38 @@ __global__ void __launch_bounds__(RDO_THREADS) k_rdo_chain(uint4* __restrict__ b
             best = ub::rdo_splice(blk, prev, first, total);
             uint8_t mark = 1;
             if (p.refine && f.mode == 0) {
-              if (hazard[bi]) best = ub::rdo_refine_mode0(s_px[b], best);  // a later block will read these endpoint bits
-              else mark = 2;                                               // re-fit postponed to k_rdo_rehint
+              if (hazard[bi]) queued = true;   // a later block may read these endpoint bits: re-fit behind the walk (worker warp)
+              else mark = 2;                   // nobody will: re-fit postponed to k_rdo_rehint
             }
             blocks[bi] = from_bits(best);
             modified[bi] = mark;
             uint64_t hi;
-            ub::rdo_get_sel(best, first, total, key_lo, hi);
+            ub::rdo_get_sel(best, first, total, key_lo, hi);   // (a re-fit does not touch the selector bits)
           }
         }
         ub::rdo_hist_set(hist, ch.hist_mask, first, key_lo, bi);
       }
+      // the ring slot about to be overwritten belongs to block bi - 256: its re-fit, if queued, must have landed
+      // (also keeps every block older than the ring final in global memory, where longer windows read it)
+      for (;;) {
+        const uint32_t tail = s_q_tail;
+        if (tail == s_q_head || s_q_bi[tail % RDO_QUEUE] + 256u > bi) break;
+        __nanosleep(100);
+      }
       s_ring[bi & 255u] = from_bits(best);
+      if (queued) {
+        const uint32_t head = s_q_head;
+        while (head - s_q_tail >= (uint32_t)RDO_QUEUE) __nanosleep(100);
+        s_q_blk[head % RDO_QUEUE] = from_bits(best);
+        s_q_bi[head % RDO_QUEUE] = bi;
+        __threadfence_block();
+        s_q_head = head + 1;
+      }
     }
     if (bi + 1 < end) stash(b ^ 1);
-    __syncthreads();
+    rdo_main_barrier();
   }
+  if (tid == 0) { __threadfence_block(); s_q_done = 1; }
 }
 
 __global__ void __launch_bounds__(128) k_rdo_rehint(uint4* __restrict__ blocks, const uint4* __restrict__ px, const uint8_t* __restrict__ modified,
