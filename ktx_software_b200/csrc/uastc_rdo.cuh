@@ -218,10 +218,25 @@ UB_FN uint64_t rdo_fast_error(const uint32_t* table, const RdoBlockInfo& f, uint
   Bits128 w;
   w.lo = lo; w.hi = hi;
   for (uint32_t k = 0; k < 3; k++) if (k < f.npos) w = bits_insert0(w, f.pos[k]);
+  // entry e = texel * planes + plane sits at bit e * wb: peel the entries off a running 128-bit shift (branch-free; the walk's
+  // trial loop spends most of its instructions here)
   uint32_t total = 0;
-  const uint32_t n = 16u * f.planes, wb = f.wb;
-  for (uint32_t e = 0; e < 32; e++)
-    if (e < n) total += table[(e << wb) + bits_get(w, e * wb, wb)];  // e = texel * planes + plane
+  const uint32_t wb = f.wb, mask = (1u << wb) - 1u;
+  uint64_t a = w.lo, b = w.hi;
+#pragma unroll
+  for (uint32_t e = 0; e < 16; e++) {
+    total += table[(e << wb) + ((uint32_t)a & mask)];
+    a = (a >> wb) | (b << (64u - wb));
+    b >>= wb;
+  }
+  if (f.planes == 2) {
+#pragma unroll
+    for (uint32_t e = 16; e < 32; e++) {
+      total += table[(e << wb) + ((uint32_t)a & mask)];
+      a = (a >> wb) | (b << (64u - wb));
+      b >>= wb;
+    }
+  }
   return (uint64_t)(total >> 1);
 }
 
