@@ -100,8 +100,8 @@ int b200_uastc_transcode_dev(uint32_t target, const void* d_src, void* d_dst, ui
  * _bc3 (:18404), _bc4 (:18442), _bc5 (:18470), _etc2_eac_r11 (:18792), _etc2_eac_rg11 (:18819).
  * dst offsets and sizes count 8 bytes per block for ETC1_RGB, BC1_RGB, BC4_R and ETC2_EAC_R11.  BC4_R and ETC2_EAC_R11 take
  * alpha instead of red when has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE are set (XC:10417, :10515); BC5_RG and
- * ETC2_EAC_RG11 take red and alpha (XC:10430, :10526).  Not accelerated
- * (B200_E_INVALID_VALUE, the glue keeps the stock path): ETC1_RGB from the alpha channel.  Device pointers must be
+ * ETC2_EAC_RG11 take red and alpha (XC:10430, :10526); ETC1_RGB with has_alpha and B200_DECODE_FLAG_ALPHA_TO_OPAQUE encodes the
+ * alpha channel alone (transcode_uastc_to_etc1(blk, dst, 3), XC:10142-10147, :16560).  Device pointers must be
  * 16-byte aligned (B200_E_INVALID_VALUE otherwise). */
 int b200_uastc_transcode_ex(uint32_t target, uint32_t decode_flags, uint32_t has_alpha, const b200_xcode_span* spans,
                             uint32_t n_spans, const uint8_t* src_base, uint8_t* dst_base, int64_t* bad_span);

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(XT_THREADS, XT_CTAS_PER_SM) k_transcode_tiled(
   uint4* s_out = (uint4*)(xt_smem + 2 * (size_t)TILE * 16);   // TARGET 2 only: [4 texel rows][TILE] row pieces of 16 (or 8) bytes
   uint2* s_out8 = (uint2*)(xt_smem + 2 * (size_t)TILE * 16);  // TARGET 3, 8-byte targets: the output tile
   uint64_t* s_bar = (uint64_t*)(xt_smem + xt_data_bytes(TARGET));
-  constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4 || KIND == 6);
+  constexpr bool out8 = TARGET == 3 && (KIND == 0 || KIND == 2 || KIND == 4 || KIND == 6 || KIND == 8);
   uint32_t* s_hist = (uint32_t*)(s_bar + 2);
   // BC1 / BC3: the cost of a block is set by which BC1 path its hint bits select (hint0: endpoints + weights as they are;
   // hint1: one least-squares fit on the block's weights; none: the full encode_bc1), so the bins are (path, mode) pairs --

@@ -245,6 +245,143 @@ UB_FN uint64_t etc1_from_form(const HintedForm& h, const HintFields& hf, const u
   return o;
 }
 
+// ---- ETC1 from ONE channel (transcode_uastc_to_etc1(blk, dst, channel), XC:16560-17260; transcode_slice passes channel 3 when the
+// caller asks for alpha data in an opaque format, :10142-10147).  There are no hints for this: flip estimate, base grey levels
+// and the intensity tables are searched here.  val = the channel's 16 values, raster order.
+#include "uastc_etc1y_tables.inc"
+UB_FN uint64_t etc1_y_bytes(const uint32_t* by) {
+  uint64_t o = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 8; i++) o |= (uint64_t)(by[i] & 255u) << (8 * i);
+  return o;
+}
+UB_FN uint64_t etc1_y_solid(uint32_t y) {
+  const uint32_t enc = UBT(etc1y_solid)[y], base = enc & 31u, sel = (enc >> 5) & 3u, table = enc >> 7;
+  uint32_t by[8];
+  by[0] = by[1] = by[2] = base << 3;
+  by[3] = 2u | (table << 5) | (table << 2);
+  by[4] = by[5] = (sel < 2) ? 255u : 0u;                 // s_etc1_solid_selectors (XC:16323)
+  by[6] = by[7] = (sel == 0 || sel == 3) ? 255u : 0u;
+  return etc1_y_bytes(by);
+}
+UB_BIG uint64_t etc1_y_from_values(const uint32_t* val) {
+  // pack_etc1_y_estimate_flipped (XC:16469): quadrant sums -> half averages -> which split leaves the greyer halves
+  int q[2][2] = {{0, 0}, {0, 0}};   // [x half][y half]
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) q[(i & 3u) >> 1][i >> 3] += (int)val[i];
+  const int upper = (q[0][0] + q[1][0] + 4) / 8, lower = (q[0][1] + q[1][1] + 4) / 8, left = (q[0][0] + q[0][1] + 4) / 8, right = (q[1][0] + q[1][1] + 4) / 8;
+  int ud = 0, ld = 0, lfd = 0, rd = 0;
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    const int v = (int)val[i];
+    const int dv = v - ((i >> 3) ? lower : upper), dh = v - (((i & 3u) >> 1) ? right : left);
+    if (i >> 3) ld += dv * dv; else ud += dv * dv;
+    if ((i & 3u) >> 1) rd += dh * dh; else lfd += dh * dh;
+  }
+  const uint32_t flip = (ud + ld) < (lfd + rd) ? 1u : 0u;
+  uint32_t low[2] = {255u, 255u}, high[2] = {0u, 0u};
+#pragma unroll
+  for (uint32_t i = 0; i < 16; i++) {
+    const uint32_t sb = flip ? (i >> 3) : ((i & 3u) >> 1);
+    low[sb] = minu(low[sb], val[i]); high[sb] = maxu(high[sb], val[i]);
+  }
+  const uint32_t range[2] = {high[0] - low[0], high[1] - low[1]};
+  uint32_t by[8] = {0, 0, 0, flip, 0, 0, 0, 0};
+  uint32_t lmask = 0, hmask = 0;
+  // a sub-block whose values span <= 3 levels: base, table and selectors straight from the run tables (individual mode)
+  auto run_subblock = [&](uint32_t sb) {
+    const uint32_t enc = (range[sb] == 0) ? UBT(etc1y_run1)[low[sb]] : ((range[sb] < 2) ? UBT(etc1y_run2)[low[sb]] : UBT(etc1y_run4)[low[sb]]);
+    const uint32_t table = enc & 7u, base = (enc >> 3) & 31u;
+    by[3] |= table << (sb ? 2 : 5);
+    const uint32_t keep = ~(0xFu << (sb ? 0 : 4)), sv = base << (sb ? 0 : 4);
+    by[0] = (by[0] & keep) | sv; by[1] = (by[1] & keep) | sv; by[2] = (by[2] & keep) | sv;
+#pragma unroll
+    for (uint32_t i = 0; i < 16; i++) {
+      const uint32_t mine = flip ? (i >> 3) : ((i & 3u) >> 1);
+      if (mine == sb) {
+        const uint32_t s = (enc >> (8 + 2 * (val[i] - low[sb]))) & 3u;
+        const uint32_t t = (0x4Bu >> (2 * s)) & 3u;                 // g_selector_index_to_etc1 = {3, 2, 0, 1}
+        const uint32_t ofs = (i & 3u) * 4 + (i >> 2);
+        lmask |= (t & 1u) << ofs; hmask |= (t >> 1) << ofs;
+      }
+    }
+  };
+  if (range[0] <= 3 && range[1] <= 3) {
+    run_subblock(0); run_subblock(1);
+  } else {
+    const int a0 = flip ? upper : left, a1 = flip ? lower : right;
+    uint32_t y0 = (uint32_t)(a0 * 31 + 127) / 255u, y1 = (uint32_t)(a1 * 31 + 127) / 255u;
+    bool diff = true;
+    int dy = (int)y1 - (int)y0;
+    if (dy < -4 || dy > 3) {
+      diff = false;
+      y0 = (uint32_t)(a0 * 15 + 127) / 255u; y1 = (uint32_t)(a1 * 15 + 127) / 255u;
+      by[0] = by[1] = by[2] = y1 | (y0 << 4);
+    } else {
+      y1 = (uint32_t)((int)y0 + dy);
+      if (dy < 0) dy += 8;
+      by[0] = by[1] = by[2] = (y0 << 3) | (uint32_t)dy;
+      by[3] |= 2u;
+    }
+    const uint32_t base_y[2] = {diff ? ((y0 << 3) | (y0 >> 2)) : ((y0 << 4) | y0), diff ? ((y1 << 3) | (y1 >> 2)) : ((y1 << 4) | y1)};
+#pragma unroll 1
+    for (uint32_t sb = 0; sb < 2; sb++) {
+      if (!diff && range[sb] <= 3) { run_subblock(sb); continue; }
+      const int base = (int)base_y[sb];
+      int pos = (int)high[sb] - base, neg = base - (int)low[sb];
+      if (pos < 0) pos = -pos;
+      if (neg < 0) neg = -neg;
+      const uint32_t er = (uint32_t)(pos > neg ? pos : neg);
+      // only the tables that can be useful for this range (XC:17019-17053)
+      uint32_t mask = 0xFFu;
+      if (er <= 51) {
+        mask = 0xFu;
+        if (er > 22) mask &= ~1u;
+        if (er < 4 || er > 39) mask &= ~2u;
+        if (er < 9) mask &= ~4u;
+        if (er < 12) mask &= ~8u;
+      } else {
+        mask &= ~3u;
+        if (er > 60) mask &= ~4u;
+        if (er > 89) mask &= ~8u;
+        if (er > 120) mask &= ~16u;
+        if (er > 136) mask &= ~32u;
+        if (er > 174) mask &= ~64u;
+      }
+      const int low_limit = -base, high_limit = 255 - base;
+      uint32_t best_err = 0xFFFFFFFFu, best_inten = 0, best_l = 0, best_h = 0;
+#pragma unroll 1
+      for (uint32_t inten = 0; inten < 8; inten++) {
+        if (!((mask >> inten) & 1u)) continue;
+        int t0 = UBT(etc1_inten)[inten * 4 + 0], t1 = UBT(etc1_inten)[inten * 4 + 1], t2 = UBT(etc1_inten)[inten * 4 + 2], t3 = UBT(etc1_inten)[inten * 4 + 3];
+        t0 = t0 > low_limit ? t0 : low_limit; t1 = t1 > low_limit ? t1 : low_limit;
+        t2 = t2 < high_limit ? t2 : high_limit; t3 = t3 < high_limit ? t3 : high_limit;
+        const int th01 = t0 + t1, th12 = t1 + t2, th23 = t2 + t3;
+        uint32_t total = 0, lm = 0, hm = 0;
+#pragma unroll
+        for (uint32_t i = 0; i < 16; i++) {
+          const uint32_t mine = flip ? (i >> 3) : ((i & 3u) >> 1);
+          if (mine == sb) {
+            const int delta = (int)val[i] - base, d2 = delta * 2;
+            const uint32_t k = (uint32_t)(d2 < th01) + (d2 < th12) + (d2 < th23);
+            const uint32_t c = (0xE1u >> (2 * k)) & 3u;                       // s_table = {1, 0, 2, 3}
+            const int tv = k == 0 ? t3 : (k == 1 ? t2 : (k == 2 ? t1 : t0));  // tv[] = {t2, t3, t1, t0} indexed by c
+            const int e = tv - delta;
+            total += (uint32_t)(e * e);
+            const uint32_t ofs = (i & 3u) * 4 + (i >> 2);
+            lm |= (c & 1u) << ofs; hm |= (c >> 1) << ofs;
+          }
+        }
+        if (total < best_err) { best_err = total; best_inten = inten; best_l = lm; best_h = hm; }
+      }
+      by[3] |= best_inten << (sb ? 2 : 5);
+      lmask |= best_l; hmask |= best_h;
+    }
+  }
+  by[7] = lmask & 255u; by[6] = (lmask >> 8) & 255u; by[5] = hmask & 255u; by[4] = (hmask >> 8) & 255u;
+  return etc1_y_bytes(by);
+}
+
 // ---- ETC2 EAC A8 (XC:17264-17339)
 UB_FN uint64_t eac_a8_bytes(uint32_t base, uint32_t table, uint32_t mul, uint64_t sels48) {
   uint64_t o = (uint64_t)(base & 255u) | ((uint64_t)((table & 15u) | ((mul & 15u) << 4)) << 8);
@@ -351,13 +488,20 @@ UB_FN uint64_t eac_r11_from_form(const HintedForm& h, const HintFields& hf, uint
 }
 
 // Output bytes per block of a hinted target (0 = not one)
-UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind == 2 || kind == 4 || kind == 6) ? 8u : (kind == 1 || kind == 3 || kind == 5 || kind == 7) ? 16u : 0u; }
+UB_FN uint32_t hinted_target_bytes(uint32_t kind) { return (kind == 0 || kind == 2 || kind == 4 || kind == 6 || kind == 8) ? 8u : (kind == 1 || kind == 3 || kind == 5 || kind == 7) ? 16u : 0u; }
 
 // The shared part.  kind = ktx_transcode_fmt_e for 0 ETC1_RGB, 1 ETC2_RGBA, 2 BC1_RGB, 3 BC3_RGBA, 4 BC4_R, 5 BC5_RG, and
-// 6 = ETC2_EAC_R11, 7 = ETC2_EAC_RG11 (KTX_TTF 20 / 21); chan0 / chan1: the channels BC4 / BC5 / R11 / RG11 take
+// 6 = ETC2_EAC_R11, 7 = ETC2_EAC_RG11 (KTX_TTF 20 / 21), 8 = ETC1_RGB from the single channel chan0; chan0 / chan1: the channels BC4 / BC5 / R11 / RG11 take
 // (transcode_image, XC:10417-10438, :10511-10527).  8-byte targets fill d.lo only.
 UB_FN void hinted_target_from_form(const HintedForm& h, uint32_t kind, bool high_quality, uint32_t chan0, uint32_t chan1, Bits128& d) {
   d.lo = 0; d.hi = 0;
+  if (kind == 8) {   // ETC1 from channel chan0 (alpha data to an opaque format)
+    if (h.mode == UASTC_MODE_SOLID) { d.lo = etc1_y_solid((h.solid >> (8 * chan0)) & 255u); return; }
+    uint32_t v[16];
+    channel_from_form(h.f, chan0, v);
+    d.lo = etc1_y_from_values(v);
+    return;
+  }
   if (kind == 4) { d.lo = bc4_from_form(h.f, chan0); return; }
   if (kind == 5) { d.lo = bc4_from_form(h.f, chan0); d.hi = bc4_from_form(h.f, chan1); return; }
   if (kind == 6 || kind == 7) {

@@ -105,6 +105,7 @@ def make_hinted():
     out["r11_hq"] = R.ref_transcode_hinted(b, 20, 32)[0]
     out["rg11_hq"] = R.ref_transcode_hinted(b, 21, 32)[0]
     out["r11_alpha"] = R.ref_transcode_hinted(b, 20, 4, True)[0]
+    out["etc1_alpha"] = R.ref_transcode_hinted(b, 0, 4, True)[0]    # ETC1 from the alpha channel (XC:16560)
     np.savez_compressed(os.path.join(HERE, "hinted_golden.npz"), **out)
     print("hinted corpus:", b.shape, "modes:", np.bincount(R.block_modes(b), minlength=19))
 

@@ -122,8 +122,9 @@ def port_transcode_hinted(blocks, tf, decode_flags=0, has_alpha=True):
     f.restype = ctypes.c_int64
     f.argtypes = [_u8p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, _u8p]
     out = np.zeros((blocks.shape[0], HINTED_TARGET_BYTES[tf]), np.uint8)
-    chan0 = 3 if (tf in (4, 20) and has_alpha and (decode_flags & 4)) else 0
-    kind = {20: 6, 21: 7}.get(tf, tf)
+    from_alpha = bool(has_alpha and (decode_flags & 4))
+    chan0 = 3 if (tf in (0, 4, 20) and from_alpha) else 0
+    kind = 8 if (tf == 0 and from_alpha) else {20: 6, 21: 7}.get(tf, tf)   # 8 = ETC1 from one channel (XC:16560)
     bad = f(_p(blocks), blocks.shape[0], kind, 1 if (decode_flags & 32) else 0, chan0, 3, _p(out))
     return out, bad
 

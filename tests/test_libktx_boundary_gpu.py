@@ -64,13 +64,20 @@ def test_cts_transcode_uastc_through_patched_libktx(ktx):
         # the other accelerated targets agree with the product's own C ABI output (itself checked against the reference elsewhere)
         import ktx_software_b200 as K
         u = np.frombuffer(bytes.fromhex(c["uastc"]), np.uint8)
-        has_alpha = sub.startswith("R8G8B8A8")
+        # alphaContent as ktxTexture2_TranscodeBasis derives it (basis_transcode.cpp:246-251): the DFD's first sample is
+        # KHR_DF_CHANNEL_UASTC_RGBA (3) or _RRRG (5); an RGBA8 source whose alpha was all 255 is stored as UASTC_RGB (0)
+        dfd_off = int.from_bytes(f[48:52], "little")
+        has_alpha = (f[dfd_off + 4 + 24 + 3] & 0xF) in (3, 5)
         for fmt in (K.TTF_BC1_RGB, K.TTF_BC3_RGBA, K.TTF_ETC1_RGB, K.TTF_ETC2_RGBA, K.TTF_BC4_R, K.TTF_BC5_RG):
             rc, got = _transcode(ktx, f, fmt)
             assert rc == 0, (sub, fmt, rc)
+        # ETC1 with KTX_TF_TRANSCODE_ALPHA_DATA_TO_OPAQUE_FORMATS: the alpha channel alone for textures that have alpha, plain ETC1 otherwise
+        rc, got = _transcode(ktx, f, K.TTF_ETC1_RGB, flags=4)
+        assert rc == 0 and (got == K.transcode(u, K.TTF_ETC1_RGB, decode_flags=4, has_alpha=has_alpha)).all(), sub
+        if R.have_ref():
+            assert (got.reshape(-1, 8) == R.ref_transcode_hinted(u, 0, 4, has_alpha)[0]).all(), sub
         rc, texels = _transcode(ktx, f, K.TTF_RGBA32)
         assert rc == 0 and (texels.reshape(8, 8, 4) == K.decode(u, K.TTF_RGBA32, [(0, 8, 8)])[0]).all()
-        del has_alpha
 
 
 @needs_ktx

@@ -346,3 +346,16 @@ def test_bit_only_unquant_identities():
     assert (t[20] == np.arange(256)).all()
     assert (t[8, :16] == np.arange(16) * 17).all()
     assert (t[11, :32] == ((np.arange(32) << 3) | (np.arange(32) >> 2))).all()
+
+
+@pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built")
+def test_etc1_from_alpha_channel_port_matches_reference():
+    """csrc/uastc_to_bcn.cuh etc1_y_from_values / etc1_y_solid (hinted kind 8) against transcode_uastc_to_etc1(blk, dst, 3)."""
+    g = np.load(os.path.join(GOLD, "transcode_golden.npz"))
+    u = g["uastc"]
+    u = u[R.etc2_transcodable(u)][:6000]
+    want, ok = R.ref_transcode_hinted(u, 0, decode_flags=4, has_alpha=True)
+    got, bad = R.port_transcode_hinted(u, 0, decode_flags=4, has_alpha=True)
+    assert ok and bad == -1 and (want == got).all()
+    e = R.ref_encode_blocks(R.ref_extract_blocks(R.img_mix(128, 128, 4)), 2)
+    assert (R.ref_transcode_hinted(e, 0, 4, True)[0] == R.port_transcode_hinted(e, 0, 4, True)[0]).all()
