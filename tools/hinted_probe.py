@@ -10,7 +10,7 @@ u = g["uastc"][:16384]   # reference-encoded part of the corpus
 n = 1 << 24
 rep = torch.from_numpy(np.tile(u, (n // u.shape[0], 1))).cuda()
 want = sys.argv[1:]
-for tf, name in [(6, "bc7"), (10, "astc"), (2, "bc1"), (3, "bc3"), (4, "bc4"), (5, "bc5"), (0, "etc1"), (1, "etc2")]:
+for tf, name in [(6, "bc7"), (10, "astc"), (2, "bc1"), (3, "bc3"), (4, "bc4"), (5, "bc5"), (0, "etc1"), (1, "etc2"), (20, "r11"), (21, "rg11")]:
     if want and name not in want:
         continue
     ob = K.target_block_bytes(tf)
