@@ -593,20 +593,41 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(con
 #ifndef EJ_THREADS
 #define EJ_THREADS 768
 #endif
+#ifndef EJ_ETC1_JOBS
+#define EJ_ETC1_JOBS 1     // ETC1 hint search as warp-jobs over (flip, colour mode) (0: inside the thread = block finish stage)
+#endif
+#ifndef EJ_SCRATCH_CG
+#define EJ_SCRATCH_CG 1    // the CTA's global scratch bypasses L1 (ld.cg / st.cg): L1 is for the jobs' local frames
+#endif
+#if EJ_SCRATCH_CG
+__device__ __forceinline__ uint2 ej_ld(const uint2* p) { return __ldcg(p); }
+__device__ __forceinline__ uint4 ej_ld(const uint4* p) { return __ldcg(p); }
+__device__ __forceinline__ uint32_t ej_ld(const uint32_t* p) { return __ldcg(p); }
+__device__ __forceinline__ void ej_st(uint2* p, uint2 v) { __stcg(p, v); }
+__device__ __forceinline__ void ej_st(uint4* p, uint4 v) { __stcg(p, v); }
+__device__ __forceinline__ void ej_st(uint32_t* p, uint32_t v) { __stcg(p, v); }
+#else
+template <class T> __device__ __forceinline__ T ej_ld(const T* p) { return *p; }
+template <class T> __device__ __forceinline__ void ej_st(T* p, T v) { *p = v; }
+#endif
 #ifndef EJ_MIN_CTAS
 #define EJ_MIN_CTAS 1
 #endif
 constexpr int EJ_T = EJ_THREADS;
-constexpr size_t EJ_SCRATCH_PER_CTA = (size_t)EJ_T * (ub::J_MAX_CELL_SLOTS * 24 + ub::J_MAX_CAND_SLOTS * 8);
+constexpr size_t EJ_SCRATCH_PER_CTA = (size_t)EJ_T * (ub::J_MAX_CELL_SLOTS * 24 + ub::J_MAX_CAND_SLOTS * 8 + 64 + 4 * 16);   // cells, scores, decoded winner, ETC1 hint jobs
 struct EjShared {
   uint32_t px[EJ_T * 17];        // texel j of tile block b at [b * 17 + j]: conflict-free whether a warp reads one block or 32
   uint8_t parts[EJ_T * ub::J_PARTS];
   uint16_t list[EJ_T];           // tile blocks by class: [opaque][LA opaque][LA alpha][alpha] -> every group is one range
   uint8_t cls[EJ_T];
   uint32_t cnt[4];
-  uint32_t next[3];              // next unclaimed warp-job of the estimate / cell / score stage
+  uint32_t next[4];              // next unclaimed warp-job of the estimate / cell / score / ETC1 hint stage
+  uint32_t e1cnt[16];            // blocks per ETC1 cost class
   unsigned long long tile;       // the tile this CTA works on
 };
+// (sizeof(EjShared) + the 1 KB the system reserves per CTA must stay <= 64 KB: the next shared-memory carve-out is 100 KB, and
+//  the 36 KB come out of the L1 that caches the jobs' local frames -- measured, a 40-byte overshoot cost 6 % of the kernel)
+static_assert(sizeof(EjShared) + 1024 <= 65536, "EjShared crosses the 64 KB carve-out");
 constexpr size_t EJ_SCRATCH_HEADER = 256;
 
 // Stage bookkeeping of one warp: how many warp-jobs every slot has (lane l holds slots l and l + 32), as inclusive prefix sums.
@@ -646,6 +667,10 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
   unsigned long long* tile_counter = (unsigned long long*)scratch_all;          // zeroed by the host before the launch
   uint2* cells = scratch_all + EJ_SCRATCH_HEADER / 8 + (size_t)blockIdx.x * (EJ_SCRATCH_PER_CTA / 8);   // [cell slot][3][EJ_T]
   uint2* scores = cells + (size_t)ub::J_MAX_CELL_SLOTS * 3 * EJ_T;                // [candidate slot][EJ_T]
+  uint32_t* gdec = (uint32_t*)(scores + (size_t)ub::J_MAX_CAND_SLOTS * EJ_T);     // [texel][EJ_T]: every block's winner, decoded
+  uint4* ge1 = (uint4*)(gdec + 16 * EJ_T);                                        // [ETC1 hint job slot][EJ_T]: {err lo, err hi, hint, -}
+  // (cells / scores / gdec / ge1 live in global memory, i.e. in L2, not in shared memory: every KB of shared memory comes out of
+  //  the L1 that holds the jobs' local frames; with gdec and ge1 in shared memory the kernel ran 19 % slower)
   ub::EncCfg cfg = ub::enc_cfg_from_flags(flags);
   // enabled slots (uniform over the launch)
   const uint32_t en_cands = ub::j_enabled_cands(cfg.mode_mask);
@@ -660,7 +685,8 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     // per CTA leaves SMs idle behind the CTA that drew the expensive tiles
     if (tid == 0) sh.tile = atomicAdd(tile_counter, 1ull);
     if (tid < 4) sh.cnt[tid] = 0;
-    if (tid < 3) sh.next[tid] = 0;
+    if (tid < 4) sh.next[tid] = 0;
+    if (tid < 16) sh.e1cnt[tid] = 0;
     __syncthreads();
     const uint64_t tile = sh.tile;
     if (tile >= n_tiles) break;   // uniform per CTA
@@ -775,9 +801,9 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
           ub::CellOut o;
           ub::j_run_cell(gc, px, parts, cfg, o);
           uint2* q = cells + (size_t)ub::j_cell_local(gc) * 3 * EJ_T + b;
-          q[0] = make_uint2(o.astc_lo, o.astc_hi);
-          q[EJ_T] = ((const uint2*)o.sel)[0];
-          q[2 * EJ_T] = ((const uint2*)o.sel)[1];
+          ej_st(q, make_uint2(o.astc_lo, o.astc_hi));
+          ej_st(q + EJ_T, ((const uint2*)o.sel)[0]);
+          ej_st(q + 2 * EJ_T, ((const uint2*)o.sel)[1]);
         }
       }
     }
@@ -807,7 +833,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
           const uint32_t nc = ub::jc_cells(d);
           for (uint32_t s = 0; s < nc; s++) {
             const uint2* q = cells + (size_t)ub::j_cell_local(ub::jc_cell0(d) + s) * 3 * EJ_T + b;
-            const uint2 a = q[0], s0 = q[EJ_T], s1 = q[2 * EJ_T];
+            const uint2 a = ej_ld(q), s0 = ej_ld(q + EJ_T), s1 = ej_ld(q + 2 * EJ_T);
             co[s].astc_lo = a.x; co[s].astc_hi = a.y;
             ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
           }
@@ -816,13 +842,15 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
           uint32_t overall;
           float uerr;
           ub::j_score(px, c, sh.cls[b], flags, overall, uerr);
-          scores[(size_t)ub::j_cand_local(gs) * EJ_T + b] = make_uint2(overall, __float_as_uint(uerr));
+          ej_st(scores + (size_t)ub::j_cand_local(gs) * EJ_T + b, make_uint2(overall, __float_as_uint(uerr)));
         }
       }
     }
     __syncthreads();
 
-    // ---- finish: thread = block
+    // ---- finish, head: thread = block.  Selection, the winner decoded, BC1 / EAC hints, the block packed but for its ETC1 hints
+    ub::Bits128 packed;
+    uint32_t etc1_at;
     {
       const bool solid = cls == ub::J_CLS_SOLID;
       ub::Candidate win;
@@ -836,7 +864,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         uint8_t modes[ub::J_MAX_CAND_SLOTS], slots[ub::J_MAX_CAND_SLOTS];
         for (uint32_t m = mine; m; m &= m - 1) {
           const uint32_t gs = __ffs(m) - 1;
-          const uint2 v = scores[(size_t)ub::j_cand_local(gs) * EJ_T + tid];
+          const uint2 v = ej_ld(scores + (size_t)ub::j_cand_local(gs) * EJ_T + tid);
           overall[n] = v.x; uerr[n] = __uint_as_float(v.y);
           modes[n] = (uint8_t)ub::jc_mode(ub::UBT(j_cand)[gs]); slots[n] = (uint8_t)gs; n++;
         }
@@ -845,14 +873,89 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         ub::CellOut co[3];
         for (uint32_t s = 0; s < nc; s++) {
           const uint2* q = cells + (size_t)ub::j_cell_local(ub::jc_cell0(d) + s) * 3 * EJ_T + tid;
-          const uint2 a = q[0], s0 = q[EJ_T], s1 = q[2 * EJ_T];
+          const uint2 a = ej_ld(q), s0 = ej_ld(q + EJ_T), s1 = ej_ld(q + 2 * EJ_T);
           co[s].astc_lo = a.x; co[s].astc_hi = a.y;
           ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
         }
         ub::j_assemble(gs, sh.parts + tid * ub::J_PARTS, co, win);
       }
-      const ub::Bits128 r = ub::j_finish(px, flags, &win, live, solid, ENC_FINE_SYNC);
-      if (live) *dst = make_uint4((uint32_t)r.lo, (uint32_t)(r.lo >> 32), (uint32_t)r.hi, (uint32_t)(r.hi >> 32));
+      uint32_t dec[16], wmode;
+      packed = ub::j_finish_head(px, flags, &win, live, solid, ENC_FINE_SYNC, dec, wmode, etc1_at);
+#if EJ_ETC1_JOBS
+      uint32_t e1cls = 16;
+      if (etc1_at != 0xFFFFu) {
+#pragma unroll
+        for (uint32_t j = 0; j < 16; j++) ej_st(gdec + j * EJ_T + tid, dec[j]);
+        sh.parts[tid * ub::J_PARTS] = (uint8_t)wmode;   // the pattern list is not needed any more: its first byte carries the winner's mode
+        e1cls = ub::etc1_cost_class(wmode, dec);
+      }
+      // the class lists are done with: sh.list now takes the non-solid blocks ordered by the cost class of their ETC1 search, dearest
+      // first, so that the 32 lanes of a hint job run searches of similar length (same two-step ranking as the load stage)
+      {
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, e1cls);
+        const uint32_t leader = __ffs(peers) - 1;
+        uint32_t b0 = 0;
+        if (lane == leader && e1cls < 16u) b0 = atomicAdd(&sh.e1cnt[e1cls], __popc(peers));
+        b0 = __shfl_sync(0xFFFFFFFFu, b0, leader);
+        const uint32_t rank = b0 + __popc(peers & ((1u << lane) - 1u));
+        __syncthreads();
+        if (e1cls < 16u) {
+          uint32_t off = 0;
+          for (uint32_t k = 0; k < e1cls; k++) off += sh.e1cnt[k];
+          sh.list[off + rank] = (uint16_t)tid;
+        }
+      }
+#else
+      if (etc1_at != 0xFFFFu) {
+        const uint32_t js = ub::etc1_job_slots(cfg.level, cfg.flags), nf = js & 3u, ni = js >> 2;
+        ub::Etc1JobOut jobs[4];
+        for (uint32_t k = 0; k < nf * ni; k++) ub::etc1_hints_job(wmode, px, dec, cfg.level, cfg.flags, k / ni, k % ni, jobs[k]);
+        ub::j_finish_tail(packed, etc1_at, jobs, nf * ni);
+      }
+#endif
+    }
+#if EJ_ETC1_JOBS
+    __syncthreads();
+
+    // ---- ETC1 hint jobs: warp-jobs over ((flip slot, colour mode), 32 non-solid blocks).  The search is the largest single item
+    // of the encoder and its cost differs 20-fold between blocks (modes with and without a bias field, the range-dependent
+    // table limit): as jobs, the lanes of a warp run one (flip, colour mode) pair and no warp waits for one unlucky block.
+    const uint32_t e1_slots = ub::etc1_job_slots(cfg.level, cfg.flags), e1_nf = e1_slots & 3u, e1_ni = e1_slots >> 2;
+    {
+      const uint32_t n_blocks = c0 + c1 + c2 + c3, per_slot = (n_blocks + 31u) >> 5, total = per_slot * e1_nf * e1_ni;
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[3], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= total) break;
+        const uint32_t n_slots = e1_nf * e1_ni, slot = w % n_slots, r = (w / n_slots) * 32 + lane;   // dearest chunks first, all their slots
+        if (r < n_blocks) {
+          const uint32_t b = sh.list[r];
+          uint32_t px[16], dec[16];
+#pragma unroll
+          for (uint32_t j = 0; j < 16; j++) { px[j] = sh.px[b * 17 + j]; dec[j] = ej_ld(gdec + j * EJ_T + b); }
+          ub::Etc1JobOut o;
+          ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, slot % e1_ni, o);
+          ej_st(ge1 + slot * EJ_T + b, make_uint4((uint32_t)o.err, (uint32_t)(o.err >> 32), o.hint, 0u));
+        }
+      }
+    }
+    __syncthreads();
+#endif
+
+    // ---- finish, tail: thread = block
+    if (live) {
+#if EJ_ETC1_JOBS
+      if (etc1_at != 0xFFFFu) {
+        ub::Etc1JobOut jobs[4];
+        for (uint32_t k = 0; k < e1_nf * e1_ni; k++) {
+          const uint4 v = ej_ld(ge1 + k * EJ_T + tid);
+          jobs[k].err = (uint64_t)v.x | ((uint64_t)v.y << 32); jobs[k].hint = v.z; jobs[k].pad_ = 0;
+        }
+        ub::j_finish_tail(packed, etc1_at, jobs, e1_nf * e1_ni);
+      }
+#endif
+      *dst = make_uint4((uint32_t)packed.lo, (uint32_t)(packed.lo >> 32), (uint32_t)packed.hi, (uint32_t)(packed.hi >> 32));
     }
     __syncthreads();
   }
@@ -1210,7 +1313,7 @@ __global__ void __launch_bounds__(256) k_mip_down(const uint32_t* __restrict__ s
 // held until the process exits.  Size: the tile counter + 1080 B x EJ_T blocks for each of at most B200_NOALLOC_MAX_CTAS
 // resident tiles (one per SM of a B200).
 constexpr unsigned B200_NOALLOC_MAX_CTAS = 148 * EJ_MIN_CTAS;   // every resident CTA of a B200
-constexpr size_t B200_NOALLOC_SCRATCH_BYTES = EJ_SCRATCH_HEADER + (size_t)B200_NOALLOC_MAX_CTAS * EJ_SCRATCH_PER_CTA;   // ~117 MiB
+constexpr size_t B200_NOALLOC_SCRATCH_BYTES = EJ_SCRATCH_HEADER + (size_t)B200_NOALLOC_MAX_CTAS * EJ_SCRATCH_PER_CTA;   // ~131 MiB
 static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
 
 namespace {

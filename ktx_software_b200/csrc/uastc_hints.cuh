@@ -340,62 +340,153 @@ UB_FN void etc1_sub_finish(Etc1Sub& sb) {
   }
 }
 
+// The two sub-block views of one flip.
+UB_FN void etc1_hints_setup(Etc1Sub* sub, uint32_t flip, const uint32_t* px, const uint32_t* dec) {
+#pragma unroll 1
+  for (uint32_t s = 0; s < 2; s++) {
+#pragma unroll 1
+    for (uint32_t j = 0; j < 8; j++) {
+      const uint32_t t = etc1_texel(flip, s, j);
+      etc1_sub_set_texel(sub[s], j, dec[t], px[t]);
+    }
+    etc1_sub_finish(sub[s]);
+  }
+}
+
+// All bias trials of one (flip, colour mode): improves (best_err, o_*) where a trial is strictly better, in trial order.
+UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t flip, uint32_t individ, uint32_t level, uint64_t& best_err,
+                             uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
+  // The result for a sub-block depends only on its base colour (given flip and the decoded texels), and bias
+  // trials that step the sub-block's base colour alike share a memo slot (etc1_bias_slot): evaluate once per slot
+  // unless the colour differs after all (differential mode couples the second sub-block to the first).
+  uint32_t memo_key[2][16];
+  uint8_t memo_inten[2][16];
+  uint64_t memo_err[2][16];
+#pragma unroll 1
+  for (uint32_t i = 0; i < 16; i++) { memo_key[0][i] = 0; memo_key[1][i] = 0; }
+#pragma unroll 1
+  for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
+    int base8[2][3];
+    uint32_t bias;
+    etc1_base_colors(sub[0].sum, sub[1].sum, pl, individ, bi, base8, bias);
+    uint32_t best_inten[2] = {0, 0};
+    uint64_t err = 0;
+#pragma unroll 1
+    for (uint32_t s = 0; s < 2; s++) {
+      const int* b8 = s ? base8[1] : base8[0];
+      const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
+      const uint32_t slot = UBT(etc1_bias_slot)[(pl.use_table ? 0u : 64u) + s * 32 + bi];
+      if (memo_key[s][slot] == key) { best_inten[s] = memo_inten[s][slot]; err += memo_err[s][slot]; continue; }
+      uint32_t bi_s;
+      uint64_t err_s;
+      etc1_eval_subblock(sub[s], b8, flip, level, bi_s, err_s);
+      best_inten[s] = bi_s;
+      err += err_s;
+      memo_key[s][slot] = key; memo_inten[s][slot] = (uint8_t)bi_s; memo_err[s][slot] = err_s;
+    }
+    if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
+  }
+}
+
+// Which (flip, colour mode) pairs the search visits, in its order: flips [first, last), colour modes [0, last_individ).
+UB_FN void etc1_hints_range(const Etc1Plan& pl, uint32_t flags, const uint32_t* dec, uint32_t& first_flip, uint32_t& last_flip) {
+  first_flip = 0; last_flip = 2;
+  if (flags & 256u) last_flip = 1;
+  else if (pl.flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
+}
+
 // One thread, one block.
 UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags,
                               uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
   const Etc1Plan pl = etc1_plan(mode, level, flags);
-  uint32_t first_flip = 0, last_flip = 2;
-  if (flags & 256u) last_flip = 1;
-  else if (pl.flip_estimate) { if (etc1_estimate_flipped(dec)) first_flip = 1; last_flip = first_flip + 1; }
-
+  uint32_t first_flip, last_flip;
+  etc1_hints_range(pl, flags, dec, first_flip, last_flip);
   uint64_t best_err = ~0ull;
   o_flip = 0; o_diff = 0; o_i0 = 0; o_i1 = 0; o_bias = 0;
   Etc1Sub sub[2];
 #pragma unroll 1
   for (uint32_t flip = first_flip; flip < last_flip; flip++) {
+    etc1_hints_setup(sub, flip, px, dec);
 #pragma unroll 1
-    for (uint32_t s = 0; s < 2; s++) {
-#pragma unroll 1
-      for (uint32_t j = 0; j < 8; j++) {
-        const uint32_t t = etc1_texel(flip, s, j);
-        etc1_sub_set_texel(sub[s], j, dec[t], px[t]);
-      }
-      etc1_sub_finish(sub[s]);
-    }
-#pragma unroll 1
-    for (uint32_t individ = 0; individ < pl.last_individ; individ++) {
-      // The result for a sub-block depends only on its base colour (given flip and the decoded texels), and bias
-      // trials that step the sub-block's base colour alike share a memo slot (etc1_bias_slot): evaluate once per slot
-      // unless the colour differs after all (differential mode couples the second sub-block to the first).
-      uint32_t memo_key[2][16];
-      uint8_t memo_inten[2][16];
-      uint64_t memo_err[2][16];
-#pragma unroll 1
-      for (uint32_t i = 0; i < 16; i++) { memo_key[0][i] = 0; memo_key[1][i] = 0; }
-#pragma unroll 1
-      for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
-        int base8[2][3];
-        uint32_t bias;
-        etc1_base_colors(sub[0].sum, sub[1].sum, pl, individ, bi, base8, bias);
-        uint32_t best_inten[2] = {0, 0};
-        uint64_t err = 0;
-#pragma unroll 1
-        for (uint32_t s = 0; s < 2; s++) {
-          const int* b8 = s ? base8[1] : base8[0];
-          const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
-          const uint32_t slot = UBT(etc1_bias_slot)[(pl.use_table ? 0u : 64u) + s * 32 + bi];
-          if (memo_key[s][slot] == key) { best_inten[s] = memo_inten[s][slot]; err += memo_err[s][slot]; continue; }
-          uint32_t bi_s;
-          uint64_t err_s;
-          etc1_eval_subblock(sub[s], b8, flip, level, bi_s, err_s);
-          best_inten[s] = bi_s;
-          err += err_s;
-          memo_key[s][slot] = key; memo_inten[s][slot] = (uint8_t)bi_s; memo_err[s][slot] = err_s;
-        }
-        if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
-      }
+    for (uint32_t individ = 0; individ < pl.last_individ; individ++)
+      etc1_hints_search(pl, sub, flip, individ, level, best_err, o_flip, o_diff, o_i0, o_i1, o_bias);
+  }
+}
+
+// The same search as independent jobs (uastc_jobs.cuh): job (fslot, individ) of a block returns the best trial of ITS
+// (flip, colour mode) pair; etc1_hints_combine over the jobs in (fslot, individ) order with a strict compare picks what the
+// loop above picks.  fslot counts from the block's first flip.  A job outside the block's range returns err = ~0.
+struct Etc1JobOut { uint64_t err; uint32_t hint; uint32_t pad_; };   // hint = flip | diff << 1 | inten0 << 2 | inten1 << 5 | bias << 8
+UB_FN uint32_t etc1_job_slots(uint32_t level, uint32_t flags) {   // bit 0..1: flip slots, bit 2..3: colour modes (uniform over a launch)
+  const Etc1Plan pl = etc1_plan(0, level, flags);
+  const uint32_t nf = ((flags & 256u) || pl.flip_estimate) ? 1u : 2u;
+  return nf | (pl.last_individ << 2);
+}
+// Cost class of a block's ETC1 hint search, 0 (dearest) .. ETC1_COST_CLASSES - 1: a proxy, used only to put blocks of similar
+// cost into one warp.  A sub-block evaluation scans 2 / 4 / 8 intensity tables (by the range of its texels around the base
+// colour), and a table whose modifiers push the base colour past 0 or 255 takes the clamping path, ~8x the plain one; lanes on
+// the plain path idle while one lane of the warp clamps.  The proxy counts, per sub-block view, tables and clamping tables for
+// the view's average colour.
+const uint32_t ETC1_COST_CLASSES = 12;
+UB_FN uint32_t etc1_cost_class(uint32_t mode, const uint32_t* dec) {
+  // per 2x2 quadrant and channel: sum, min, max; the four sub-block views (flip 0: left / right, flip 1: top / bottom) pair them up
+  int qs[4][3], qmn[4][3], qmx[4][3];
+#pragma unroll
+  for (uint32_t q = 0; q < 4; q++) {
+    const uint32_t t0 = (q >> 1) * 8 + (q & 1u) * 2;
+#pragma unroll
+    for (uint32_t c = 0; c < 3; c++) {
+      const int a = (int)ch(dec[t0], c), b = (int)ch(dec[t0 + 1], c), d = (int)ch(dec[t0 + 4], c), e = (int)ch(dec[t0 + 5], c);
+      qs[q][c] = a + b + d + e;
+      const int m0 = a < b ? a : b, m1 = d < e ? d : e, x0 = a > b ? a : b, x1 = d > e ? d : e;
+      qmn[q][c] = m0 < m1 ? m0 : m1; qmx[q][c] = x0 > x1 ? x0 : x1;
     }
   }
+  uint32_t cost = 0;
+#pragma unroll
+  for (uint32_t v = 0; v < 4; v++) {
+    const uint32_t qa = (v == 0) ? 0u : (v == 1) ? 1u : (v == 2) ? 0u : 2u, qb = (v == 0) ? 2u : (v == 1) ? 3u : (v == 2) ? 1u : 3u;
+    int range = 0, amin = 255, amax = 0;
+#pragma unroll
+    for (uint32_t c = 0; c < 3; c++) {
+      const int avg = (qs[qa][c] + qs[qb][c] + 4) >> 3;
+      const int mn = qmn[qa][c] < qmn[qb][c] ? qmn[qa][c] : qmn[qb][c], mx = qmx[qa][c] > qmx[qb][c] ? qmx[qa][c] : qmx[qb][c];
+      const int r = (mx - avg) > (avg - mn) ? (mx - avg) : (avg - mn);
+      range = r > range ? r : range;
+      amin = avg < amin ? avg : amin; amax = avg > amax ? avg : amax;
+    }
+    const int room = amin < 255 - amax ? amin : 255 - amax;   // a table clamps when its larger modifier exceeds this
+    // larger modifiers of the tables: 8, 17, 29, 42, 60, 80, 106, 183
+    const uint32_t plain = (room >= 8) + (room >= 17) + (room >= 29) + (room >= 42) + (room >= 60) + (room >= 80) + (room >= 106) + (room >= 183);
+    const uint32_t limit = (range > 51) ? 8u : (range >= 7 ? 4u : 2u);
+    const uint32_t n_plain = plain < limit ? plain : limit;
+    cost += n_plain + 8u * (limit - n_plain);
+  }
+  // cost: 8 .. 256, halving classes
+  uint32_t cls = cost >= 192u ? 0u : cost >= 128u ? 1u : cost >= 96u ? 2u : cost >= 64u ? 3u : cost >= 48u ? 4u : cost >= 32u ? 5u :
+                 cost >= 24u ? 6u : cost >= 16u ? 7u : cost >= 12u ? 8u : cost >= 9u ? 9u : 10u;
+  return UBT(uastc_mode_has_etc1_bias)[mode] ? cls : 11u;
+}
+
+UB_BIG void etc1_hints_job(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags, uint32_t fslot, uint32_t individ,
+                          Etc1JobOut& o) {
+  const Etc1Plan pl = etc1_plan(mode, level, flags);
+  uint32_t first_flip, last_flip;
+  etc1_hints_range(pl, flags, dec, first_flip, last_flip);
+  o.err = ~0ull; o.hint = 0; o.pad_ = 0;
+  const uint32_t flip = first_flip + fslot;
+  if (flip >= last_flip || individ >= pl.last_individ) return;
+  Etc1Sub sub[2];
+  etc1_hints_setup(sub, flip, px, dec);
+  uint32_t f = 0, d = 0, i0 = 0, i1 = 0, bias = 0;
+  etc1_hints_search(pl, sub, flip, individ, level, o.err, f, d, i0, i1, bias);
+  o.hint = f | (d << 1) | (i0 << 2) | (i1 << 5) | (bias << 8);
+}
+UB_FN void etc1_hints_combine(const Etc1JobOut* jobs, uint32_t n, uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
+  uint64_t best = ~0ull;
+  uint32_t h = 0;
+  for (uint32_t i = 0; i < n; i++) if (jobs[i].err < best) { best = jobs[i].err; h = jobs[i].hint; }
+  o_flip = h & 1u; o_diff = (h >> 1) & 1u; o_i0 = (h >> 2) & 7u; o_i1 = (h >> 5) & 7u; o_bias = h >> 8;
 }
 
 // ---------------------------------------------------------------------------------------------------------

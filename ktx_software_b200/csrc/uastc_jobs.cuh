@@ -205,6 +205,53 @@ UB_FN Bits128 j_finish(const uint32_t* px, uint32_t flags, const Candidate* bc, 
   return r;
 }
 
+// ---- the block job split around the ETC1 hint jobs.  j_finish_head does everything of j_finish except the ETC1 hint search:
+// the block comes out packed with the ETC1 hint fields (flip, diff, inten0, inten1[, bias]: one contiguous bit field right
+// behind the mode code and the BC1 hint bits, ENC pack_uastc :111-135) left zero, `dec` holds the decoded winner and
+// `etc1_at` the bit position of that field | has_bias << 8 (0xFFFF: nothing to fill in, solid or dead block).
+UB_FN Bits128 j_finish_head(const uint32_t* px, uint32_t flags, const Candidate* bc, bool live, bool solid, bool cta_sync, uint32_t* dec,
+                            uint32_t& mode, uint32_t& etc1_at) {
+  BlockHints h;
+  memset(&h, 0, sizeof(h));
+  EncCfg cfg = enc_cfg_from_flags(flags);
+  cfg.cta_sync = cta_sync;
+  const bool active = live && !solid;
+  Candidate nc;
+  mode = UASTC_MODE_SOLID; etc1_at = 0xFFFFu;
+  if (active) {
+    decode_uastc_pixels(*bc, dec);
+    normalize_candidate(*bc, nc);
+    mode = nc.mode;
+  }
+  UB_STAGE_SYNC(cfg);
+  if (cfg.bc1_hints) { if (active) compute_bc1_hints(nc, px, dec, h.bc1_hint0, h.bc1_hint1); UB_STAGE_SYNC(cfg); }
+  Bits128 r;
+  r.lo = 0; r.hi = 0;
+  if (active) {
+    const uint32_t d = UBT(uastc_mode_desc)[nc.mode];
+    h.etc2_hints = (md_comps(d) != 3) ? compute_eac_hint(dec, cfg.eac_mul_rad, cfg.eac_table_mask) : 0u;
+    r = pack_uastc(nc, 0, h);
+    etc1_at = (md_huff_len(d) + UBT(uastc_mode_has_bc1_hint0)[nc.mode] + UBT(uastc_mode_has_bc1_hint1)[nc.mode]) |
+              ((uint32_t)UBT(uastc_mode_has_etc1_bias)[nc.mode] << 8);
+  } else if (live) {
+    Candidate c;
+    memset(&c, 0, sizeof(c));
+    c.mode = UASTC_MODE_SOLID;
+    hints_solid_etc1(px[0], h.etc1_diff, h.etc1_inten0, h.etc1_selector, h.etc1_r, h.etc1_g, h.etc1_b);
+    r = pack_uastc(c, px[0], h);
+  }
+  return r;
+}
+// ... and the tail: the ETC1 hint jobs' results (in (flip slot, colour mode) order) into the packed block.
+UB_FN void j_finish_tail(Bits128& r, uint32_t etc1_at, const Etc1JobOut* jobs, uint32_t n) {
+  if (etc1_at == 0xFFFFu) return;
+  uint32_t flip, diff, i0, i1, bias;
+  etc1_hints_combine(jobs, n, flip, diff, i0, i1, bias);
+  uint32_t f = flip | (diff << 1) | (i0 << 2) | (i1 << 5);
+  if (etc1_at >> 8) f |= bias << 8;
+  r.lo |= (uint64_t)f << (etc1_at & 255u);   // the field ends below bit 64 in every mode (7 + 2 + 13 bits at most)
+}
+
 // The jobs of one block run one after the other: what the CUDA kernel computes, in the order a single thread would.
 // (Host checker; levels 0-3 only.)
 UB_FN Bits128 encode_uastc_block_jobs(const uint32_t* px, uint32_t flags) {
@@ -235,7 +282,14 @@ UB_FN Bits128 encode_uastc_block_jobs(const uint32_t* px, uint32_t flags) {
     }
   const uint32_t gs = slot[j_select(n, overall, uerr, modes, flags)];
   j_assemble(gs, parts, cells + jc_cell0(UBT(j_cand)[gs]), c);
-  return j_finish(px, flags, &c, true, false, false);
+  uint32_t dec[16], mode, etc1_at;
+  Bits128 r = j_finish_head(px, flags, &c, true, false, false, dec, mode, etc1_at);
+  const uint32_t js = etc1_job_slots(cfg.level, cfg.flags), nf = js & 3u, ni = js >> 2;
+  Etc1JobOut jobs[4];
+  for (uint32_t f = 0; f < nf; f++)
+    for (uint32_t i = 0; i < ni; i++) etc1_hints_job(mode, px, dec, cfg.level, cfg.flags, f, i, jobs[f * ni + i]);
+  j_finish_tail(r, etc1_at, jobs, nf * ni);
+  return r;
 }
 
 }  // namespace ub
