@@ -929,13 +929,14 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         w = __shfl_sync(0xFFFFFFFFu, w, 0);
         if (w >= total) break;
         const uint32_t n_slots = e1_nf * e1_ni, slot = w % n_slots, r = (w / n_slots) * 32 + lane;   // dearest chunks first, all their slots
+        const uint32_t together = __ballot_sync(0xFFFFFFFFu, r < n_blocks);
         if (r < n_blocks) {
           const uint32_t b = sh.list[r];
           uint32_t px[16], dec[16];
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) { px[j] = sh.px[b * 17 + j]; dec[j] = ej_ld(gdec + j * EJ_T + b); }
           ub::Etc1JobOut o;
-          ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, slot % e1_ni, o);
+          ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, slot % e1_ni, o, together);
           ej_st(ge1 + slot * EJ_T + b, make_uint4((uint32_t)o.err, (uint32_t)(o.err >> 32), o.hint, 0u));
         }
       }

@@ -147,7 +147,7 @@ struct EtcMoments {
 // One ETC1 sub-block's view of a block under a given flip: the 8 decoded texels (selectors are picked on these) and the
 // 8 source texels (the reported error is against these), plus what the search needs of them in aggregate.
 struct Etc1Sub {
-  int dy[8], dcr[8], dcb[8];    // decoded texels: luma (not doubled), chroma
+  int dy[8], ndcr[8], ndcb[8];  // decoded texels: luma (not doubled), chroma NEGATED (the form the clamping-table scan multiplies)
   int sy2[8], scr[8], scb[8];   // source texels: doubled luma, chroma
   uint32_t drgb[8];             // decoded texels, packed
   EtcMoments dmom, smom;
@@ -201,13 +201,14 @@ UB_FN void etc1_base_colors(const uint32_t* sum0, const uint32_t* sum1, const Et
   }
 }
 
-// One colour of an ETC1 sub-block (base + modifier, clamped) prepared for distance tests against many texels.
+// One colour P of an ETC1 sub-block (base + modifier, clamped) prepared for distance tests against many texels T, in the
+// weighted (2y, cr, cb) space: |P - T|^2 - |T|^2 = |P|^2 - 2 P.T.  The scan wants, per texel, the entry of least distance, the
+// lowest entry index among equals: all of it times four with the entry index in the two low bits makes that ONE 64-bit minimum
+// (4 g + k orders like (g, k)), and the index comes back out of the winner's low bits.
 struct EtcEntry {
-  int64_t norm;     // 4 y^2 + cr^2 + cb^2
-  int my, mcr, mcb; // -8 y, -2 cr, -2 cb
-  UB_MFN int64_t dist_less_norm(int ty, int tcr, int tcb) const {  // squared distance to the texel minus the texel's own norm
-    return norm + (int64_t)my * ty + (int64_t)mcr * tcr + (int64_t)mcb * tcb;
-  }
+  int64_t n4k;      // 4 (4 y^2 + cr^2 + cb^2) + k
+  int a4, b4, c4;   // 32 y, 8 cr, 8 cb: multiplied by the NEGATED texel (-ty, -tcr, -tcb)
+  UB_MFN int64_t d4(int nty, int ntcr, int ntcb) const { return n4k + (int64_t)a4 * nty + (int64_t)b4 * ntcr + (int64_t)c4 * ntcb; }
 };
 UB_FN void etc1_table_entries(const int* base8, uint32_t inten, EtcEntry* e) {
 #pragma unroll
@@ -215,107 +216,15 @@ UB_FN void etc1_table_entries(const int* base8, uint32_t inten, EtcEntry* e) {
     const int m = UBT(etc1_inten)[inten * 4 + k];
     const int r = clamp255(base8[0] + m), g = clamp255(base8[1] + m), b = clamp255(base8[2] + m);
     const int y = r * 54 + g * 183 + b * 19, cr = (r << 8) - y, cb = (b << 8) - y;
-    e[k].norm = 4 * (int64_t)y * y + (int64_t)cr * cr + (int64_t)cb * cb;
-    e[k].my = -8 * y; e[k].mcr = -2 * cr; e[k].mcb = -2 * cb;
+    e[k].n4k = 4 * (4 * (int64_t)y * y + (int64_t)cr * cr + (int64_t)cb * cb) + (int64_t)k;
+    e[k].a4 = 32 * y; e[k].b4 = 8 * cr; e[k].c4 = 8 * cb;
   }
-}
-
-// Best intensity table of one sub-block for base colour b8, and its error against the source texels.  The result
-// depends only on (flip, sub-block, b8), which is what lets callers evaluate each distinct base colour once.
-UB_FN void etc1_eval_subblock(const Etc1Sub& sb, const int* b8, uint32_t flip, uint32_t level, uint32_t& o_inten, uint64_t& o_err) {
-  int range = 0;
-#pragma unroll
-  for (uint32_t c = 0; c < 3; c++) {
-    int a = sb.mx[c] - b8[c]; if (a < 0) a = -a;
-    int b = b8[c] - sb.mn[c]; if (b < 0) b = -b;
-    if (a > range) range = a;
-    if (b > range) range = b;
-  }
-  const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
-  const Ycc2 by = to_ycc2((uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16));
-  const int yb = by.y2 >> 1;
-  const int bmin = b8[0] < b8[1] ? (b8[0] < b8[2] ? b8[0] : b8[2]) : (b8[1] < b8[2] ? b8[1] : b8[2]);
-  const int bmax = b8[0] > b8[1] ? (b8[0] > b8[2] ? b8[0] : b8[2]) : (b8[1] > b8[2] ? b8[1] : b8[2]);
-  const uint64_t ksum = sb.dmom.chroma_sum(by);
-  uint64_t best_sub = ~0ull;
-  uint32_t bi_s = 0;
-#pragma unroll 1
-  for (uint32_t it = 0; it < limit; it++) {
-    const int m0 = UBT(etc1_inten)[it * 4 + 2], m1 = UBT(etc1_inten)[it * 4 + 3];  // table = {-m1, -m0, m0, m1}
-    uint64_t total = 0;
-    if (bmin - m1 >= 0 && bmax + m1 <= 255) {
-      // No entry clamps: all four share the base chroma and sit at luma yb + 256*m.  The nearest entry to a
-      // texel follows from |dy| against the midpoint 128*(m0+m1); the squared distance fits 32 bits.
-      const int mid = 128 * (m0 + m1), o0 = 256 * m0, o1 = 256 * m1;
-#pragma unroll
-      for (uint32_t j = 0; j < 8; j++) {
-        int d = sb.dy[j] - yb; d = d < 0 ? -d : d;
-        const int x = d - (d < mid ? o0 : o1);
-        total += (uint32_t)(x * x);
-      }
-      total = total * 4 + ksum;
-    } else {
-      // Some entry clamps.  |P - T|^2 = |P|^2 - 2 P.T + |T|^2 in the weighted (2y, cr, cb) space: per entry the constant
-      // |P|^2 and three coefficients, per texel three multiply-adds and a compare; sum |T|^2 is a sub-block constant.
-      EtcEntry e[4];
-      etc1_table_entries(b8, it, e);
-      int64_t acc = sb.dnorm;
-#pragma unroll 1
-      for (uint32_t j = 0; j < 8; j++) {
-        const int ty = sb.dy[j], tcr = sb.dcr[j], tcb = sb.dcb[j];
-        int64_t m = e[0].dist_less_norm(ty, tcr, tcb);
-#pragma unroll
-        for (uint32_t k = 1; k < 4; k++) {
-          const int64_t g = e[k].dist_less_norm(ty, tcr, tcb);
-          m = g < m ? g : m;
-        }
-        acc += m;
-      }
-      total = (uint64_t)acc;
-    }
-    // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
-    if (!flip && total >= best_sub) break;
-    if (total < best_sub) { best_sub = total; bi_s = it; }
-  }
-  // error of the chosen table against the ORIGINAL texels (selectors still picked on the decoded ones; equal
-  // distances keep the lowest entry index)
-  uint64_t err_s = 0;
-  const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
-  if (bmin - m1 >= 0 && bmax + m1 <= 255) {
-    const int mid = 128 * (m0 + m1);
-#pragma unroll
-    for (uint32_t j = 0; j < 8; j++) {
-      const int sd = sb.dy[j] - yb, d = sd < 0 ? -sd : sd;
-      // entries by luma: k0 = -m1, k1 = -m0, k2 = +m0, k3 = +m1
-      const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
-      err_s += sq64(sb.sy2[j] - (by.y2 + 512 * m));
-    }
-    err_s += sb.smom.chroma_sum(by);
-  } else {
-    EtcEntry e[4];
-    etc1_table_entries(b8, bi_s, e);
-#pragma unroll 1
-    for (uint32_t j = 0; j < 8; j++) {
-      const int ty = sb.dy[j], tcr = sb.dcr[j], tcb = sb.dcb[j];
-      int64_t m = e[0].dist_less_norm(ty, tcr, tcb);
-      EtcEntry pick = e[0];
-#pragma unroll
-      for (uint32_t k = 1; k < 4; k++) {
-        const int64_t g = e[k].dist_less_norm(ty, tcr, tcb);
-        if (g < m) { m = g; pick = e[k]; }
-      }
-      // distance of the source texel to the picked entry: |P|^2 - 2 P.S + |S|^2
-      const int sy = sb.sy2[j] >> 1, scr = sb.scr[j], scb = sb.scb[j];
-      err_s += (uint64_t)(pick.dist_less_norm(sy, scr, scb) + 4 * (int64_t)sy * sy + (int64_t)scr * scr + (int64_t)scb * scb);
-    }
-  }
-  o_inten = bi_s; o_err = err_s;
 }
 
 // Texel j of sub-block s under `flip` into the sub-block view; etc1_sub_finish then derives the aggregates.
 UB_FN void etc1_sub_set_texel(Etc1Sub& sb, uint32_t j, uint32_t dec_px, uint32_t src_px) {
   const Ycc2 d = to_ycc2(dec_px), q = to_ycc2(src_px);
-  sb.dy[j] = d.y2 >> 1; sb.dcr[j] = d.cr; sb.dcb[j] = d.cb;
+  sb.dy[j] = d.y2 >> 1; sb.ndcr[j] = -d.cr; sb.ndcb[j] = -d.cb;
   sb.sy2[j] = q.y2; sb.scr[j] = q.cr; sb.scb[j] = q.cb;
   sb.drgb[j] = dec_px;
 }
@@ -333,7 +242,7 @@ UB_FN void etc1_sub_finish(Etc1Sub& sb) {
       sb.mn[c] = v < sb.mn[c] ? v : sb.mn[c];
       sb.mx[c] = v > sb.mx[c] ? v : sb.mx[c];
     }
-    Ycc2 d; d.y2 = 0; d.cr = sb.dcr[j]; d.cb = sb.dcb[j];
+    Ycc2 d; d.y2 = 0; d.cr = -sb.ndcr[j]; d.cb = -sb.ndcb[j];
     Ycc2 q; q.y2 = 0; q.cr = sb.scr[j]; q.cb = sb.scb[j];
     sb.dmom.add(d); sb.smom.add(q);
     sb.dnorm += 4 * (int64_t)sb.dy[j] * sb.dy[j] + (int64_t)d.cr * d.cr + (int64_t)d.cb * d.cb;
@@ -354,37 +263,191 @@ UB_FN void etc1_hints_setup(Etc1Sub* sub, uint32_t flip, const uint32_t* px, con
 }
 
 // All bias trials of one (flip, colour mode): improves (best_err, o_*) where a trial is strictly better, in trial order.
+//
+// An evaluation = one (sub-block, base colour): scan 2 / 4 / 8 intensity tables (by the range of the texels around the base
+// colour) for the lowest error against the DECODED texels -- in table order, first of equals, and in the non-flipped layout the
+// scan stops at the first table that does not improve -- then report the chosen table's error against the SOURCE texels.  Its
+// result depends only on (flip, sub-block, base colour): bias trials that step a sub-block's base colour alike share it.
+//
+// The scan of a table whose modifiers push the base colour past 0 or 255 (4 clamped entries x 8 texels of 64-bit distance
+// arithmetic, ~8x a plain table) is most of the search.  Run trial by trial, a warp paid for it whenever ANY lane's current table
+// clamped while the other lanes waited (13 of 32 lanes active on those lines).  So the search runs in four passes:
+//   1  per trial: base colours, the distinct evaluations listed (memo by slot, as the reference's trial order finds them), their
+//      plain tables scanned (the tables' larger modifiers grow with the table index, so an evaluation's tables are plain below
+//      n_plain and clamping from there on);
+//   2  the clamping tables: every lane walks ITS list of open evaluations, one clamping table per step, the lanes of the warp
+//      stepping together -- no lane waits for another's table, only for the lane with the most of them at the very end;
+//   3  per evaluation: the chosen table's error against the source texels (a clamping table reuses the entry picks recorded
+//      when it was scored);
+//   4  per trial, in trial order: the sum of its two evaluations against the best so far.
+// `lanes` (device): the lanes of the warp that run this call together -- they step through pass 2 together; 0 = the caller's
+// lanes are not known to be together (thread = block callers).
+struct Etc1Eval {
+  uint32_t key;     // base colour, r | g << 8 | b << 16
+  uint32_t st;      // sub-block | limit << 4 | n_plain << 8 | next table << 12 (== limit: scan over) | best table << 16
+  uint64_t best;    // lowest table error so far; after pass 3 the error against the source texels
+  uint32_t picks;   // entry of every texel (2 bits each) under the best table, when that is a clamping one
+  uint32_t pad_;
+};
 UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t flip, uint32_t individ, uint32_t level, uint64_t& best_err,
-                             uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
-  // The result for a sub-block depends only on its base colour (given flip and the decoded texels), and bias
-  // trials that step the sub-block's base colour alike share a memo slot (etc1_bias_slot): evaluate once per slot
-  // unless the colour differs after all (differential mode couples the second sub-block to the first).
-  uint32_t memo_key[2][16];
-  uint8_t memo_inten[2][16];
-  uint64_t memo_err[2][16];
+                             uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias, uint32_t lanes = 0) {
+  Etc1Eval ev[64];          // at most two new evaluations per trial, at most 32 trials
+  uint8_t slot_ev[2][16];   // the evaluation a memo slot (etc1_bias_slot) holds; differential mode couples the second sub-block's
+                            // colour to the first's, so a slot can meet a second colour: that is a new evaluation
+  uint8_t trial_ev[32][2];
+  uint32_t n_ev = 0;
 #pragma unroll 1
-  for (uint32_t i = 0; i < 16; i++) { memo_key[0][i] = 0; memo_key[1][i] = 0; }
+  for (uint32_t i = 0; i < 16; i++) { slot_ev[0][i] = 0xFF; slot_ev[1][i] = 0xFF; }
+  // ---- pass 1
 #pragma unroll 1
   for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
     int base8[2][3];
     uint32_t bias;
     etc1_base_colors(sub[0].sum, sub[1].sum, pl, individ, bi, base8, bias);
-    uint32_t best_inten[2] = {0, 0};
-    uint64_t err = 0;
 #pragma unroll 1
     for (uint32_t s = 0; s < 2; s++) {
       const int* b8 = s ? base8[1] : base8[0];
-      const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16) | 0x80000000u;
+      const uint32_t key = (uint32_t)b8[0] | ((uint32_t)b8[1] << 8) | ((uint32_t)b8[2] << 16);
       const uint32_t slot = UBT(etc1_bias_slot)[(pl.use_table ? 0u : 64u) + s * 32 + bi];
-      if (memo_key[s][slot] == key) { best_inten[s] = memo_inten[s][slot]; err += memo_err[s][slot]; continue; }
-      uint32_t bi_s;
-      uint64_t err_s;
-      etc1_eval_subblock(sub[s], b8, flip, level, bi_s, err_s);
-      best_inten[s] = bi_s;
-      err += err_s;
-      memo_key[s][slot] = key; memo_inten[s][slot] = (uint8_t)bi_s; memo_err[s][slot] = err_s;
+      const uint32_t held = slot_ev[s][slot];
+      if (held != 0xFFu && ev[held].key == key) { trial_ev[bi][s] = (uint8_t)held; continue; }
+      const Etc1Sub& sb = sub[s];
+      int range = 0;
+#pragma unroll
+      for (uint32_t c = 0; c < 3; c++) {
+        int a = sb.mx[c] - b8[c]; if (a < 0) a = -a;
+        int b = b8[c] - sb.mn[c]; if (b < 0) b = -b;
+        if (a > range) range = a;
+        if (b > range) range = b;
+      }
+      const uint32_t limit = (level == 4) ? 8u : ((range > 51) ? 8u : (range >= 7 ? 4u : 2u));
+      const Ycc2 by = to_ycc2(key);
+      const int yb = by.y2 >> 1;
+      const int bmin = b8[0] < b8[1] ? (b8[0] < b8[2] ? b8[0] : b8[2]) : (b8[1] < b8[2] ? b8[1] : b8[2]);
+      const int bmax = b8[0] > b8[1] ? (b8[0] > b8[2] ? b8[0] : b8[2]) : (b8[1] > b8[2] ? b8[1] : b8[2]);
+      const int room = bmin < 255 - bmax ? bmin : 255 - bmax;   // a table is plain while its larger modifier fits
+      // larger modifiers of the tables: 8, 17, 29, 42, 60, 80, 106, 183
+      uint32_t n_plain = (uint32_t)((room >= 8) + (room >= 17) + (room >= 29) + (room >= 42) + (room >= 60) + (room >= 80) + (room >= 106) + (room >= 183));
+      n_plain = n_plain < limit ? n_plain : limit;
+      const uint64_t ksum = sb.dmom.chroma_sum(by);
+      uint64_t best_sub = ~0ull;
+      uint32_t bi_s = 0, it = 0;
+#pragma unroll 1
+      while (it < n_plain) {
+        // No entry clamps: all four share the base chroma and sit at luma yb + 256*m.  The nearest entry to a
+        // texel follows from |dy| against the midpoint 128*(m0+m1); the squared distance fits 32 bits.
+        const int m0 = UBT(etc1_inten)[it * 4 + 2], m1 = UBT(etc1_inten)[it * 4 + 3];  // table = {-m1, -m0, m0, m1}
+        const int mid = 128 * (m0 + m1), o0 = 256 * m0, o1 = 256 * m1;
+        uint64_t total = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < 8; j++) {
+          int d = sb.dy[j] - yb; d = d < 0 ? -d : d;
+          const int x = d - (d < mid ? o0 : o1);
+          total += (uint32_t)(x * x);
+        }
+        total = total * 4 + ksum;
+        // the reference stops scanning tables at the first non-improving one only in the non-flipped layout
+        if (!flip && total >= best_sub) { it = limit; break; }
+        if (total < best_sub) { best_sub = total; bi_s = it; }
+        it++;
+      }
+      Etc1Eval& e = ev[n_ev];
+      e.key = key; e.st = s | (limit << 4) | (n_plain << 8) | (it << 12) | (bi_s << 16); e.best = best_sub; e.picks = 0; e.pad_ = 0;
+      slot_ev[s][slot] = (uint8_t)n_ev; trial_ev[bi][s] = (uint8_t)n_ev;
+      n_ev++;
     }
-    if (err < best_err) { best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = best_inten[0]; o_i1 = best_inten[1]; o_bias = bias; }
+  }
+  // ---- pass 2: one clamping table per step
+  {
+    uint32_t cur = 0;
+    for (;;) {
+#pragma unroll 1
+      while (cur < n_ev && ((ev[cur].st >> 12) & 15u) >= ((ev[cur].st >> 4) & 15u)) cur++;
+      const bool done = cur >= n_ev;
+#ifdef __CUDA_ARCH__
+      if (lanes) { if (!__any_sync(lanes, !done)) break; }
+      else
+#endif
+      if (done) break;
+      if (!done) {
+        // |P - T|^2 = |P|^2 - 2 P.T + |T|^2 in the weighted (2y, cr, cb) space: per entry the constant |P|^2 and three
+        // coefficients, per texel three multiply-adds and a compare; sum |T|^2 is a sub-block constant (EtcEntry)
+        Etc1Eval& e = ev[cur];
+        const uint32_t st = e.st, it = (st >> 12) & 15u, limit = (st >> 4) & 15u;
+        const Etc1Sub& sb = sub[st & 1u];
+        const int b8[3] = {(int)(e.key & 255u), (int)((e.key >> 8) & 255u), (int)((e.key >> 16) & 255u)};
+        EtcEntry en[4];
+        etc1_table_entries(b8, it, en);
+        int64_t acc4 = 0;
+        uint32_t picks = 0;
+#pragma unroll 1
+        for (uint32_t j = 0; j < 8; j++) {
+          const int nty = -sb.dy[j], ntcr = sb.ndcr[j], ntcb = sb.ndcb[j];
+          int64_t m = en[0].d4(nty, ntcr, ntcb);
+#pragma unroll
+          for (uint32_t k = 1; k < 4; k++) {
+            const int64_t g = en[k].d4(nty, ntcr, ntcb);
+            m = g < m ? g : m;
+          }
+          acc4 += m;
+          picks |= ((uint32_t)m & 3u) << (2 * j);
+        }
+        uint32_t ks = (picks & 0x3333u) + ((picks >> 2) & 0x3333u);   // sum of the eight entry indices
+        ks = (ks & 0x0F0Fu) + ((ks >> 4) & 0x0F0Fu);
+        ks = (ks & 0xFFu) + (ks >> 8);
+        const uint64_t total = (uint64_t)(sb.dnorm + ((acc4 - (int64_t)ks) >> 2));   // acc4 - ks = 4 x the sum of the distances, exactly
+        uint32_t next = it + 1;
+        if (!flip && total >= e.best) next = limit;
+        else if (total < e.best) { e.best = total; e.picks = picks; e.st = (st & 0xFFFFu) | (it << 16); }
+        e.st = (e.st & ~0xF000u) | (next << 12);
+      }
+    }
+  }
+  // ---- pass 3: error of the chosen table against the ORIGINAL texels (selectors picked on the decoded ones; equal
+  // distances keep the lowest entry index)
+#pragma unroll 1
+  for (uint32_t i = 0; i < n_ev; i++) {
+    Etc1Eval& e = ev[i];
+    const uint32_t st = e.st, bi_s = st >> 16, n_plain = (st >> 8) & 15u;
+    const Etc1Sub& sb = sub[st & 1u];
+    const Ycc2 by = to_ycc2(e.key);
+    uint64_t err_s = 0;
+    if (bi_s < n_plain) {
+      const int yb = by.y2 >> 1;
+      const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
+      const int mid = 128 * (m0 + m1);
+#pragma unroll
+      for (uint32_t j = 0; j < 8; j++) {
+        const int sd = sb.dy[j] - yb, d = sd < 0 ? -sd : sd;
+        // entries by luma: k0 = -m1, k1 = -m0, k2 = +m0, k3 = +m1
+        const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
+        err_s += sq64(sb.sy2[j] - (by.y2 + 512 * m));
+      }
+      err_s += sb.smom.chroma_sum(by);
+    } else {
+      const int b8[3] = {(int)(e.key & 255u), (int)((e.key >> 8) & 255u), (int)((e.key >> 16) & 255u)};
+      const uint32_t picks = e.picks;
+#pragma unroll 1
+      for (uint32_t j = 0; j < 8; j++) {
+        const int m = UBT(etc1_inten)[bi_s * 4 + ((picks >> (2 * j)) & 3u)];
+        const int r = clamp255(b8[0] + m), g = clamp255(b8[1] + m), b = clamp255(b8[2] + m);
+        const int y = r * 54 + g * 183 + b * 19, cr = (r << 8) - y, cb = (b << 8) - y;
+        const int ey = y - (sb.sy2[j] >> 1), ecr = cr - sb.scr[j], ecb = cb - sb.scb[j];
+        err_s += (uint64_t)(4 * (int64_t)ey * ey + (int64_t)ecr * ecr + (int64_t)ecb * ecb);
+      }
+    }
+    e.best = err_s;
+  }
+  // ---- pass 4
+#pragma unroll 1
+  for (uint32_t bi = 0; bi < pl.last_bias; bi++) {
+    const Etc1Eval& e0 = ev[trial_ev[bi][0]];
+    const Etc1Eval& e1 = ev[trial_ev[bi][1]];
+    const uint64_t err = e0.best + e1.best;
+    if (err < best_err) {
+      best_err = err; o_flip = flip; o_diff = individ ? 0u : 1u; o_i0 = e0.st >> 16; o_i1 = e1.st >> 16;
+      o_bias = pl.use_table ? UBT(etc1_sorted_bias)[bi] : bi;
+    }
   }
 }
 
@@ -468,18 +531,25 @@ UB_FN uint32_t etc1_cost_class(uint32_t mode, const uint32_t* dec) {
   return UBT(uastc_mode_has_etc1_bias)[mode] ? cls : 11u;
 }
 
+// `lanes` (device): mask of the warp's lanes that make this call together (0: unknown, see etc1_hints_search).
 UB_BIG void etc1_hints_job(uint32_t mode, const uint32_t* px, const uint32_t* dec, uint32_t level, uint32_t flags, uint32_t fslot, uint32_t individ,
-                          Etc1JobOut& o) {
+                          Etc1JobOut& o, uint32_t lanes = 0) {
   const Etc1Plan pl = etc1_plan(mode, level, flags);
   uint32_t first_flip, last_flip;
   etc1_hints_range(pl, flags, dec, first_flip, last_flip);
   o.err = ~0ull; o.hint = 0; o.pad_ = 0;
   const uint32_t flip = first_flip + fslot;
-  if (flip >= last_flip || individ >= pl.last_individ) return;
+  const bool none = flip >= last_flip || individ >= pl.last_individ;
+#ifdef __CUDA_ARCH__
+  if (lanes) lanes = __ballot_sync(lanes, !none);
+#endif
+  if (none) return;
   Etc1Sub sub[2];
   etc1_hints_setup(sub, flip, px, dec);
   uint32_t f = 0, d = 0, i0 = 0, i1 = 0, bias = 0;
-  etc1_hints_search(pl, sub, flip, individ, level, o.err, f, d, i0, i1, bias);
+  uint64_t best = ~0ull;
+  etc1_hints_search(pl, sub, flip, individ, level, best, f, d, i0, i1, bias, lanes);
+  o.err = best;
   o.hint = f | (d << 1) | (i0 << 2) | (i1 << 5) | (bias << 8);
 }
 UB_FN void etc1_hints_combine(const Etc1JobOut* jobs, uint32_t n, uint32_t& o_flip, uint32_t& o_diff, uint32_t& o_i0, uint32_t& o_i1, uint32_t& o_bias) {
