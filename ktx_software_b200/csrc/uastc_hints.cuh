@@ -208,7 +208,18 @@ UB_FN void etc1_base_colors(const uint32_t* sum0, const uint32_t* sum1, const Et
 struct EtcEntry {
   int64_t n4k;      // 4 (4 y^2 + cr^2 + cb^2) + k
   int a4, b4, c4;   // 32 y, 8 cr, 8 cb: multiplied by the NEGATED texel (-ty, -tcr, -tcb)
-  UB_MFN int64_t d4(int nty, int ntcr, int ntcb) const { return n4k + (int64_t)a4 * nty + (int64_t)b4 * ntcr + (int64_t)c4 * ntcb; }
+  // c + a * b, 32 x 32 -> 64 signed: one IMAD.WIDE.  (Left to the compiler, the product with a4 -- known to be >= 0 -- became an
+  // unsigned wide multiply plus a three-instruction sign fix-up.)
+  static UB_MFN int64_t mad_wide(int a, int b, int64_t c) {
+#ifdef __CUDA_ARCH__
+    int64_t d;
+    asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+    return d;
+#else
+    return c + (int64_t)a * b;
+#endif
+  }
+  UB_MFN int64_t d4(int nty, int ntcr, int ntcb) const { return mad_wide(c4, ntcb, mad_wide(b4, ntcr, mad_wide(a4, nty, n4k))); }
 };
 UB_FN void etc1_table_entries(const int* base8, uint32_t inten, EtcEntry* e) {
 #pragma unroll
@@ -282,6 +293,10 @@ UB_FN void etc1_hints_setup(Etc1Sub* sub, uint32_t flip, const uint32_t* px, con
 //   4  per trial, in trial order: the sum of its two evaluations against the best so far.
 // `lanes` (device): the lanes of the warp that run this call together -- they step through pass 2 together; 0 = the caller's
 // lanes are not known to be together (thread = block callers).
+#ifndef ETC1_CLAMP_UNROLL
+#define ETC1_CLAMP_UNROLL 1
+#endif
+constexpr int ETC1_CLAMP_UNROLL_N = ETC1_CLAMP_UNROLL;
 struct Etc1Eval {
   uint32_t key;     // base colour, r | g << 8 | b << 16
   uint32_t st;      // sub-block | limit << 4 | n_plain << 8 | next table << 12 (== limit: scan over) | best table << 16
@@ -380,7 +395,7 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
         etc1_table_entries(b8, it, en);
         int64_t acc4 = 0;
         uint32_t picks = 0;
-#pragma unroll 1
+#pragma unroll ETC1_CLAMP_UNROLL_N
         for (uint32_t j = 0; j < 8; j++) {
           const int nty = -sb.dy[j], ntcr = sb.ndcr[j], ntcb = sb.ndcb[j];
           int64_t m = en[0].d4(nty, ntcr, ntcb);
