@@ -207,7 +207,7 @@ int b200_uastc_encode_image_dev(const void* d_rgba, uint32_t width, uint32_t hei
 /* Allocation-free variant of b200_uastc_encode_image_dev.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc).  Same arguments, same output bytes.  The encode kernel's scratch (cell results and candidate scores of the tiles in
- * flight, ~117 MiB) is a static array inside the library's device image: every GPU that loads the library holds it until the
+ * flight, ~131 MiB) is a static array inside the library's device image: every GPU that loads the library holds it until the
  * process exits.  The call makes no cudaMalloc / cudaFree / cudaMallocAsync and creates no stream (stream = NULL runs on the
  * legacy default stream and synchronises it).  Limits: pack levels 0-3 only, and at most B200_NOALLOC_MAX_BLOCKS 4x4 blocks per
  * call (an 8192 x 8192 image); beyond either, B200_E_INVALID_VALUE.  EVERY call on a device shares the one array: calls whose

@@ -578,38 +578,27 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(con
 
 // ---------------------------------------------------------------------------------------------------------
 // Job-based encode, levels 0-3 (uastc_jobs.cuh).  A CTA of EJ_T threads owns tiles of EJ_T blocks and walks each tile
-// through five stages, a CTA barrier between them:
+// through seven stages, a CTA barrier between them:
 //   load      thread = block: texels -> shared memory, block class, compacted class lists
 //   estimate  warp-jobs over (estimate slot, 32 blocks of the slot's class group): partition patterns -> shared memory
 //   cells     warp-jobs over (cell slot, 32 blocks): one colour-cell fit per lane -> 24 B per cell in the CTA's scratch
 //   score     warp-jobs over (candidate slot, 32 blocks): assemble from the cells, score -> 8 B per candidate in the scratch
-//   finish    thread = block: the reference's selection rules over the stored scores, hints, pack, store
-// In the three middle stages a warp claims its next warp-job from a shared counter, so every warp of the CTA is busy until
+//   head      thread = block: the reference's selection rules over the stored scores, the winner decoded, BC1 / EAC hints, pack
+//   etc1      warp-jobs over ((flip, colour mode), 32 blocks ordered by the cost of their search): the ETC1 hint search
+//   tail      thread = block: the hint jobs' results into the packed block, store
+// In the four job stages a warp claims its next warp-job from a shared counter, so every warp of the CTA is busy until
 // the stage's jobs run out (the block-at-a-time kernel waited at every stage barrier for the warp that held the
 // most expensive blocks), the 32 lanes of a warp-job run the SAME mode on 32 different blocks (a block-at-a-time warp that
 // holds opaque and alpha blocks runs both mode lists one after the other, each under a partial mask), and a thread holds one
-// cell or one candidate at a time instead of the block's whole candidate list.  The scratch (cells + scores, 1080 B per block
+// cell or one candidate at a time instead of the block's whole candidate list.  The scratch (cells + scores + decoded winners + ETC1 hint job results, 1208 B per block
 // of the tile) is written and read by the same CTA within one tile and reused for the next: it lives in L2.
 #ifndef EJ_THREADS
 #define EJ_THREADS 768
 #endif
-#ifndef EJ_ETC1_JOBS
-#define EJ_ETC1_JOBS 1     // ETC1 hint search as warp-jobs over (flip, colour mode) (0: inside the thread = block finish stage)
-#endif
-#ifndef EJ_SCRATCH_CG
-#define EJ_SCRATCH_CG 1    // the CTA's global scratch bypasses L1 (ld.cg / st.cg): L1 is for the jobs' local frames
-#endif
-#if EJ_SCRATCH_CG
-__device__ __forceinline__ uint2 ej_ld(const uint2* p) { return __ldcg(p); }
-__device__ __forceinline__ uint4 ej_ld(const uint4* p) { return __ldcg(p); }
-__device__ __forceinline__ uint32_t ej_ld(const uint32_t* p) { return __ldcg(p); }
-__device__ __forceinline__ void ej_st(uint2* p, uint2 v) { __stcg(p, v); }
-__device__ __forceinline__ void ej_st(uint4* p, uint4 v) { __stcg(p, v); }
-__device__ __forceinline__ void ej_st(uint32_t* p, uint32_t v) { __stcg(p, v); }
-#else
-template <class T> __device__ __forceinline__ T ej_ld(const T* p) { return *p; }
-template <class T> __device__ __forceinline__ void ej_st(T* p, T v) { *p = v; }
-#endif
+// The CTA's scratch is read and written with ld.cg / st.cg (L2 only; measured neutral against cached accesses, kept because the
+// data is streamed and L1 is what holds the jobs' local frames).
+template <class T> __device__ __forceinline__ T ej_ld(const T* p) { return __ldcg(p); }
+template <class T> __device__ __forceinline__ void ej_st(T* p, T v) { __stcg(p, v); }
 #ifndef EJ_MIN_CTAS
 #define EJ_MIN_CTAS 1
 #endif
@@ -881,7 +870,6 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
       }
       uint32_t dec[16], wmode;
       packed = ub::j_finish_head(px, flags, &win, live, solid, ENC_FINE_SYNC, dec, wmode, etc1_at);
-#if EJ_ETC1_JOBS
       uint32_t e1cls = 16;
       if (etc1_at != 0xFFFFu) {
 #pragma unroll
@@ -905,16 +893,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
           sh.list[off + rank] = (uint16_t)tid;
         }
       }
-#else
-      if (etc1_at != 0xFFFFu) {
-        const uint32_t js = ub::etc1_job_slots(cfg.level, cfg.flags), nf = js & 3u, ni = js >> 2;
-        ub::Etc1JobOut jobs[4];
-        for (uint32_t k = 0; k < nf * ni; k++) ub::etc1_hints_job(wmode, px, dec, cfg.level, cfg.flags, k / ni, k % ni, jobs[k]);
-        ub::j_finish_tail(packed, etc1_at, jobs, nf * ni);
-      }
-#endif
     }
-#if EJ_ETC1_JOBS
     __syncthreads();
 
     // ---- ETC1 hint jobs: warp-jobs over ((flip slot, colour mode), 32 non-solid blocks).  The search is the largest single item
@@ -942,11 +921,9 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
       }
     }
     __syncthreads();
-#endif
 
     // ---- finish, tail: thread = block
     if (live) {
-#if EJ_ETC1_JOBS
       if (etc1_at != 0xFFFFu) {
         ub::Etc1JobOut jobs[4];
         for (uint32_t k = 0; k < e1_nf * e1_ni; k++) {
@@ -955,7 +932,6 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
         ub::j_finish_tail(packed, etc1_at, jobs, e1_nf * e1_ni);
       }
-#endif
       *dst = make_uint4((uint32_t)packed.lo, (uint32_t)(packed.lo >> 32), (uint32_t)packed.hi, (uint32_t)(packed.hi >> 32));
     }
     __syncthreads();
@@ -1311,7 +1287,7 @@ __global__ void __launch_bounds__(256) k_mip_down(const uint32_t* __restrict__ s
 // b200_uastc_encode_image_dev launches k_encode_jobs with a stream-ordered scratch allocation per launch; callers that
 // cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the same kernel over a
 // scratch that lives in the library's own device image: a file-scope array, one copy on every GPU that loads the library,
-// held until the process exits.  Size: the tile counter + 1080 B x EJ_T blocks for each of at most B200_NOALLOC_MAX_CTAS
+// held until the process exits.  Size: the tile counter + 1208 B x EJ_T blocks for each of at most B200_NOALLOC_MAX_CTAS
 // resident tiles (one per SM of a B200).
 constexpr unsigned B200_NOALLOC_MAX_CTAS = 148 * EJ_MIN_CTAS;   // every resident CTA of a B200
 constexpr size_t B200_NOALLOC_SCRATCH_BYTES = EJ_SCRATCH_HEADER + (size_t)B200_NOALLOC_MAX_CTAS * EJ_SCRATCH_PER_CTA;   // ~131 MiB
