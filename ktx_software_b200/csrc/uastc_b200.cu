@@ -899,7 +899,10 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     // ---- ETC1 hint jobs: warp-jobs over ((flip slot, colour mode), 32 non-solid blocks).  The search is the largest single item
     // of the encoder and its cost differs 20-fold between blocks (modes with and without a bias field, the range-dependent
     // table limit): as jobs, the lanes of a warp run one (flip, colour mode) pair and no warp waits for one unlucky block.
-    const uint32_t e1_slots = ub::etc1_job_slots(cfg.level, cfg.flags), e1_nf = e1_slots & 3u, e1_ni = e1_slots >> 2;
+#ifndef EJ_ETC1_SPLIT_MODES
+#define EJ_ETC1_SPLIT_MODES 1
+#endif
+    const uint32_t e1_slots = ub::etc1_job_slots(cfg.level, cfg.flags), e1_nf = e1_slots & 3u, e1_ni = EJ_ETC1_SPLIT_MODES ? e1_slots >> 2 : 1u;
     {
       const uint32_t n_blocks = c0 + c1 + c2 + c3, per_slot = (n_blocks + 31u) >> 5, total = per_slot * e1_nf * e1_ni;
       for (;;) {
@@ -915,7 +918,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) { px[j] = sh.px[b * 17 + j]; dec[j] = ej_ld(gdec + j * EJ_T + b); }
           ub::Etc1JobOut o;
-          ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, slot % e1_ni, o, together);
+          ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, EJ_ETC1_SPLIT_MODES ? slot % e1_ni : ub::ETC1_JOB_BOTH_MODES, o, together);
           ej_st(ge1 + slot * EJ_T + b, make_uint4((uint32_t)o.err, (uint32_t)(o.err >> 32), o.hint, 0u));
         }
       }

@@ -293,6 +293,15 @@ UB_FN void etc1_hints_setup(Etc1Sub* sub, uint32_t flip, const uint32_t* px, con
 //   4  per trial, in trial order: the sum of its two evaluations against the best so far.
 // `lanes` (device): the lanes of the warp that run this call together -- they step through pass 2 together; 0 = the caller's
 // lanes are not known to be together (thread = block callers).
+// index of the lowest set bit (x != 0)
+UB_FN uint32_t ctz64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+  return (uint32_t)__ffsll((long long)x) - 1u;
+#else
+  return (uint32_t)__builtin_ctzll(x);
+#endif
+}
+
 #ifndef ETC1_CLAMP_UNROLL
 #define ETC1_CLAMP_UNROLL 4   // texels per iteration of the clamping-table scan: 1 / 2 / 4 / 8 measured 24.3 / 23.6 / 23.35 / 23.6 ms (4096^2 img_mix level 2)
 #endif
@@ -311,6 +320,7 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
                             // colour to the first's, so a slot can meet a second colour: that is a new evaluation
   uint8_t trial_ev[32][2];
   uint32_t n_ev = 0;
+  uint64_t open = 0;        // evaluations with clamping tables still to scan (bit = index in ev): the cursor of pass 2 lives in registers
 #pragma unroll 1
   for (uint32_t i = 0; i < 16; i++) { slot_ev[0][i] = 0xFF; slot_ev[1][i] = 0xFF; }
   // ---- pass 1
@@ -369,16 +379,15 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
       Etc1Eval& e = ev[n_ev];
       e.key = key; e.st = s | (limit << 4) | (n_plain << 8) | (it << 12) | (bi_s << 16); e.best = best_sub; e.picks = 0; e.pad_ = 0;
       slot_ev[s][slot] = (uint8_t)n_ev; trial_ev[bi][s] = (uint8_t)n_ev;
+      if (it < limit) open |= 1ull << n_ev;
       n_ev++;
     }
   }
   // ---- pass 2: one clamping table per step
+  uint64_t by_picks = 0;    // evaluations whose best table is a clamping one
   {
-    uint32_t cur = 0;
     for (;;) {
-#pragma unroll 1
-      while (cur < n_ev && ((ev[cur].st >> 12) & 15u) >= ((ev[cur].st >> 4) & 15u)) cur++;
-      const bool done = cur >= n_ev;
+      const bool done = open == 0;
 #ifdef __CUDA_ARCH__
       if (lanes) { if (!__any_sync(lanes, !done)) break; }
       else
@@ -387,6 +396,7 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
       if (!done) {
         // |P - T|^2 = |P|^2 - 2 P.T + |T|^2 in the weighted (2y, cr, cb) space: per entry the constant |P|^2 and three
         // coefficients, per texel three multiply-adds and a compare; sum |T|^2 is a sub-block constant (EtcEntry)
+        const uint32_t cur = ctz64(open);
         Etc1Eval& e = ev[cur];
         const uint32_t st = e.st, it = (st >> 12) & 15u, limit = (st >> 4) & 15u;
         const Etc1Sub& sb = sub[st & 1u];
@@ -411,26 +421,30 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
         ks = (ks & 0x0F0Fu) + ((ks >> 4) & 0x0F0Fu);
         ks = (ks & 0xFFu) + (ks >> 8);
         const uint64_t total = (uint64_t)(sb.dnorm + ((acc4 - (int64_t)ks) >> 2));   // acc4 - ks = 4 x the sum of the distances, exactly
-        uint32_t next = it + 1;
+        uint32_t next = it + 1, st2 = st;
         if (!flip && total >= e.best) next = limit;
-        else if (total < e.best) { e.best = total; e.picks = picks; e.st = (st & 0xFFFFu) | (it << 16); }
-        e.st = (e.st & ~0xF000u) | (next << 12);
+        else if (total < e.best) { e.best = total; e.picks = picks; st2 = (st & 0xFFFFu) | (it << 16); by_picks |= 1ull << cur; }
+        e.st = (st2 & ~0xF000u) | (next << 12);
+        if (next >= limit) open &= ~(1ull << cur);
       }
     }
   }
   // ---- pass 3: error of the chosen table against the ORIGINAL texels (selectors picked on the decoded ones; equal
-  // distances keep the lowest entry index)
+  // distances keep the lowest entry index).  Two loops, each over a lane's own evaluations of one kind, so the bodies run converged.
+  {
+    uint64_t todo = (n_ev >= 64u ? ~0ull : ((1ull << n_ev) - 1ull)) & ~by_picks;   // best table is a plain one
 #pragma unroll 1
-  for (uint32_t i = 0; i < n_ev; i++) {
-    Etc1Eval& e = ev[i];
-    const uint32_t st = e.st, bi_s = st >> 16, n_plain = (st >> 8) & 15u;
-    const Etc1Sub& sb = sub[st & 1u];
-    const Ycc2 by = to_ycc2(e.key);
-    uint64_t err_s = 0;
-    if (bi_s < n_plain) {
+    while (todo) {
+      const uint32_t i = ctz64(todo);
+      todo &= todo - 1;
+      Etc1Eval& e = ev[i];
+      const uint32_t st = e.st, bi_s = st >> 16;
+      const Etc1Sub& sb = sub[st & 1u];
+      const Ycc2 by = to_ycc2(e.key);
       const int yb = by.y2 >> 1;
       const int m0 = UBT(etc1_inten)[bi_s * 4 + 2], m1 = UBT(etc1_inten)[bi_s * 4 + 3];
       const int mid = 128 * (m0 + m1);
+      uint64_t err_s = 0;
 #pragma unroll
       for (uint32_t j = 0; j < 8; j++) {
         const int sd = sb.dy[j] - yb, d = sd < 0 ? -sd : sd;
@@ -438,11 +452,19 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
         const int m = (sd <= 0) ? ((d >= mid) ? -m1 : -m0) : ((d > mid) ? m1 : m0);
         err_s += sq64(sb.sy2[j] - (by.y2 + 512 * m));
       }
-      err_s += sb.smom.chroma_sum(by);
-    } else {
-      const int b8[3] = {(int)(e.key & 255u), (int)((e.key >> 8) & 255u), (int)((e.key >> 16) & 255u)};
-      const uint32_t picks = e.picks;
+      e.best = err_s + sb.smom.chroma_sum(by);
+    }
+    todo = by_picks;   // best table is a clamping one: the entry of every texel was recorded when it was scored
 #pragma unroll 1
+    while (todo) {
+      const uint32_t i = ctz64(todo);
+      todo &= todo - 1;
+      Etc1Eval& e = ev[i];
+      const uint32_t st = e.st, bi_s = st >> 16, picks = e.picks;
+      const Etc1Sub& sb = sub[st & 1u];
+      const int b8[3] = {(int)(e.key & 255u), (int)((e.key >> 8) & 255u), (int)((e.key >> 16) & 255u)};
+      uint64_t err_s = 0;
+#pragma unroll 2
       for (uint32_t j = 0; j < 8; j++) {
         const int m = UBT(etc1_inten)[bi_s * 4 + ((picks >> (2 * j)) & 3u)];
         const int r = clamp255(b8[0] + m), g = clamp255(b8[1] + m), b = clamp255(b8[2] + m);
@@ -450,8 +472,8 @@ UB_FN void etc1_hints_search(const Etc1Plan& pl, const Etc1Sub* sub, uint32_t fl
         const int ey = y - (sb.sy2[j] >> 1), ecr = cr - sb.scr[j], ecb = cb - sb.scb[j];
         err_s += (uint64_t)(4 * (int64_t)ey * ey + (int64_t)ecr * ecr + (int64_t)ecb * ecb);
       }
+      e.best = err_s;
     }
-    e.best = err_s;
   }
   // ---- pass 4
 #pragma unroll 1
@@ -494,6 +516,7 @@ UB_BIG void compute_etc1_hints(uint32_t mode, const uint32_t* px, const uint32_t
 // The same search as independent jobs (uastc_jobs.cuh): job (fslot, individ) of a block returns the best trial of ITS
 // (flip, colour mode) pair; etc1_hints_combine over the jobs in (fslot, individ) order with a strict compare picks what the
 // loop above picks.  fslot counts from the block's first flip.  A job outside the block's range returns err = ~0.
+const uint32_t ETC1_JOB_BOTH_MODES = 0xFFu;   // `individ` of a job that runs the colour modes one after the other (shares the sub-block set-up)
 struct Etc1JobOut { uint64_t err; uint32_t hint; uint32_t pad_; };   // hint = flip | diff << 1 | inten0 << 2 | inten1 << 5 | bias << 8
 UB_FN uint32_t etc1_job_slots(uint32_t level, uint32_t flags) {   // bit 0..1: flip slots, bit 2..3: colour modes (uniform over a launch)
   const Etc1Plan pl = etc1_plan(0, level, flags);
@@ -554,7 +577,7 @@ UB_BIG void etc1_hints_job(uint32_t mode, const uint32_t* px, const uint32_t* de
   etc1_hints_range(pl, flags, dec, first_flip, last_flip);
   o.err = ~0ull; o.hint = 0; o.pad_ = 0;
   const uint32_t flip = first_flip + fslot;
-  const bool none = flip >= last_flip || individ >= pl.last_individ;
+  const bool none = flip >= last_flip || (individ != ETC1_JOB_BOTH_MODES && individ >= pl.last_individ);
 #ifdef __CUDA_ARCH__
   if (lanes) lanes = __ballot_sync(lanes, !none);
 #endif
@@ -563,7 +586,10 @@ UB_BIG void etc1_hints_job(uint32_t mode, const uint32_t* px, const uint32_t* de
   etc1_hints_setup(sub, flip, px, dec);
   uint32_t f = 0, d = 0, i0 = 0, i1 = 0, bias = 0;
   uint64_t best = ~0ull;
-  etc1_hints_search(pl, sub, flip, individ, level, best, f, d, i0, i1, bias, lanes);
+  if (individ == ETC1_JOB_BOTH_MODES) {
+#pragma unroll 1
+    for (uint32_t i = 0; i < pl.last_individ; i++) etc1_hints_search(pl, sub, flip, i, level, best, f, d, i0, i1, bias, lanes);
+  } else etc1_hints_search(pl, sub, flip, individ, level, best, f, d, i0, i1, bias, lanes);
   o.err = best;
   o.hint = f | (d << 1) | (i0 << 2) | (i1 << 5) | (bias << 8);
 }
