@@ -599,6 +599,12 @@ __global__ void __launch_bounds__(ENC_THREADS, ENC_MIN_CTAS) k_encode_blocks(con
 // data is streamed and L1 is what holds the jobs' local frames).
 template <class T> __device__ __forceinline__ T ej_ld(const T* p) { return __ldcg(p); }
 template <class T> __device__ __forceinline__ void ej_st(T* p, T v) { __stcg(p, v); }
+#ifndef EJ_PX_SHARED
+#define EJ_PX_SHARED 1   // jobs read the block's texels in place; copying them into the local frame first measured 3-4 % slower
+#endif
+#ifndef EJ_PARTS_SHARED
+#define EJ_PARTS_SHARED 1   // ... and the pattern list, and the block-head stage its texels: another 1 %
+#endif
 #ifndef EJ_MIN_CTAS
 #define EJ_MIN_CTAS 1
 #endif
@@ -756,9 +762,13 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         const uint32_t g = ub::UBT(j_est)[e] >> 22, r = r0 + lane;
         if (r < g_count[g]) {
           const uint32_t b = sh.list[g_start[g] + r];
+#if EJ_PX_SHARED
+          const uint32_t* px = sh.px + b * 17;   // read in place (generic loads from shared memory): no copy into the local frame
+#else
           uint32_t px[16];
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+#endif
           ub::j_run_estimate(e, px, sh.parts + b * ub::J_PARTS);
         }
       }
@@ -781,12 +791,20 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         const uint32_t g = ub::jc_group(ub::UBT(j_cand)[ub::UBT(j_cell)[gc] & 31u]), r = r0 + lane;
         if (r < g_count[g]) {
           const uint32_t b = sh.list[g_start[g] + r];
+#if EJ_PX_SHARED
+          const uint32_t* px = sh.px + b * 17;   // read in place (generic loads from shared memory): no copy into the local frame
+#else
           uint32_t px[16];
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+#endif
+#if EJ_PARTS_SHARED
+          const uint8_t* parts = sh.parts + b * ub::J_PARTS;
+#else
           alignas(4) uint8_t parts[ub::J_PARTS];
 #pragma unroll
           for (uint32_t j = 0; j < ub::J_PARTS / 4; j++) ((uint32_t*)parts)[j] = ((const uint32_t*)(sh.parts + b * ub::J_PARTS))[j];
+#endif
           ub::CellOut o;
           ub::j_run_cell(gc, px, parts, cfg, o);
           uint2* q = cells + (size_t)ub::j_cell_local(gc) * 3 * EJ_T + b;
@@ -812,12 +830,20 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         const uint32_t d = ub::UBT(j_cand)[gs], g = ub::jc_group(d), r = r0 + lane;
         if (r < g_count[g]) {
           const uint32_t b = sh.list[g_start[g] + r];
+#if EJ_PX_SHARED
+          const uint32_t* px = sh.px + b * 17;   // read in place (generic loads from shared memory): no copy into the local frame
+#else
           uint32_t px[16];
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[b * 17 + j];
+#endif
+#if EJ_PARTS_SHARED
+          const uint8_t* parts = sh.parts + b * ub::J_PARTS;
+#else
           alignas(4) uint8_t parts[ub::J_PARTS];
 #pragma unroll
           for (uint32_t j = 0; j < ub::J_PARTS / 4; j++) ((uint32_t*)parts)[j] = ((const uint32_t*)(sh.parts + b * ub::J_PARTS))[j];
+#endif
           ub::CellOut co[3];
           const uint32_t nc = ub::jc_cells(d);
           for (uint32_t s = 0; s < nc; s++) {
@@ -843,9 +869,13 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     {
       const bool solid = cls == ub::J_CLS_SOLID;
       ub::Candidate win;
+#if EJ_PARTS_SHARED
+      const uint32_t* px = sh.px + tid * 17;
+#else
       uint32_t px[16];
 #pragma unroll
       for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[tid * 17 + j];
+#endif
       if (live && !solid) {
         const uint32_t mine = ub::j_block_cands(cls, en_cands);
         uint32_t overall[ub::J_MAX_CAND_SLOTS], n = 0;
@@ -914,9 +944,16 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         const uint32_t together = __ballot_sync(0xFFFFFFFFu, r < n_blocks);
         if (r < n_blocks) {
           const uint32_t b = sh.list[r];
+#if EJ_PX_SHARED
+          const uint32_t* px = sh.px + b * 17;
+          uint32_t dec[16];
+#pragma unroll
+          for (uint32_t j = 0; j < 16; j++) dec[j] = ej_ld(gdec + j * EJ_T + b);
+#else
           uint32_t px[16], dec[16];
 #pragma unroll
           for (uint32_t j = 0; j < 16; j++) { px[j] = sh.px[b * 17 + j]; dec[j] = ej_ld(gdec + j * EJ_T + b); }
+#endif
           ub::Etc1JobOut o;
           ub::etc1_hints_job(sh.parts[b * ub::J_PARTS], px, dec, cfg.level, cfg.flags, slot / e1_ni, EJ_ETC1_SPLIT_MODES ? slot % e1_ni : ub::ETC1_JOB_BOTH_MODES, o, together);
           ej_st(ge1 + slot * EJ_T + b, make_uint4((uint32_t)o.err, (uint32_t)(o.err >> 32), o.hint, 0u));
