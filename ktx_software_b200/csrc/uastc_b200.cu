@@ -651,6 +651,19 @@ struct EjStage {
   }
 };
 
+// Stage barriers of k_encode_jobs.  A build with -DEJ_STAGE_CLOCKS=1 (development only) adds up, per barrier, the cycles lane 0 of
+// every warp spent before arriving and until released: busy / (warps x wall) is what the stage's tail costs (tools/stage_clocks.py).
+#ifndef EJ_STAGE_CLOCKS
+#define EJ_STAGE_CLOCKS 0
+#endif
+#if EJ_STAGE_CLOCKS
+__device__ unsigned long long g_ej_clk[2][10];
+#define EJ_SYNC(k) do { const long long t_a_ = clock64(); __syncthreads(); const long long t_b_ = clock64(); \
+    if (lane == 0) { ej_busy[k] += (unsigned long long)(t_a_ - ej_t0); ej_wall[k] += (unsigned long long)(t_b_ - ej_t0); } ej_t0 = t_b_; } while (0)
+#else
+#define EJ_SYNC(k) __syncthreads()
+#endif
+
 template <bool PACKED>
 __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const __grid_constant__ EncDescPack pack, const EncImageDesc* __restrict__ d_descs,
                                                                          uint32_t n_images, uint64_t total_blocks, uint32_t flags,
@@ -675,6 +688,10 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
   for (uint32_t e = 0; e < ub::J_NUM_EST; e++) if ((cfg.mode_mask >> (ub::UBT(j_est)[e] & 31u)) & 1u) en_est |= 1u << e;
 
   const uint64_t n_tiles = (total_blocks + EJ_T - 1) / EJ_T;
+#if EJ_STAGE_CLOCKS
+  unsigned long long ej_busy[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, ej_wall[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  long long ej_t0 = clock64();
+#endif
   for (;;) {
     // tiles are claimed from a global counter: tile costs differ several-fold (solid / opaque / alpha content), a fixed share
     // per CTA leaves SMs idle behind the CTA that drew the expensive tiles
@@ -682,8 +699,11 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     if (tid < 4) sh.cnt[tid] = 0;
     if (tid < 4) sh.next[tid] = 0;
     if (tid < 16) sh.e1cnt[tid] = 0;
-    __syncthreads();
+    EJ_SYNC(0);
     const uint64_t tile = sh.tile;
+#if EJ_STAGE_CLOCKS
+    if (tile >= n_tiles) { if (lane == 0) for (int k = 0; k < 10; k++) { atomicAdd(&g_ej_clk[0][k], ej_busy[k]); atomicAdd(&g_ej_clk[1][k], ej_wall[k]); } }
+#endif
     if (tile >= n_tiles) break;   // uniform per CTA
     const uint64_t base = tile * EJ_T;
     // ---- load: thread = block
@@ -740,13 +760,13 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
       b0 = __shfl_sync(0xFFFFFFFFu, b0, leader);
       my_rank = b0 + __popc(peers & ((1u << lane) - 1u));
     }
-    __syncthreads();
+    EJ_SYNC(1);
     const uint32_t c0 = sh.cnt[0], c1 = sh.cnt[1], c2 = sh.cnt[2], c3 = sh.cnt[3];
     if (ci < 4u) sh.list[(ci == 0 ? 0u : ci == 1 ? c0 : ci == 2 ? c0 + c1 : c0 + c1 + c2) + my_rank] = (uint16_t)tid;
     // group -> range of the list: LA = [c0, c0 + c1 + c2), opaque = [0, c0 + c1), alpha = [c0 + c1, all)
     const uint32_t g_start[3] = {c0, 0u, c0 + c1}, g_count[3] = {c1 + c2, c0 + c1, c2 + c3};
     auto warps_of = [&](uint32_t g) { return (g_count[g] + 31u) >> 5; };
-    __syncthreads();
+    EJ_SYNC(2);
 
     // ---- estimate jobs
     {
@@ -773,7 +793,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
       }
     }
-    __syncthreads();
+    EJ_SYNC(3);
 
     // ---- cell jobs
     {
@@ -814,7 +834,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
       }
     }
-    __syncthreads();   // (global scratch written above is read below by other threads of this CTA: the barrier orders it)
+    EJ_SYNC(4);   // (global scratch written above is read below by other threads of this CTA: the barrier orders it)
 
     // ---- candidate jobs: assemble + score
     {
@@ -861,7 +881,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
       }
     }
-    __syncthreads();
+    EJ_SYNC(5);
 
     // ---- finish, head: thread = block.  Selection, the winner decoded, BC1 / EAC hints, the block packed but for its ETC1 hints
     ub::Bits128 packed;
@@ -916,7 +936,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         if (lane == leader && e1cls < 16u) b0 = atomicAdd(&sh.e1cnt[e1cls], __popc(peers));
         b0 = __shfl_sync(0xFFFFFFFFu, b0, leader);
         const uint32_t rank = b0 + __popc(peers & ((1u << lane) - 1u));
-        __syncthreads();
+        EJ_SYNC(6);
         if (e1cls < 16u) {
           uint32_t off = 0;
           for (uint32_t k = 0; k < e1cls; k++) off += sh.e1cnt[k];
@@ -924,7 +944,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
       }
     }
-    __syncthreads();
+    EJ_SYNC(7);
 
     // ---- ETC1 hint jobs: warp-jobs over ((flip slot, colour mode), 32 non-solid blocks).  The search is the largest single item
     // of the encoder and its cost differs 20-fold between blocks (modes with and without a bias field, the range-dependent
@@ -960,7 +980,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
         }
       }
     }
-    __syncthreads();
+    EJ_SYNC(8);
 
     // ---- finish, tail: thread = block
     if (live) {
@@ -974,7 +994,7 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
       }
       *dst = make_uint4((uint32_t)packed.lo, (uint32_t)(packed.lo >> 32), (uint32_t)packed.hi, (uint32_t)(packed.hi >> 32));
     }
-    __syncthreads();
+    EJ_SYNC(9);
   }
 }
 
@@ -1380,3 +1400,11 @@ extern "C" int b200_uastc_encode_image_dev_noalloc(const void* d_rgba, uint32_t 
   if (!stream) CU(cudaStreamSynchronize(st));
   return B200_OK;
 }
+
+#if EJ_STAGE_CLOCKS
+extern "C" int b200_uastc_debug_stage_clocks(unsigned long long* out20, int reset) {
+  if (cudaMemcpyFromSymbol(out20, g_ej_clk, sizeof(unsigned long long) * 20) != cudaSuccess) return -1;
+  if (reset) { unsigned long long z[20] = {0}; if (cudaMemcpyToSymbol(g_ej_clk, z, sizeof z) != cudaSuccess) return -1; }
+  return 0;
+}
+#endif
