@@ -487,7 +487,7 @@ def bench_c2(cx, args):
         ok_b = bool((R.ref_transcode(got, 0)[0] == d_bc7[tsel].cpu().numpy()).all())
         ok_a = bool((R.ref_transcode(got, 1)[0] == d_astc[tsel].cpu().numpy()).all())
         parity = {"encode_bit_exact": ok_e, "bc7_bit_exact": ok_b, "astc_bit_exact": ok_a, "blocks_checked": int(len(sel)),
-                  "full_size_sweep": "profiles/r4_parity_sweep.json (all 5592407 blocks of this config, 0 mismatches)"}
+                  "full_size_sweep": "profiles/r7_parity_sweep.json (all 5592407 blocks of this config, 0 mismatches)"}
         cpu = {"value": r["mpix_s"], "unit": "Mpix/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"],
                "encode_only_mpix_s": r["encode_mpix_s"], "transcode_gbs": r["transcode_gbs"]}
     enc_key = "k_encode_jobs@c2"
@@ -577,7 +577,7 @@ def bench_c3(cx, args):
     sel = (rows[:, None] * 1024 + np.arange(1024)[None, :]).reshape(-1)
     l3 = bench_single_image(cx, args, C3_NAME + " -- level 3, no RDO", img, 3, "k_encode_jobs@c3_l3",
                             ref_px=(blocks_of_rows(img, rows), sel), ref_desc="block rows r = 0 mod 8 (131072 blocks)")
-    l3["parity_vs_reference"]["full_size_sweep"] = "profiles/r4_parity_sweep.json (all 1048576 blocks, 0 mismatches)"
+    l3["parity_vs_reference"]["full_size_sweep"] = "profiles/r7_parity_sweep.json (all 1048576 blocks, 0 mismatches)"
     # level 4 + RDO through the host API (the RDO post-pass has no device-pointer image entry): flags 4 | 512 as libktx sets them
     flags = 4 | 512
     n = n_blocks_of(img)
@@ -626,7 +626,7 @@ def bench_c3(cx, args):
         rdo["parity_vs_reference"] = {"sample": "rows/cols 1536..2559 of the image as a 1024x1024 image of its own (65536 blocks)", "bit_exact": bool((ours[0] == ref).all()),
                                       "psnr_ours_db": pa, "psnr_reference_db": pb, "psnr_delta_db": abs(pa - pb), "within_0.01_db": bool(abs(pa - pb) <= 0.01),
                                       "mode_agreement": float((R.block_modes(ours[0]) == R.block_modes(ref)).mean()),
-                                      "full_size_sweep": "profiles/r4_parity_sweep.json (all 1048576 blocks of this config bit-exact; PSNR, mode agreement, zstd-19 sizes there)"}
+                                      "full_size_sweep": "profiles/r7_parity_sweep.json (all 1048576 blocks of this config bit-exact; PSNR, mode agreement, zstd-19 sizes there)"}
         rdo["cpu_baseline"] = {"value": 16 * len(px) / (t2 - t0) / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "reference",
                                "sample": "the same 1024x1024 crop: reference encode_uastc level 4 over %d threads (%.1f s) + uastc_rdo on 4 job threads (%.1f s)" % (cores, t1 - t0, t2 - t1)}
     return l3, rdo
@@ -711,7 +711,7 @@ def bench_c5(cx, args, with_cpu_targets=False):
     if R.have_ref():
         sub = slice(0, 1 << 18)
         parity = {"bc7_bit_exact": bool((R.ref_transcode(d_src[sub].cpu().numpy(), 0)[0] == d_dst[sub].cpu().numpy()).all()), "blocks_checked": 1 << 18,
-                  "full_size_sweep": "profiles/r4_parity_sweep.json (2^26 blocks to BC7 and to ASTC, 0 mismatches)"}
+                  "full_size_sweep": "profiles/r7_parity_sweep.json (2^26 blocks to BC7 and to ASTC, 0 mismatches)"}
     ref_head = d_dst[:1 << 14].cpu().numpy().copy()
 
     # e2e: same metric through the C-ABI host call, pinned host buffers, H2D + D2H inside the timed region
