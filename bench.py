@@ -680,6 +680,34 @@ def bench_c4(cx, args, n_images=384):
                                           "sample": "face 0 and face %d (same content) against the reference" % (n_images - n_distinct)}
             rec["cpu_baseline"] = {"value": 16 * nb / dtr / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "reference",
                                    "sample": "face 0 of 384 (262144 blocks): reference encode_uastc level 2 over %d threads (nproc = %d); faces are independent" % (cores, cores)}
+        # ---- supercompression of finished faces under the encode of later ones (b200_uastc_encode_stream).  One device,
+        # 48 faces, Zstd level 1 through pyarrow on the calling thread: serial = encode, then compress every face; streamed = compress
+        # face i inside its completion callback while faces i+1.. are on the GPU.
+        try:
+            import pyarrow as pa
+            codec = pa.Codec("zstd", compression_level=1)
+            n_z = min(48, n_images)
+            p1 = K.api.make_params(LEVEL)
+            sizes = [0] * n_z
+
+            def compress(i):
+                sizes[i] = len(codec.compress(memoryview(out[i * nb:(i + 1) * nb].reshape(-1)), asbytes=True))
+
+            t0 = time.perf_counter()
+            K.api._check(K.lib().b200_uastc_encode(arr, n_z, ctypes.byref(p1), optr, ctypes.byref(aa)))
+            t1 = time.perf_counter()
+            for i in range(n_z):
+                compress(i)
+            t2 = time.perf_counter()
+            serial_sizes = list(sizes)
+            cb = K.api.IMAGE_DONE_FN(lambda i, _u: compress(int(i)))
+            K.api._check(K.lib().b200_uastc_encode_stream(arr, n_z, None, ctypes.byref(p1), optr, ctypes.byref(aa), cb, None))
+            t3 = time.perf_counter()
+            rec["zstd_under_encode"] = {"faces": n_z, "codec": "zstd level 1 (pyarrow), one host thread", "encode_ms": (t1 - t0) * 1e3, "zstd_ms": (t2 - t1) * 1e3,
+                                        "serial_ms": (t2 - t0) * 1e3, "streamed_ms": (t3 - t2) * 1e3, "same_compressed_sizes": serial_sizes == sizes,
+                                        "api": "b200_uastc_encode_stream: a completion callback per face"}
+        except ImportError:
+            pass
         cx.torch.cuda.cudart().cudaHostUnregister(out.ctypes.data)
     cx.cpu_barrier()
     return rec
@@ -849,7 +877,7 @@ def main():
             line = {"metric": rec["metric"], "value": rec["value"], "unit": rec["unit"], "n_gpus": cx.world, "steps": rec.get("steps", args.steps), "warmup": 3,
                     "ms_per_step": rec.get("ms_per_step", rec.get("kernel_ms")), "higher_is_better": True, "scaling": rec.get("scaling", "weak"), "vs_baseline": None,
                     "dtype": "u8", "data": "synthetic", "config": {"workload": rec["workload"], "build": cx.build, "parity_vs_reference": rec.get("parity_vs_reference")}}
-            for k in ("e2e", "gpu_launches", "roofline", "cpu_baseline", "clocks", "level4_rdo", "gpus_active", "device_mask", "note"):
+            for k in ("e2e", "gpu_launches", "roofline", "cpu_baseline", "clocks", "level4_rdo", "gpus_active", "device_mask", "note", "zstd_under_encode"):
                 if k in rec:
                     line[k] = rec[k]
     if cx.rank == 0 and line is not None:

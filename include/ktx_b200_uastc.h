@@ -182,6 +182,21 @@ typedef struct b200_src_format {
 int b200_uastc_encode_ex(const b200_image* images, uint32_t n_images, const b200_src_format* format,
                          const b200_uastc_params* params, uint8_t* const* out_blocks, uint32_t* out_any_alpha);
 
+/* b200_uastc_encode_ex with a call per finished image: lets the host start the Zstd / ZLIB supercompression of a
+ * level (ktxTexture2_DeflateZstd, lib/src/texture2.c; `ktx create --zstd`, tools/ktx/command_create.cpp:2077-2090) while later
+ * levels are still being encoded.  on_done(i, user) is called once per image, after ALL bytes of out_blocks[i] are in host
+ * memory and before the call returns.  Without RDO it runs between batch submissions on the calling thread, with up to two later
+ * batches in flight on the GPU -- time spent inside it is hidden as long as the GPU has queued work; images of one device finish in
+ * submission order.  When a device mask names several GPUs the call comes from whichever device's worker thread retires the
+ * image's last slab: on_done must then be thread-safe.  With rdo_enable the calls come after the device's walk, in image order.
+ * on_done must not call back into this library with the same lane-hungry entry points recursively (it may call any entry point
+ * from another thread).  on_done = NULL: exactly b200_uastc_encode_ex.  No counterpart in the reference (its compress and
+ * deflate steps are separate, serial API calls). */
+typedef void (*b200_image_done_fn)(uint32_t image_index, void* user);
+int b200_uastc_encode_stream(const b200_image* images, uint32_t n_images, const b200_src_format* format,
+                             const b200_uastc_params* params, uint8_t* const* out_blocks, uint32_t* out_any_alpha,
+                             b200_image_done_fn on_done, void* user);
+
 /* Device-resident pipeline: only the BASE level crosses PCIe.  Levels 1 .. n_levels-1 (level l is
  * max(1, w >> l) x max(1, h >> l)) are filtered from the level above on the device with the 2x2 box filter, per channel
  * (a + b + c + d + 2) >> 2 with source coordinates clamped to the level, then every level is encoded.  This is the integer box

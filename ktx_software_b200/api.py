@@ -23,7 +23,7 @@ EXPORTED_SYMBOLS = ["b200_uastc_init", "b200_uastc_shutdown", "b200_uastc_last_e
                     "b200_uastc_encode_image_dev", "b200_uastc_rdo_blocks_dev", "b200_uastc_encode_images_dev",
                     "b200_uastc_decode", "b200_uastc_decode_image_dev", "b200_uastc_transcode_ex", "b200_uastc_transcode_dev_ex", "b200_uastc_encode_ex",
                     "b200_uastc_set_devices", "b200_uastc_device_count", "b200_uastc_build_id", "b200_uastc_encode_mipchain",
-                    "b200_uastc_encode_image_dev_noalloc"]
+                    "b200_uastc_encode_image_dev_noalloc", "b200_uastc_encode_stream"]
 
 _u8p = ctypes.POINTER(ctypes.c_uint8)
 
@@ -90,6 +90,8 @@ def lib():
                                         ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
         l.b200_uastc_encode_ex.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(SrcFormat), ctypes.POINTER(UastcParams),
                                            ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32)]
+        l.b200_uastc_encode_stream.argtypes = [ctypes.POINTER(Image), ctypes.c_uint32, ctypes.POINTER(SrcFormat), ctypes.POINTER(UastcParams),
+                                               ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint32), IMAGE_DONE_FN, ctypes.c_void_p]
         l.b200_uastc_encode_blocks_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_void_p]
         l.b200_uastc_encode_image_dev.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p,
                                                   ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
@@ -260,6 +262,40 @@ def encode_images(images, pack_flags, **rdo):
     p = make_params(pack_flags, **rdo)
     any_alpha = ctypes.c_uint32(0)
     _check(lib().b200_uastc_encode(arr, len(imgs), ctypes.byref(p), optr, ctypes.byref(any_alpha)))
+    return outs, bool(any_alpha.value)
+
+
+IMAGE_DONE_FN = ctypes.CFUNCTYPE(None, ctypes.c_uint32, ctypes.c_void_p)
+
+
+def encode_images_stream(images, pack_flags, on_done, **rdo):
+    """b200_uastc_encode_stream: as encode_images, and on_done(i, blocks_of_image_i) is called as soon as image i is complete
+    in host memory (while later images are still on the GPU).  Returns (outs, any_alpha)."""
+    imgs = [np.ascontiguousarray(im, dtype=np.uint8) for im in images]
+    arr = (Image * max(1, len(imgs)))()
+    outs = []
+    optr = (ctypes.c_void_p * max(1, len(imgs)))()
+    for i, im in enumerate(imgs):
+        h, w = im.shape[:2]
+        assert im.shape[2] == 4
+        arr[i] = Image(im.ctypes.data, w, h, 0)
+        o = np.zeros((((w + 3) // 4) * ((h + 3) // 4), 16), np.uint8)
+        outs.append(o)
+        optr[i] = o.ctypes.data
+    p = make_params(pack_flags, **rdo)
+    any_alpha = ctypes.c_uint32(0)
+    errs = []
+
+    def _cb(i, _user):
+        try:
+            on_done(int(i), outs[int(i)])
+        except BaseException as e:   # noqa: BLE001 -- must not unwind through the C frames
+            errs.append(e)
+
+    cb = IMAGE_DONE_FN(_cb)
+    _check(lib().b200_uastc_encode_stream(arr, len(imgs), None, ctypes.byref(p), optr, ctypes.byref(any_alpha), cb, None))
+    if errs:
+        raise errs[0]
     return outs, bool(any_alpha.value)
 
 

@@ -167,3 +167,45 @@ def test_mipchain_from_base_level(K):
         assert alpha == alpha2
         for l in range(n):
             assert (outs[l] == want[l]).all(), (w, h, l)
+
+
+def test_stream_callbacks_see_finished_images(K):
+    """b200_uastc_encode_stream: one call per image, in submission order on one device, each made when the image's
+    bytes are final (a copy taken inside the callback equals the result of the plain call); also with RDO (calls at the end) and
+    over the device mask (any order, every image once)."""
+    base = R.img_mix(2048, 2048, 13)
+    chain = [base]
+    while chain[-1].shape[0] > 4:
+        a = chain[-1].astype(np.uint16)
+        chain.append(((a[0::2, 0::2] + a[1::2, 0::2] + a[0::2, 1::2] + a[1::2, 1::2] + 2) >> 2).astype(np.uint8))
+    imgs = chain + [R.img_noise(64, 48, 3), R.img_smooth(1024, 512, 4)]
+    want, alpha = K.encode_images(imgs, 2)
+    seen, order = {}, []
+
+    def on_done(i, blocks):
+        order.append(i)
+        seen[i] = blocks.copy()
+
+    got, alpha2 = K.encode_images_stream(imgs, 2, on_done)
+    assert alpha == alpha2
+    assert order == list(range(len(imgs)))
+    for i in range(len(imgs)):
+        assert (seen[i] == want[i]).all(), i
+        assert (got[i] == want[i]).all(), i
+    # RDO: callbacks after the walk
+    small = imgs[4:]
+    want_r, _ = K.encode_images(small, 1 | 512, rdo=True, rdo_lambda=2.0, total_jobs=4)
+    seen.clear(); order.clear()
+    K.encode_images_stream(small, 1 | 512, on_done, rdo=True, rdo_lambda=2.0, total_jobs=4)
+    assert sorted(order) == list(range(len(small)))
+    assert all((seen[i] == want_r[i]).all() for i in range(len(small)))
+    # several devices: every image exactly once
+    mask, _ = _mask(K, 8)
+    seen.clear(); order.clear()
+    K.encode_images_stream(imgs, 2, on_done, device_mask=mask)
+    assert sorted(order) == list(range(len(imgs)))
+    assert all((seen[i] == want[i]).all() for i in range(len(imgs)))
+    # an exception in the callback surfaces after the call, the library stays usable
+    with pytest.raises(ZeroDivisionError):
+        K.encode_images_stream(imgs[:3], 1, lambda i, b: 1 / 0)
+    assert (K.encode_images(imgs[5:6], 2)[0][0] == want[5]).all()
