@@ -609,7 +609,10 @@ template <class T> __device__ __forceinline__ void ej_st(T* p, T v) { __stcg(p, 
 #define EJ_MIN_CTAS 1
 #endif
 constexpr int EJ_T = EJ_THREADS;
-constexpr size_t EJ_SCRATCH_PER_CTA = (size_t)EJ_T * (ub::J_MAX_CELL_SLOTS * 24 + ub::J_MAX_CAND_SLOTS * 8 + 64 + 4 * 16);   // cells, scores, decoded winner, ETC1 hint jobs
+__host__ __device__ constexpr size_t ej_scratch_per_cta(bool full) {   // cells, scores, decoded winner, ETC1 hint jobs
+  return (size_t)EJ_T * ((full ? ub::J4_NUM_CELL : ub::J_MAX_CELL_SLOTS) * 24 + (full ? ub::J4_NUM_CAND : ub::J_MAX_CAND_SLOTS) * 8 + 64 + 4 * 16);
+}
+constexpr size_t EJ_SCRATCH_PER_CTA = ej_scratch_per_cta(false);
 struct EjShared {
   uint32_t px[EJ_T * 17];        // texel j of tile block b at [b * 17 + j]: conflict-free whether a warp reads one block or 32
   uint8_t parts[EJ_T * ub::J_PARTS];
@@ -664,7 +667,8 @@ __device__ unsigned long long g_ej_clk[2][10];
 #define EJ_SYNC(k) __syncthreads()
 #endif
 
-template <bool PACKED>
+// FULL = level 4 (no partition estimates: the j4_* slot enumeration of uastc_jobs.cuh, 343 cell and 170 candidate slots per block).
+template <bool PACKED, bool FULL = false>
 __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const __grid_constant__ EncDescPack pack, const EncImageDesc* __restrict__ d_descs,
                                                                          uint32_t n_images, uint64_t total_blocks, uint32_t flags,
                                                                          unsigned int* __restrict__ any_alpha, uint2* scratch_all) {
@@ -673,9 +677,11 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
   const EncImageDesc* descs = PACKED ? pack.d : d_descs;
   const uint32_t tid = threadIdx.x, lane = tid & 31u;
   unsigned long long* tile_counter = (unsigned long long*)scratch_all;          // zeroed by the host before the launch
-  uint2* cells = scratch_all + EJ_SCRATCH_HEADER / 8 + (size_t)blockIdx.x * (EJ_SCRATCH_PER_CTA / 8);   // [cell slot][3][EJ_T]
-  uint2* scores = cells + (size_t)ub::J_MAX_CELL_SLOTS * 3 * EJ_T;                // [candidate slot][EJ_T]
-  uint32_t* gdec = (uint32_t*)(scores + (size_t)ub::J_MAX_CAND_SLOTS * EJ_T);     // [texel][EJ_T]: every block's winner, decoded
+  constexpr size_t EJ_SCRATCH_BYTES = ej_scratch_per_cta(FULL);
+  constexpr uint32_t CELL_SLOTS = FULL ? ub::J4_NUM_CELL : ub::J_MAX_CELL_SLOTS, CAND_SLOTS = FULL ? ub::J4_NUM_CAND : ub::J_MAX_CAND_SLOTS;
+  uint2* cells = scratch_all + EJ_SCRATCH_HEADER / 8 + (size_t)blockIdx.x * (EJ_SCRATCH_BYTES / 8);   // [cell slot][3][EJ_T]
+  uint2* scores = cells + (size_t)CELL_SLOTS * 3 * EJ_T;                          // [candidate slot][EJ_T]
+  uint32_t* gdec = (uint32_t*)(scores + (size_t)CAND_SLOTS * EJ_T);               // [texel][EJ_T]: every block's winner, decoded
   uint4* ge1 = (uint4*)(gdec + 16 * EJ_T);                                        // [ETC1 hint job slot][EJ_T]: {err lo, err hi, hint, -}
   // (cells / scores / gdec / ge1 live in global memory, i.e. in L2, not in shared memory: every KB of shared memory comes out of
   //  the L1 that holds the jobs' local frames; with gdec and ge1 in shared memory the kernel ran 19 % slower)
@@ -764,12 +770,13 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     const uint32_t c0 = sh.cnt[0], c1 = sh.cnt[1], c2 = sh.cnt[2], c3 = sh.cnt[3];
     if (ci < 4u) sh.list[(ci == 0 ? 0u : ci == 1 ? c0 : ci == 2 ? c0 + c1 : c0 + c1 + c2) + my_rank] = (uint16_t)tid;
     // group -> range of the list: LA = [c0, c0 + c1 + c2), opaque = [0, c0 + c1), alpha = [c0 + c1, all)
-    const uint32_t g_start[3] = {c0, 0u, c0 + c1}, g_count[3] = {c1 + c2, c0 + c1, c2 + c3};
+    // (level 4 tries the alpha modes on every live block: its "alpha" group is the whole list)
+    const uint32_t g_start[3] = {c0, 0u, FULL ? 0u : c0 + c1}, g_count[3] = {c1 + c2, c0 + c1, FULL ? c0 + c1 + c2 + c3 : c2 + c3};
     auto warps_of = [&](uint32_t g) { return (g_count[g] + 31u) >> 5; };
     EJ_SYNC(2);
 
     // ---- estimate jobs
-    {
+    if (!FULL) {
       EjStage stg;
       stg.build(lane, (lane < ub::J_NUM_EST && ((en_est >> lane) & 1u)) ? warps_of(ub::UBT(j_est)[lane] >> 22) : 0u, 0u);
       for (;;) {
@@ -796,7 +803,30 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     EJ_SYNC(3);
 
     // ---- cell jobs
-    {
+    if (FULL) {
+      // warp-job = (mode entry, candidate, cell, 32 blocks of the entry's group): lane e < 18 holds entry e's job count
+      EjStage stg;
+      stg.build(lane, lane < ub::J4_NUM_MODES ? ub::j4_count(lane) * ub::j4_cells(lane) * warps_of(ub::j4_group(lane)) : 0u, 0u);
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[1], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= stg.total) break;
+        uint32_t e, r0;
+        stg.decode(w, e, r0);
+        const uint32_t g = ub::j4_group(e), chunks = warps_of(g), local = r0 >> 5, slot = local / chunks, r = (local - slot * chunks) * 32 + lane;
+        const uint32_t k = slot / ub::j4_cells(e), cell = slot - k * ub::j4_cells(e);
+        if (r < g_count[g]) {
+          const uint32_t b = sh.list[g_start[g] + r];
+          ub::CellOut o;
+          ub::j4_run_cell(e, k, cell, sh.px + b * 17, cfg, o);
+          uint2* q = cells + (size_t)(ub::UBT(j4_cell_base)[e] + slot) * 3 * EJ_T + b;
+          ej_st(q, make_uint2(o.astc_lo, o.astc_hi));
+          ej_st(q + EJ_T, ((const uint2*)o.sel)[0]);
+          ej_st(q + 2 * EJ_T, ((const uint2*)o.sel)[1]);
+        }
+      }
+    } else {
       EjStage stg;
       const uint32_t s_hi = lane + 32u;
       stg.build(lane, ((en_cells >> lane) & 1ull) ? warps_of(ub::jc_group(ub::UBT(j_cand)[ub::UBT(j_cell)[lane] & 31u])) : 0u,
@@ -837,7 +867,36 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
     EJ_SYNC(4);   // (global scratch written above is read below by other threads of this CTA: the barrier orders it)
 
     // ---- candidate jobs: assemble + score
-    {
+    if (FULL) {
+      EjStage stg;
+      stg.build(lane, lane < ub::J4_NUM_MODES ? ub::j4_count(lane) * warps_of(ub::j4_group(lane)) : 0u, 0u);
+      for (;;) {
+        uint32_t w = 0;
+        if (lane == 0) w = atomicAdd(&sh.next[2], 1u);
+        w = __shfl_sync(0xFFFFFFFFu, w, 0);
+        if (w >= stg.total) break;
+        uint32_t e, r0;
+        stg.decode(w, e, r0);
+        const uint32_t g = ub::j4_group(e), chunks = warps_of(g), local = r0 >> 5, k = local / chunks, r = (local - k * chunks) * 32 + lane;
+        if (r < g_count[g]) {
+          const uint32_t b = sh.list[g_start[g] + r];
+          ub::CellOut co[3];
+          const uint32_t nc = ub::j4_cells(e);
+          for (uint32_t s = 0; s < nc; s++) {
+            const uint2* q = cells + (size_t)(ub::UBT(j4_cell_base)[e] + k * nc + s) * 3 * EJ_T + b;
+            const uint2 a = ej_ld(q), s0 = ej_ld(q + EJ_T), s1 = ej_ld(q + 2 * EJ_T);
+            co[s].astc_lo = a.x; co[s].astc_hi = a.y;
+            ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
+          }
+          ub::Candidate c;
+          ub::j4_assemble(e, k, co, c);
+          uint32_t overall;
+          float uerr;
+          ub::j_score(sh.px + b * 17, c, sh.cls[b], flags, overall, uerr);
+          ej_st(scores + (size_t)(ub::UBT(j4_cand_base)[e] + k) * EJ_T + b, make_uint2(overall, __float_as_uint(uerr)));
+        }
+      }
+    } else {
       EjStage stg;
       stg.build(lane, ((en_cands >> lane) & 1u) ? warps_of(ub::jc_group(ub::UBT(j_cand)[lane])) : 0u, 0u);
       for (;;) {
@@ -896,7 +955,35 @@ __global__ void __launch_bounds__(EJ_THREADS, EJ_MIN_CTAS) k_encode_jobs(const _
 #pragma unroll
       for (uint32_t j = 0; j < 16; j++) px[j] = sh.px[tid * 17 + j];
 #endif
-      if (live && !solid) {
+      if (FULL) {
+        if (live && !solid) {
+          // the block's candidates in list order: the entries of its groups, every candidate of each
+          uint32_t overall[ub::J4_NUM_CAND], n = 0;
+          float uerr[ub::J4_NUM_CAND];
+          uint8_t modes[ub::J4_NUM_CAND], slots[ub::J4_NUM_CAND];
+          for (uint32_t e = 0; e < ub::J4_NUM_MODES; e++) {
+            if (!ub::j4_block_in_group(cls, ub::j4_group(e))) continue;
+            const uint32_t c0s = ub::UBT(j4_cand_base)[e], cnt = ub::j4_count(e);
+            for (uint32_t k = 0; k < cnt; k++) {
+              const uint2 v = ej_ld(scores + (size_t)(c0s + k) * EJ_T + tid);
+              overall[n] = v.x; uerr[n] = __uint_as_float(v.y);
+              modes[n] = (uint8_t)ub::j4_mode(e); slots[n] = (uint8_t)(c0s + k); n++;
+            }
+          }
+          const uint32_t gs = slots[ub::j_select(n, overall, uerr, modes, flags)];
+          uint32_t e = 0;
+          while (ub::UBT(j4_cand_base)[e + 1] <= gs) e++;
+          const uint32_t k = gs - ub::UBT(j4_cand_base)[e], nc = ub::j4_cells(e);
+          ub::CellOut co[3];
+          for (uint32_t s = 0; s < nc; s++) {
+            const uint2* q = cells + (size_t)(ub::UBT(j4_cell_base)[e] + k * nc + s) * 3 * EJ_T + tid;
+            const uint2 a = ej_ld(q), s0 = ej_ld(q + EJ_T), s1 = ej_ld(q + 2 * EJ_T);
+            co[s].astc_lo = a.x; co[s].astc_hi = a.y;
+            ((uint2*)co[s].sel)[0] = s0; ((uint2*)co[s].sel)[1] = s1;
+          }
+          ub::j4_assemble(e, k, co, win);
+        }
+      } else if (live && !solid) {
         const uint32_t mine = ub::j_block_cands(cls, en_cands);
         uint32_t overall[ub::J_MAX_CAND_SLOTS], n = 0;
         float uerr[ub::J_MAX_CAND_SLOTS];
@@ -1394,7 +1481,7 @@ extern "C" int b200_uastc_encode_image_dev_noalloc(const void* d_rgba, uint32_t 
   CU(cudaMemsetAsync(scratch, 0, EJ_SCRATCH_HEADER, st));   // the tile counter must start at zero; the rest is written before it is read
   EncDescPack pack;
   pack.d[0] = {(const uint8_t*)d_rgba, (uint4*)d_out, width, height, pitch, bx, 0};
-  k_encode_jobs<true><<<grid, EJ_T, sizeof(EjShared), st>>>(pack, nullptr, 1, n, pack_flags, d_any_alpha, (uint2*)scratch);
+  k_encode_jobs<true, false><<<grid, EJ_T, sizeof(EjShared), st>>>(pack, nullptr, 1, n, pack_flags, d_any_alpha, (uint2*)scratch);
   g_launches++;
   CU(cudaGetLastError());
   if (!stream) CU(cudaStreamSynchronize(st));

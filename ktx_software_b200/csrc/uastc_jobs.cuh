@@ -13,7 +13,7 @@
 //
 // Slots are static: candidate slot = position in the reference's candidate list if every mode were enabled and the
 // block were of every class; a block's own list is the enabled slots of its class groups in ascending slot order,
-// which is the reference's order.  Level 4 (no estimates, up to 170 candidates) keeps the block-at-a-time path.
+// which is the reference's order.  Level 4 (no estimates, 170 candidates) has its own, arithmetic slot enumeration (j4_*, below).
 #pragma once
 #include "uastc_encode.cuh"
 
@@ -149,6 +149,44 @@ UB_FN void j_score(const uint32_t* px, const Candidate& c, uint32_t cls, uint32_
   uerr = f_sqrt(u64_to_float(ue));
 }
 
+// ---- level 4 ("full"): no partition estimates -- every pattern of every partitioned mode and every rotation of every dual-plane
+// mode is a candidate (ENC:3290-3351 with estimate_partition off): 170 candidate slots and 343 cell slots, enumerated mode by
+// mode in the reference's list order.  Alpha modes are tried on opaque blocks too (always_try_alpha, ENC:3201-3256), so the
+// "alpha" group is every live block.  Within a warp-job all lanes share the mode AND the pattern: subsets have the same size in
+// every lane, which the block-at-a-time level-4 kernel (evaluate_solution at 13.7 of 32 lanes) could not offer.
+const uint32_t J4_NUM_MODES = 18, J4_NUM_CAND = 170, J4_NUM_CELL = 343;
+// mode, candidates, cells per candidate, group
+UB_TABLE(uint8_t, j4_modes, 72) = {
+  15, 1, 1, 0,  16, 30, 2, 0,  17, 1, 2, 0,
+  0, 1, 1, 1,  1, 1, 1, 1,  2, 30, 2, 1,  3, 11, 3, 1,  4, 30, 2, 1,  5, 1, 1, 1,  6, 3, 2, 1,  7, 19, 2, 1,  18, 1, 1, 1,
+  9, 30, 2, 2,  10, 1, 1, 2,  11, 4, 2, 2,  12, 1, 1, 2,  13, 4, 2, 2,  14, 1, 1, 2};
+UB_TABLE(uint16_t, j4_cand_base, 19) = {0, 1, 31, 32, 33, 34, 64, 75, 105, 106, 109, 128, 129, 159, 160, 164, 165, 169, 170};
+UB_TABLE(uint16_t, j4_cell_base, 19) = {0, 1, 61, 63, 64, 65, 125, 158, 218, 219, 225, 263, 264, 324, 325, 333, 334, 342, 343};
+UB_FN uint32_t j4_mode(uint32_t e) { return UBT(j4_modes)[e * 4]; }
+UB_FN uint32_t j4_count(uint32_t e) { return UBT(j4_modes)[e * 4 + 1]; }
+UB_FN uint32_t j4_cells(uint32_t e) { return UBT(j4_modes)[e * 4 + 2]; }
+UB_FN uint32_t j4_group(uint32_t e) { return UBT(j4_modes)[e * 4 + 3]; }
+UB_FN bool j4_block_in_group(uint32_t cls, uint32_t g) {
+  return g == J_GROUP_LA ? (cls & J_CLS_LA) != 0 : (g == J_GROUP_OPQ ? !(cls & J_CLS_ALPHA) : true);
+}
+// cell `cell` of candidate k of mode entry e
+UB_FN void j4_run_cell(uint32_t e, uint32_t k, uint32_t cell, const uint32_t* px, const EncCfg& cfg, CellOut& o) {
+  const uint32_t mode = j4_mode(e);
+  if (j_mode_dual(mode)) { dual_plane_cell(mode, k, cell, px, cfg, o); return; }
+  uint32_t la_px[16];
+  const bool la = (mode == 15 || mode == 16);
+  if (la) j_la_texels(px, la_px);
+  single_plane_cell(mode, j_mode_kind(mode), k, cell, la ? la_px : px, cfg, o);
+}
+UB_FN void j4_assemble(uint32_t e, uint32_t k, const CellOut* cells, Candidate& c) {
+  const uint32_t mode = j4_mode(e);
+  if (j_mode_dual(mode)) { dual_plane_assemble(mode, k, cells[0], cells[1], c); return; }
+  const int kind = j_mode_kind(mode);
+  const uint32_t n = j4_cells(e);
+  candidate_init(mode, kind ? k : 0u, 0, c);
+  for (uint32_t s = 0; s < n; s++) single_plane_place(mode, kind, kind ? k : 0u, s, cells[s], c, false);
+}
+
 // ---- block job, first half: the reference's selection rules (ENC:3456-3549) over the stored scores of the block's n
 // candidates (list order); modes[i] = mode of candidate i.  Returns the winning list index.
 UB_FN uint32_t j_select(uint32_t n, const uint32_t* overall, const float* uerr_f, const uint8_t* modes, uint32_t flags) {
@@ -254,8 +292,45 @@ UB_FN void j_finish_tail(Bits128& r, uint32_t etc1_at, const Etc1JobOut* jobs, u
 
 // The jobs of one block run one after the other: what the CUDA kernel computes, in the order a single thread would.
 // (Host checker; levels 0-3 only.)
+UB_FN Bits128 j_etc1_jobs_and_tail(const uint32_t* px, const EncCfg& cfg, Bits128 r, const uint32_t* dec, uint32_t mode, uint32_t etc1_at) {
+  const uint32_t js = etc1_job_slots(cfg.level, cfg.flags), nf = js & 3u, ni = js >> 2;
+  Etc1JobOut jobs[4];
+  for (uint32_t f = 0; f < nf; f++)
+    for (uint32_t i = 0; i < ni; i++) etc1_hints_job(mode, px, dec, cfg.level, cfg.flags, f, i, jobs[f * ni + i]);
+  j_finish_tail(r, etc1_at, jobs, nf * ni);
+  return r;
+}
+
+// level 4: the jobs of k_encode_jobs<.., true>, one block after the other
+UB_FN Bits128 encode_uastc_block_jobs_full(const uint32_t* px, uint32_t flags) {
+  const EncCfg cfg = enc_cfg_from_flags(flags);
+  const uint32_t cls = j_classify(px, cfg);
+  if (cls == J_CLS_SOLID) return j_finish(px, flags, nullptr, true, true, false);
+  uint32_t overall[J4_NUM_CAND], n = 0;
+  float uerr[J4_NUM_CAND];
+  uint8_t modes[J4_NUM_CAND], ent[J4_NUM_CAND], kk[J4_NUM_CAND];
+  Candidate c;
+  CellOut cells[3];
+  for (uint32_t e = 0; e < J4_NUM_MODES; e++) {
+    if (!j4_block_in_group(cls, j4_group(e))) continue;
+    for (uint32_t k = 0; k < j4_count(e); k++) {
+      for (uint32_t s = 0; s < j4_cells(e); s++) j4_run_cell(e, k, s, px, cfg, cells[s]);
+      j4_assemble(e, k, cells, c);
+      j_score(px, c, cls, flags, overall[n], uerr[n]);
+      modes[n] = (uint8_t)j4_mode(e); ent[n] = (uint8_t)e; kk[n] = (uint8_t)k; n++;
+    }
+  }
+  const uint32_t w = j_select(n, overall, uerr, modes, flags);
+  for (uint32_t s = 0; s < j4_cells(ent[w]); s++) j4_run_cell(ent[w], kk[w], s, px, cfg, cells[s]);
+  j4_assemble(ent[w], kk[w], cells, c);
+  uint32_t dec[16], mode, etc1_at;
+  const Bits128 r = j_finish_head(px, flags, &c, true, false, false, dec, mode, etc1_at);
+  return j_etc1_jobs_and_tail(px, cfg, r, dec, mode, etc1_at);
+}
+
 UB_FN Bits128 encode_uastc_block_jobs(const uint32_t* px, uint32_t flags) {
   const EncCfg cfg = enc_cfg_from_flags(flags);
+  if (cfg.level >= 4) return encode_uastc_block_jobs_full(px, flags);
   const uint32_t cls = j_classify(px, cfg);
   if (cls == J_CLS_SOLID) return j_finish(px, flags, nullptr, true, true, false);
   const uint32_t enabled = j_enabled_cands(cfg.mode_mask);
@@ -283,13 +358,8 @@ UB_FN Bits128 encode_uastc_block_jobs(const uint32_t* px, uint32_t flags) {
   const uint32_t gs = slot[j_select(n, overall, uerr, modes, flags)];
   j_assemble(gs, parts, cells + jc_cell0(UBT(j_cand)[gs]), c);
   uint32_t dec[16], mode, etc1_at;
-  Bits128 r = j_finish_head(px, flags, &c, true, false, false, dec, mode, etc1_at);
-  const uint32_t js = etc1_job_slots(cfg.level, cfg.flags), nf = js & 3u, ni = js >> 2;
-  Etc1JobOut jobs[4];
-  for (uint32_t f = 0; f < nf; f++)
-    for (uint32_t i = 0; i < ni; i++) etc1_hints_job(mode, px, dec, cfg.level, cfg.flags, f, i, jobs[f * ni + i]);
-  j_finish_tail(r, etc1_at, jobs, nf * ni);
-  return r;
+  const Bits128 r = j_finish_head(px, flags, &c, true, false, false, dec, mode, etc1_at);
+  return j_etc1_jobs_and_tail(px, cfg, r, dec, mode, etc1_at);
 }
 
 }  // namespace ub

@@ -111,7 +111,7 @@ PORT_API void port_encode_blocks(const uint8_t* px, uint64_t n, uint32_t flags, 
   }
 }
 
-// The same encode cut into jobs (csrc/uastc_jobs.cuh: what k_encode_jobs computes), one block after the other.  Levels 0-3.
+// The same encode cut into jobs (csrc/uastc_jobs.cuh: what k_encode_jobs computes), one block after the other (level 4: the j4_* enumeration).
 PORT_API void port_encode_blocks_jobs(const uint8_t* px, uint64_t n, uint32_t flags, uint8_t* out) {
   for (uint64_t i = 0; i < n; i++) {
     uint32_t p[16];

@@ -317,6 +317,23 @@ def test_job_decomposition_matches_reference(flags):
     assert len(bad) == 0, (flags, bad[:8])
 
 
+@pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built")
+def test_level4_job_decomposition_matches_reference():
+    """Level 4 as jobs (170 candidate slots, 343 cell slots, alpha modes on opaque blocks too: csrc/uastc_jobs.cuh j4_*), walked
+    by the host build, against the unmodified reference encoder."""
+    import ctypes
+    f = R.port().port_encode_blocks_jobs
+    f.argtypes = [R._u8p, ctypes.c_uint64, ctypes.c_uint32, R._u8p]
+    f.restype = None
+    px = np.concatenate([R.ref_extract_blocks(R.img_mix(64, 64, 1)), R.adversarial_blocks(3, 6), R.ref_extract_blocks(R.img_noise(16, 16, 2))])
+    for flags in (4, 4 | 512):
+        out = np.zeros((len(px), 16), np.uint8)
+        f(R._p(px), len(px), flags, R._p(out))
+        want = R.ref_encode_blocks(px, flags)
+        bad = np.nonzero((out != want).any(1))[0]
+        assert len(bad) == 0, (flags, bad[:8])
+
+
 def test_mode_specialised_transcoders_match_golden():
     """The code path the CUDA kernels run (mode as a template parameter) compiled for the host, against the reference outputs
     of the golden corpus: every mode, random payloads, invalid blocks."""
