@@ -208,6 +208,8 @@ def main():
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "r4_parity_sweep.json"))
     a = ap.parse_args()
     res = Sweep(a.quick).run(a.only.split(","))
+    import ktx_software_b200 as K
+    res["build"] = K.build_id()   # the library the sweep ran through (SHA-1 of its sources, as in bench.py's records)
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     json.dump(res, open(a.out, "w"), indent=1)
     print("SUMMARY", json.dumps({k: v for k, v in res.items() if k != "rows"}))
